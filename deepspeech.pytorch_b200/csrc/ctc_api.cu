@@ -1,0 +1,303 @@
+// csrc/ctc_api.cu -- C ABI of libctc_b200.so (see include/ctc_b200.h for the contract and the reference
+// interfaces each entry point replaces: warp-ctc's get_workspace_size / compute_ctc_loss / ctcGetStatusString /
+// get_warpctc_version reached from /root/reference/train.py:12,904,600,352,457 through warpctc_pytorch).
+//
+// Host side only plans the launch (shape -> lattice warps, rows per checkpoint block, shared memory, workspace
+// carving) and enqueues; it never synchronises the device and keeps no state besides a per-device
+// "max dynamic smem attribute already set" cache.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <new>
+
+#include "../../include/ctc_b200.h"
+#include "ctc_kernels.cuh"
+
+using namespace ctcb200;
+
+namespace {
+
+constexpr int kK = 8;               // states per lattice thread
+constexpr size_t kSmemLimit = 227 * 1024;
+thread_local int g_last_launches = 0;
+
+struct Plan {
+    int nwl;   // lattice warps per CTA
+    int R;     // rows per checkpoint block (16 or 8)
+    int nblk;  // ceil(T / R)
+    int Lmax;
+    size_t smem_engine, smem_grad;
+    // workspace byte offsets
+    size_t o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_lpos, o_coff, o_labels, o_llen, o_alen;
+    size_t total;
+};
+
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// Shape -> launch plan.  Returns false if the shape is outside what this build supports.
+bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
+    if (T < 0 || B < 1 || C < 2 || C > kMaxSmallC || Lmax < 0) return false;
+    const int S = 2 * Lmax + 1;
+    const int nwl = (S + 32 * kK - 1) / (32 * kK);
+    if (nwl > kMaxLatticeWarps) return false;  // label length > 1023
+    pl->nwl = nwl;
+    pl->Lmax = Lmax;
+    const int NT = nwl * 32;
+    int R = 16;
+    if (grad_smem(C, Lmax, NT, kK, R).total > kSmemLimit) R = 8;
+    if (grad_smem(C, Lmax, NT, kK, R).total > kSmemLimit) return false;
+    pl->R = R;
+    pl->nblk = T > 0 ? (T + R - 1) / R : 1;
+    pl->smem_engine = engine_smem(C, Lmax, R).total;
+    pl->smem_grad = grad_smem(C, Lmax, NT, kK, R).total;
+    if (pl->smem_engine > kSmemLimit) return false;
+    size_t o = 0;
+    const size_t ck = sizeof(double) * (size_t)B * pl->nblk * NT * kK;
+    const size_t ckE = sizeof(int) * (size_t)B * pl->nblk * NT;
+    pl->o_ckA = o;    o = align256(o + ck);
+    pl->o_ckB = o;    o = align256(o + ck);
+    pl->o_ckAE = o;   o = align256(o + ckE);
+    pl->o_ckBE = o;   o = align256(o + ckE);
+    pl->o_Pm = o;     o = align256(o + sizeof(double) * B);
+    pl->o_Pe = o;     o = align256(o + sizeof(int) * B);
+    pl->o_feas = o;   o = align256(o + sizeof(int) * B);
+    pl->o_laboff = o; o = align256(o + sizeof(int) * B);
+    pl->o_lpos = o;   o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
+    pl->o_coff = o;   o = align256(o + sizeof(int) * (size_t)B * (C + 1));
+    pl->o_labels = o; o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
+    pl->o_llen = o;   o = align256(o + sizeof(int) * B);
+    pl->o_alen = o;   o = align256(o + sizeof(int) * B);
+    pl->total = o;
+    return true;
+}
+
+template <int R>
+cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int *launches) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(ctc_engine_kernel<kK, R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_grad_kernel<kK, R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    const int engine_ctas = p.score_only ? p.B : 2 * p.B;
+    ctc_engine_kernel<kK, R><<<engine_ctas, (pl.nwl + 1) * 32, pl.smem_engine, st>>>(p);
+    ++*launches;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    if (!p.score_only && p.T > 0) {
+        dim3 grid(pl.nblk, p.B);
+        ctc_grad_kernel<kK, R><<<grid, pl.nwl * 32, pl.smem_grad, st>>>(p);
+        ++*launches;
+        e = cudaGetLastError();
+    }
+    return e;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ctc_b200_get_version(void) { return 100; }  // 0.1.0
+
+const char *ctc_b200_status_string(ctcB200Status s) {
+    switch (s) {
+        case CTC_B200_STATUS_SUCCESS: return "no error";
+        case CTC_B200_STATUS_MEMOPS_FAILED: return "cuda memcpy or memset failed";
+        case CTC_B200_STATUS_INVALID_VALUE: return "invalid value";
+        case CTC_B200_STATUS_EXECUTION_FAILED: return "execution failed";
+        default: return "unknown error";
+    }
+}
+
+void ctc_b200_default_options(ctcB200Options *o) {
+    if (!o) return;
+    memset(o, 0, sizeof(*o));
+    o->blank = 0;
+    o->zero_infinity = 1;
+    o->grad_scale = 1.0f;
+}
+
+ctcB200Status ctc_b200_workspace_size(int T, int B, int C, int max_label_len, const ctcB200Options *opts,
+                                      size_t *bytes) {
+    (void)opts;
+    if (!bytes) return CTC_B200_STATUS_INVALID_VALUE;
+    Plan pl;
+    if (!make_plan(T, B, C, max_label_len, &pl)) return CTC_B200_STATUS_INVALID_VALUE;
+    *bytes = pl.total;
+    return CTC_B200_STATUS_SUCCESS;
+}
+
+int ctc_b200_last_launch_count(void) { return g_last_launches; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------ compute
+extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const int *labels, const int *label_lens,
+                                          const int *act_lens, int T, int B, int C, float *costs, void *workspace,
+                                          size_t workspace_bytes, const ctcB200Options *opts_in) {
+    g_last_launches = 0;
+    ctcB200Options o;
+    if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
+    if (!acts || !costs || !label_lens || !act_lens || !workspace) return CTC_B200_STATUS_INVALID_VALUE;
+    if (B < 1 || T < 0 || C < 2 || o.blank < 0 || o.blank >= C) return CTC_B200_STATUS_INVALID_VALUE;
+    if (((uintptr_t)workspace & 255) != 0) return CTC_B200_STATUS_INVALID_VALUE;
+    cudaStream_t st = (cudaStream_t)o.stream;
+
+    int Lmax = o.max_label_len;
+    long long total_labels = 0;
+    if (!o.lengths_on_device) {
+        // host lengths (what train.py:600 passes): validate like warp-ctc would and derive the launch bound
+        int mx = 0;
+        for (int b = 0; b < B; ++b) {
+            if (label_lens[b] < 0 || act_lens[b] < 0 || act_lens[b] > T) return CTC_B200_STATUS_INVALID_VALUE;
+            mx = label_lens[b] > mx ? label_lens[b] : mx;
+            total_labels += label_lens[b];
+        }
+        if (total_labels > 0 && !labels) return CTC_B200_STATUS_INVALID_VALUE;
+        for (long long i = 0; i < total_labels; ++i)
+            if (labels[i] < 0 || labels[i] >= C || labels[i] == o.blank) return CTC_B200_STATUS_INVALID_VALUE;
+        Lmax = mx;
+    } else if (Lmax <= 0) {
+        return CTC_B200_STATUS_INVALID_VALUE;  // device lengths need an explicit bound
+    }
+    Plan pl;
+    if (!make_plan(T, B, C, Lmax, &pl)) return CTC_B200_STATUS_INVALID_VALUE;
+    if (workspace_bytes < pl.total) return CTC_B200_STATUS_INVALID_VALUE;
+
+    unsigned char *ws = static_cast<unsigned char *>(workspace);
+    CtcParams p;
+    memset(&p, 0, sizeof(p));
+    p.acts = acts;
+    p.grads = grads;
+    p.costs = costs;
+    if (o.lengths_on_device) {
+        p.labels = labels;
+        p.label_lens = label_lens;
+        p.act_lens = act_lens;
+    } else {
+        int *dl = reinterpret_cast<int *>(ws + pl.o_labels);
+        int *dll = reinterpret_cast<int *>(ws + pl.o_llen);
+        int *dal = reinterpret_cast<int *>(ws + pl.o_alen);
+        if (total_labels > 0 &&
+            cudaMemcpyAsync(dl, labels, sizeof(int) * (size_t)total_labels, cudaMemcpyHostToDevice, st) != cudaSuccess)
+            return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (cudaMemcpyAsync(dll, label_lens, sizeof(int) * B, cudaMemcpyHostToDevice, st) != cudaSuccess)
+            return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (cudaMemcpyAsync(dal, act_lens, sizeof(int) * B, cudaMemcpyHostToDevice, st) != cudaSuccess)
+            return CTC_B200_STATUS_MEMOPS_FAILED;
+        p.labels = dl;
+        p.label_lens = dll;
+        p.act_lens = dal;
+    }
+    p.T = T; p.B = B; p.C = C;
+    p.blank = o.blank;
+    p.zero_infinity = o.zero_infinity;
+    p.grad_scale = o.grad_scale;
+    p.nwl = pl.nwl;
+    p.nblk = pl.nblk;
+    p.Lmax = pl.Lmax;
+    p.score_only = grads ? 0 : 1;
+    p.ckA = reinterpret_cast<double *>(ws + pl.o_ckA);
+    p.ckB = reinterpret_cast<double *>(ws + pl.o_ckB);
+    p.ckAE = reinterpret_cast<int *>(ws + pl.o_ckAE);
+    p.ckBE = reinterpret_cast<int *>(ws + pl.o_ckBE);
+    p.Pm = reinterpret_cast<double *>(ws + pl.o_Pm);
+    p.Pe = reinterpret_cast<int *>(ws + pl.o_Pe);
+    p.feas = reinterpret_cast<int *>(ws + pl.o_feas);
+    p.laboff = reinterpret_cast<int *>(ws + pl.o_laboff);
+    p.lpos = reinterpret_cast<int *>(ws + pl.o_lpos);
+    p.coff = reinterpret_cast<int *>(ws + pl.o_coff);
+
+    int launches = 0;
+    cudaError_t e = (pl.R == 16) ? launch_all<16>(p, pl, st, &launches) : launch_all<8>(p, pl, st, &launches);
+    g_last_launches = launches;
+    return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
+}
+
+// ------------------------------------------------------------------------------------------------ host-buffer path
+struct ctcB200Context {
+    float *d_acts = nullptr, *d_grads = nullptr, *d_costs = nullptr;
+    void *d_ws = nullptr;
+    size_t n_acts = 0, n_costs = 0, n_ws = 0;
+};
+
+static bool grow(void **ptr, size_t *have, size_t need) {
+    if (need <= *have) return true;
+    if (*ptr) cudaFree(*ptr);
+    *ptr = nullptr;
+    *have = 0;
+    if (cudaMalloc(ptr, need) != cudaSuccess) return false;
+    *have = need;
+    return true;
+}
+
+extern "C" ctcB200Status ctc_b200_create(ctcB200Context **ctx) {
+    if (!ctx) return CTC_B200_STATUS_INVALID_VALUE;
+    *ctx = new (std::nothrow) ctcB200Context();
+    return *ctx ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_MEMOPS_FAILED;
+}
+
+extern "C" ctcB200Status ctc_b200_destroy(ctcB200Context *c) {
+    if (!c) return CTC_B200_STATUS_SUCCESS;
+    cudaFree(c->d_acts);
+    cudaFree(c->d_grads);
+    cudaFree(c->d_costs);
+    cudaFree(c->d_ws);
+    delete c;
+    return CTC_B200_STATUS_SUCCESS;
+}
+
+extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *acts_host, float *grads_host,
+                                               const int *labels, const int *label_lens, const int *act_lens, int T,
+                                               int B, int C, float *costs_host, double *loss_sum,
+                                               const ctcB200Options *opts_in) {
+    if (!c || !acts_host || !costs_host || !label_lens || !act_lens) return CTC_B200_STATUS_INVALID_VALUE;
+    ctcB200Options o;
+    if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
+    if (o.lengths_on_device) return CTC_B200_STATUS_INVALID_VALUE;
+    int mx = 0;
+    for (int b = 0; b < B; ++b) mx = label_lens[b] > mx ? label_lens[b] : mx;
+    size_t wsb = 0;
+    ctcB200Status s = ctc_b200_workspace_size(T, B, C, mx, &o, &wsb);
+    if (s != CTC_B200_STATUS_SUCCESS) return s;
+    const size_t nel = (size_t)T * B * C;
+    size_t n_grads = c->n_acts;
+    void *pa = c->d_acts, *pg = c->d_grads, *pc = c->d_costs;
+    size_t ha = c->n_acts, hc = c->n_costs;
+    if (!grow(&pa, &ha, nel * sizeof(float))) return CTC_B200_STATUS_MEMOPS_FAILED;
+    c->d_acts = (float *)pa; c->n_acts = ha;
+    if (grads_host) {
+        size_t hg = c->d_grads ? n_grads : 0;
+        if (!grow(&pg, &hg, nel * sizeof(float))) return CTC_B200_STATUS_MEMOPS_FAILED;
+        c->d_grads = (float *)pg;
+    }
+    if (!grow(&pc, &hc, sizeof(float) * B)) return CTC_B200_STATUS_MEMOPS_FAILED;
+    c->d_costs = (float *)pc; c->n_costs = hc;
+    if (!grow(&c->d_ws, &c->n_ws, wsb)) return CTC_B200_STATUS_MEMOPS_FAILED;
+    cudaStream_t st = (cudaStream_t)o.stream;
+    if (cudaMemcpyAsync(c->d_acts, acts_host, nel * sizeof(float), cudaMemcpyHostToDevice, st) != cudaSuccess)
+        return CTC_B200_STATUS_MEMOPS_FAILED;
+    s = ctc_b200_compute(c->d_acts, grads_host ? c->d_grads : nullptr, labels, label_lens, act_lens, T, B, C,
+                         c->d_costs, c->d_ws, c->n_ws, &o);
+    if (s != CTC_B200_STATUS_SUCCESS) return s;
+    if (grads_host &&
+        cudaMemcpyAsync(grads_host, c->d_grads, nel * sizeof(float), cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        return CTC_B200_STATUS_MEMOPS_FAILED;
+    if (cudaMemcpyAsync(costs_host, c->d_costs, sizeof(float) * B, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        return CTC_B200_STATUS_MEMOPS_FAILED;
+    if (cudaStreamSynchronize(st) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+    if (loss_sum) {
+        double acc = 0.0;
+        for (int b = 0; b < B; ++b) acc += (double)costs_host[b];
+        *loss_sum = acc;
+    }
+    return CTC_B200_STATUS_SUCCESS;
+}

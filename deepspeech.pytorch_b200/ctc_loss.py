@@ -1,0 +1,181 @@
+"""Drop-in for the reference's `CTCLoss` (from warpctc_pytorch; /root/reference/train.py:12, ctor :904).
+
+    criterion = CTCLoss()
+    loss = criterion(acts, labels, act_lens, label_lens)      # train.py:600 ; eval: train.py:352, :457
+
+Same argument meaning as the reference call sites:
+    acts        cuda fp32 [T,B,C] unnormalised logits (a non-contiguous view is accepted; train.py:593)
+    labels      int32 1-D, flat concatenation of the targets (data/data_loader_aug.py:546-547) -- CPU (reference)
+                or CUDA
+    act_lens    int32 [B] (`output_sizes.cpu()`, model.py:382-393) -- CPU or CUDA
+    label_lens  int32 [B] (`target_sizes`, data_loader_aug.py:545) -- CPU or CUDA
+returns a 1-element fp32 tensor: sum over the batch of -log p(l_b|x_b)  (the caller divides by B, train.py:601).
+Like the reference binding, gradients w.r.t. acts are produced in the same pass as the costs and the autograd
+backward is `grads * grad_output`.
+
+Everything runs through the C ABI of libctc_b200.so (include/ctc_b200.h) with raw pointers; there is no CPU
+fallback: tensors that are not CUDA fp32, or a missing library, raise.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+_ws_cache = {}
+
+
+def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _ws_cache.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)
+        _ws_cache[key] = ws
+    return ws
+
+
+def _as_i32(x, name: str) -> torch.Tensor:
+    if not isinstance(x, torch.Tensor):
+        x = torch.as_tensor(x, dtype=torch.int32)
+    if x.dtype != torch.int32:
+        x = x.to(torch.int32)
+    if x.requires_grad:
+        raise ValueError(f"{name} must not require grad")
+    return x.contiguous().view(-1)
+
+
+def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank: int = 0,
+                         zero_infinity: bool = True, grad_scale: float = 1.0, want_grads: bool = True,
+                         max_label_len: Optional[int] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
+
+    No host synchronisation happens here when labels/lengths are CUDA tensors (then `max_label_len` is required);
+    with CPU labels/lengths (the reference's calling convention) they are staged to the device inside the call.
+    """
+    if not (isinstance(acts, torch.Tensor) and acts.is_cuda and acts.dtype == torch.float32 and acts.dim() == 3):
+        raise ValueError("acts must be a CUDA float32 tensor of shape [T,B,C] (no CPU fallback exists)")
+    lib = _lib.load()
+    acts_c = acts.detach().contiguous()
+    T, B, C = acts_c.shape
+    labels = _as_i32(labels, "labels")
+    act_lens = _as_i32(act_lens, "act_lens")
+    label_lens = _as_i32(label_lens, "label_lens")
+    if act_lens.numel() != B or label_lens.numel() != B:
+        raise ValueError("act_lens and label_lens must have one entry per batch element")
+    on_dev = act_lens.is_cuda
+    if labels.is_cuda != on_dev or label_lens.is_cuda != on_dev:
+        raise ValueError("labels, act_lens and label_lens must all live on the host or all on the device")
+    dev = acts_c.device
+    opts = _lib.CtcOptions()
+    lib.ctc_b200_default_options(ctypes.byref(opts))
+    with torch.cuda.device(dev):
+        opts.stream = torch.cuda.current_stream(dev).cuda_stream
+        opts.blank = int(blank)
+        opts.zero_infinity = int(bool(zero_infinity))
+        opts.grad_scale = float(grad_scale)
+        opts.lengths_on_device = int(on_dev)
+        if on_dev:
+            if max_label_len is None:
+                raise ValueError("max_label_len is required when lengths live on the device (avoids a sync)")
+            lmax = int(max_label_len)
+        else:
+            lmax = int(label_lens.max().item()) if B > 0 else 0
+            if max_label_len is not None:
+                lmax = max(lmax, int(max_label_len))
+        opts.max_label_len = lmax
+        nbytes = ctypes.c_size_t(0)
+        _lib.check(lib.ctc_b200_workspace_size(T, B, C, lmax, ctypes.byref(opts), ctypes.byref(nbytes)),
+                   "ctc_b200_workspace_size")
+        ws = _workspace(dev, nbytes.value)
+        ws_ptr = (ws.data_ptr() + 255) & ~255
+        ws_len = ws.numel() - (ws_ptr - ws.data_ptr())
+        costs = torch.empty(B, dtype=torch.float32, device=dev)
+        grads = torch.empty_like(acts_c) if want_grads else None
+        st = lib.ctc_b200_compute(acts_c.data_ptr(), grads.data_ptr() if want_grads else None,
+                                  labels.data_ptr() if labels.numel() else None, label_lens.data_ptr(),
+                                  act_lens.data_ptr(), T, B, C, costs.data_ptr(), ws_ptr, ws_len, ctypes.byref(opts))
+        _lib.check(st, "ctc_b200_compute")
+    return costs, grads
+
+
+def last_launch_count() -> int:
+    return int(_lib.load().ctc_b200_last_launch_count())
+
+
+# ---------------------------------------------------------------------------------------------- torch custom op
+@torch.library.custom_op("ctc_b200::ctc_loss", mutates_args=(), device_types="cuda")
+def _ctc_loss_op(acts: torch.Tensor, labels: torch.Tensor, act_lens: torch.Tensor, label_lens: torch.Tensor,
+                 blank: int, zero_infinity: bool, grad_scale: float, want_grads: bool,
+                 max_label_len: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    costs, grads = ctc_forward_backward(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale,
+                                        want_grads, max_label_len if max_label_len >= 0 else None)
+    if grads is None:
+        grads = torch.empty(0, dtype=torch.float32, device=acts.device)
+    return costs, grads
+
+
+@_ctc_loss_op.register_fake
+def _(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale, want_grads, max_label_len):
+    costs = acts.new_empty((acts.shape[1],))
+    grads = torch.empty_like(acts) if want_grads else acts.new_empty((0,))
+    return costs, grads
+
+
+class _CTCFunction(torch.autograd.Function):
+    """forward: costs and grads in one pass (grads cached); backward: grads * grad_output -- the reference
+    binding's autograd contract."""
+
+    @staticmethod
+    def forward(ctx, acts, labels, act_lens, label_lens, blank, zero_infinity, scale, max_label_len, want):
+        costs, grads = _ctc_loss_op(acts, labels, act_lens, label_lens, blank, zero_infinity, scale, want,
+                                    -1 if max_label_len is None else int(max_label_len))
+        ctx.has_grads = want
+        if want:
+            ctx.save_for_backward(grads)
+        loss = costs.sum().reshape(1)
+        return loss * scale if scale != 1.0 else loss
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        if not ctx.has_grads:
+            return (None,) * 9
+        (grads,) = ctx.saved_tensors
+        return (grads * grad_output.reshape(1, 1, 1).to(grads.device),) + (None,) * 8
+
+
+class CTCLoss(torch.nn.Module):
+    """`CTCLoss()` as constructed at /root/reference/train.py:904.
+
+    blank=0, size_average=False, length_average=False are the reference binding's defaults: the result is the SUM
+    of the per-utterance costs.  size_average divides loss and gradients by B, length_average by sum(act_lens)
+    (both folded into the kernel's gradient scale, no extra pass).  zero_infinity=True gives an infeasible
+    utterance (L + repeats > T) cost 0 and zero gradient (warp-ctc's CPU behaviour); False gives cost +inf with
+    zero gradient.  loss_on_cpu=True returns the loss on the host exactly like the reference binding does
+    (`loss.to(device)` at train.py:602 is then a real copy); the default keeps it on the device and avoids a sync.
+    """
+
+    def __init__(self, blank: int = 0, size_average: bool = False, length_average: bool = False,
+                 zero_infinity: bool = True, loss_on_cpu: bool = False):
+        super().__init__()
+        self.blank = blank
+        self.size_average = size_average
+        self.length_average = length_average
+        self.zero_infinity = zero_infinity
+        self.loss_on_cpu = loss_on_cpu
+
+    def forward(self, acts, labels, act_lens, label_lens, max_label_len: Optional[int] = None):
+        if labels.dim() != 1:
+            raise ValueError("labels must be 1-D (flat concatenation of the targets)")
+        scale = 1.0
+        if self.length_average:
+            scale = 1.0 / float(torch.as_tensor(act_lens).sum().item())
+        elif self.size_average:
+            scale = 1.0 / float(acts.shape[1])
+        # grad mode is off inside autograd.Function.forward, so decide here whether gradients are wanted
+        want = bool(acts.requires_grad and torch.is_grad_enabled())
+        loss = _CTCFunction.apply(acts, labels, act_lens, label_lens, self.blank, self.zero_infinity, scale,
+                                  max_label_len, want)
+        return loss.cpu() if self.loss_on_cpu else loss

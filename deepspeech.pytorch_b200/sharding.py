@@ -1,0 +1,63 @@
+"""Batch sharding across the GPUs of one box, and the single loss all-reduce.
+
+Utterances are independent, so the CTC path shards on the batch axis with no data-path collective: each rank keeps
+acts[:, R_r, :], its label slice and lengths, and produces grads[:, R_r, :] locally.  The only exchange step is a
+scalar: the summed loss.  This generalises the reference's DistributedBucketingSampler
+(/root/reference/data/data_loader_aug.py:582-617: rank-strided bins of duration-sorted ids) and replaces
+`reduce_tensor` (/root/reference/data/utils.py:40-44: clone -> all_reduce(SUM) -> /world_size, gloo by default,
+train.py:99) with one all-reduce on the compute stream (NCCL over NVLink/NVSwitch on the GPU box).
+"""
+from __future__ import annotations
+
+from typing import List, Sequence
+
+import torch
+
+
+def lattice_work(act_lens: Sequence[int], label_lens: Sequence[int]) -> List[int]:
+    """Per-utterance lattice work T_b * S_b (S_b = 2 L_b + 1): what the recursion kernels' time follows."""
+    return [int(t) * (2 * int(l) + 1) for t, l in zip(act_lens, label_lens)]
+
+
+def length_bucketed_shards(act_lens: Sequence[int], label_lens: Sequence[int], world_size: int) -> List[List[int]]:
+    """Longest-processing-time-first deal of utterance ids to ranks, balanced on lattice work, with equal shard
+    sizes when B divides evenly (so every rank launches the same grid).  Within a shard ids are ordered
+    longest-first so the longest recursion starts first.  Deterministic."""
+    B = len(act_lens)
+    w = lattice_work(act_lens, label_lens)
+    order = sorted(range(B), key=lambda i: (-w[i], i))
+    cap = (B + world_size - 1) // world_size
+    shards: List[List[int]] = [[] for _ in range(world_size)]
+    load = [0] * world_size
+    for i in order:
+        r = min((r for r in range(world_size) if len(shards[r]) < cap), key=lambda r: (load[r], r))
+        shards[r].append(i)
+        load[r] += w[i]
+    return shards
+
+
+def take_shard(acts: torch.Tensor, labels: torch.Tensor, act_lens: torch.Tensor, label_lens: torch.Tensor,
+               ids: Sequence[int]):
+    """Slice one rank's utterances out of a packed batch (acts [T,B,C], flat labels)."""
+    offs = torch.zeros(label_lens.numel() + 1, dtype=torch.int64)
+    offs[1:] = torch.cumsum(label_lens.to(torch.int64), 0)
+    idx = torch.as_tensor(list(ids), dtype=torch.int64)
+    lab = [labels[int(offs[i]):int(offs[i + 1])] for i in ids]
+    flat = torch.cat(lab) if lab else labels[:0]
+    return acts[:, idx.to(acts.device), :].contiguous(), flat.contiguous(), act_lens[idx].contiguous(), \
+        label_lens[idx].contiguous()
+
+
+def all_reduce_loss(loss_sum: torch.Tensor, mean_of_means: bool = False, local_batch: int = 1) -> torch.Tensor:
+    """The path's one collective.  Default: global SUM of the per-rank summed losses (north-star).
+    mean_of_means=True reproduces the reference's logging value: each rank's batch-mean, summed, / world_size
+    (data/utils.py:40-44 applied to train.py:601's `loss / B`)."""
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return loss_sum / local_batch if mean_of_means else loss_sum
+    rt = (loss_sum / local_batch).clone() if mean_of_means else loss_sum.clone()
+    dist.all_reduce(rt, op=dist.ReduceOp.SUM)
+    if mean_of_means:
+        rt /= dist.get_world_size()
+    return rt

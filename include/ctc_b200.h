@@ -1,0 +1,106 @@
+/*
+ * include/ctc_b200.h -- C ABI of the B200-native CTC loss library (libctc_b200.so).
+ *
+ * Drop-in boundary for the ONE hot path of vadimkantorov/deepspeech.pytorch: the CTC loss forward+backward
+ *     loss = criterion(logits, targets, output_sizes.cpu(), target_sizes)        /root/reference/train.py:600
+ *     (same call under no_grad at train.py:352 and train.py:457; criterion = CTCLoss() at train.py:904,
+ *      imported from the third-party `warpctc_pytorch` at train.py:12).
+ * The reference reaches native code for this path through warpctc_pytorch's binding over warp-ctc's C API
+ * (get_workspace_size / compute_ctc_loss / ctcGetStatusString / get_warpctc_version -- external, un-vendored,
+ * described from its published interface in SURVEY.md section 8(b)).  The entry points below are what a binding
+ * for this path binds instead; each names the interface it replaces.  Plain pointers and sizes only -- no torch
+ * types cross this boundary.  The reference-side stub is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   acts   : DEVICE fp32 [T,B,C] contiguous, unnormalised logits (train.py:593 "TxNxH")
+ *   grads  : DEVICE fp32 [T,B,C] contiguous, receives grad_scale * d(sum_b cost_b)/d acts; every element is
+ *            written exactly once (rows t >= act_lens[b] and infeasible utterances get zeros).  NULL => score only
+ *            (the eval call sites train.py:352,457 use only the cost).
+ *   labels : int32 flat concatenation of the B targets in batch order (data/data_loader_aug.py:546-547),
+ *            values in [0,C) and != blank
+ *   label_lens, act_lens : int32 [B]            (data_loader_aug.py:545, model.py:382-393 via train.py:600)
+ *   costs  : DEVICE fp32 [B], -log p(l_b | x_b); the caller sums (train.py:601 then divides by B)
+ *   lengths/labels may live on the host (what the reference passes) or on the device (lets the caller drop the
+ *            `.cpu()` sync at train.py:600) -- see ctcB200Options.lengths_on_device
+ *   All work is enqueued on options->stream; no call synchronises the device or keeps global state.
+ *   Errors are returned as ctcB200Status, never thrown or aborted.
+ */
+#ifndef CTC_B200_H_
+#define CTC_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* replaces warp-ctc's ctcStatus_t (same five states) */
+typedef enum {
+    CTC_B200_STATUS_SUCCESS = 0,
+    CTC_B200_STATUS_MEMOPS_FAILED = 1,
+    CTC_B200_STATUS_INVALID_VALUE = 2,
+    CTC_B200_STATUS_EXECUTION_FAILED = 3,
+    CTC_B200_STATUS_UNKNOWN_ERROR = 4
+} ctcB200Status;
+
+/* replaces warp-ctc's ctcOptions {loc, stream|num_threads, blank_label}; there is no CPU location here */
+typedef struct {
+    void *stream;          /* cudaStream_t; NULL = legacy default stream */
+    int blank;             /* blank label index; the reference uses 0 (labels.json "_", train.py:904 defaults) */
+    int zero_infinity;     /* 1: infeasible utterance (L + repeats > T) -> cost 0 ; 0: cost +inf.  Its grads are 0
+                              in both modes (never NaN). */
+    float grad_scale;      /* multiplies every gradient (fuses train.py:601 `loss / B` into the kernel); 1.0 = raw */
+    int lengths_on_device; /* 0: labels/label_lens/act_lens are HOST pointers (reference behaviour)
+                              1: they are DEVICE pointers; max_label_len must then be given */
+    int max_label_len;     /* upper bound on label_lens[b]; <=0 means "derive it" (host lengths only) */
+    int reserved[4];       /* must be zero */
+} ctcB200Options;
+
+/* replaces get_warpctc_version() */
+int ctc_b200_get_version(void);
+
+/* replaces ctcGetStatusString() */
+const char *ctc_b200_status_string(ctcB200Status status);
+
+/* fills `opts` with the reference's defaults: blank 0, zero_infinity 1, grad_scale 1, host lengths */
+void ctc_b200_default_options(ctcB200Options *opts);
+
+/*
+ * replaces get_workspace_size(label_lengths, input_lengths, alphabet_size, minibatch, options, &bytes).
+ * Shape-only query (no pointers are dereferenced): T = max time steps, B = minibatch, C = alphabet size,
+ * max_label_len = upper bound on any label length.  Workspace is caller-owned scratch; contents are
+ * meaningless between calls.
+ */
+ctcB200Status ctc_b200_workspace_size(int T, int B, int C, int max_label_len, const ctcB200Options *opts,
+                                      size_t *bytes);
+
+/*
+ * replaces compute_ctc_loss(activations, gradients, flat_labels, label_lengths, input_lengths, alphabet_size,
+ *                           minibatch, costs, workspace, options).
+ * Enqueues the whole forward+backward on opts->stream and returns.  workspace must be a DEVICE buffer of at
+ * least the size reported by ctc_b200_workspace_size for the same (T,B,C,max_label_len), 256-byte aligned.
+ */
+ctcB200Status ctc_b200_compute(const float *acts, float *grads, const int *labels, const int *label_lens,
+                               const int *act_lens, int T, int B, int C, float *costs, void *workspace,
+                               size_t workspace_bytes, const ctcB200Options *opts);
+
+/*
+ * Host-buffer convenience path (what a non-torch caller of the reference's CPU location would use, and what
+ * bench.py's end-to-end leg times): acts/grads/costs are HOST pointers (pinned memory recommended); the call
+ * stages them through device buffers owned by `ctx`, runs ctc_b200_compute and copies results back, all on
+ * opts->stream, then synchronises that stream.  *loss_sum receives sum_b costs[b].
+ */
+typedef struct ctcB200Context ctcB200Context;
+ctcB200Status ctc_b200_create(ctcB200Context **ctx);
+ctcB200Status ctc_b200_destroy(ctcB200Context *ctx);
+ctcB200Status ctc_b200_compute_host(ctcB200Context *ctx, const float *acts_host, float *grads_host,
+                                    const int *labels, const int *label_lens, const int *act_lens, int T, int B,
+                                    int C, float *costs_host, double *loss_sum, const ctcB200Options *opts);
+
+/* number of kernel launches the last ctc_b200_compute on this thread enqueued (bench.py's gpu_launches claim) */
+int ctc_b200_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTC_B200_H_ */

@@ -1,0 +1,170 @@
+"""Parity of the CUDA path (through the C ABI / public op) against the CPU oracle.  Run with -m gpu on a B200.
+
+Tolerance (BASELINE.json north_star): loss rel <= 1e-5, grad abs <= 1e-5 against the fp64 oracle.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL = 1e-5
+GRAD_ATOL = 1e-5
+
+
+def _run(b200, d, zero_infinity=True, device_lens=False, want_grads=True, grad_scale=1.0):
+    acts = d["acts"].cuda()
+    lab, al, ll = d["labels"], d["act_lens"], d["label_lens"]
+    kw = {}
+    if device_lens:
+        kw["max_label_len"] = int(ll.max())
+        lab, al, ll = lab.cuda(), al.cuda(), ll.cuda()
+    costs, grads = b200.ctc_forward_backward(acts, lab, al, ll, blank=0, zero_infinity=zero_infinity,
+                                             grad_scale=grad_scale, want_grads=want_grads, **kw)
+    torch.cuda.synchronize()
+    return costs.cpu().numpy().astype(np.float64), (grads.cpu().numpy().astype(np.float64) if want_grads else None)
+
+
+def _check(oracle, b200, d, **kw):
+    costs, grads = _run(b200, d, **kw)
+    oc, og = oracle.compute(d["acts"].numpy(), d["labels"].numpy(), d["act_lens"].numpy(), d["label_lens"].numpy(),
+                            zero_infinity=kw.get("zero_infinity", True))
+    fin = np.isfinite(oc)
+    assert np.array_equal(np.isfinite(costs), fin)
+    rel = np.abs(costs[fin] - oc[fin]) / np.maximum(np.abs(oc[fin]), 1e-30)
+    # per-utterance costs are fp32 on the device: allow fp32 rounding of the value itself
+    assert rel.max(initial=0.0) <= LOSS_RTOL, f"cost rel err {rel.max()}"
+    tot_rel = abs(costs[fin].sum() - oc[fin].sum()) / max(abs(oc[fin].sum()), 1e-30)
+    assert tot_rel <= LOSS_RTOL
+    if grads is not None:
+        err = np.abs(grads - og * kw.get("grad_scale", 1.0)).max()
+        assert err <= GRAD_ATOL, f"grad max-abs err {err}"
+    return costs, grads
+
+
+def _wl(b200, name, **kw):
+    return b200.workloads.make(b200.workloads.CONFIGS[name], **kw)
+
+
+def test_tiny_closed_form(oracle, b200):
+    # T=3, L=2 with and without a repeated label: enumeration over all C^T alignments
+    rng = np.random.default_rng(0)
+    for label in ([1, 2], [2, 2], [1], []):
+        T = 3 if len(label) else 2
+        a = rng.standard_normal((T, 1, 4)).astype(np.float32)
+        d = {"acts": torch.from_numpy(a), "labels": torch.tensor(label, dtype=torch.int32),
+             "act_lens": torch.tensor([T], dtype=torch.int32), "label_lens": torch.tensor([len(label)], dtype=torch.int32)}
+        costs, grads = _run(b200, d)
+        bf = oracle.brute_force_cost(a[:, 0], label)
+        if np.isfinite(bf):
+            assert abs(costs[0] - bf) <= 1e-5 * abs(bf)
+            g = oracle.brute_force_grad(a[:, 0], label)
+            assert np.abs(grads[:, 0] - g).max() <= 1e-5
+        else:
+            assert costs[0] == 0.0 and np.all(grads == 0)
+
+
+@pytest.mark.parametrize("C", [29, 30])
+def test_config1_cpu_shape(oracle, b200, C):
+    _check(oracle, b200, _wl(b200, "cpu_b16_t500", C=C))
+
+
+@pytest.mark.parametrize("sigma", [1.0, 5.0])
+def test_config2_headline(oracle, b200, sigma):
+    d = _wl(b200, "headline_b64_t1500", sigma=sigma)
+    costs, grads = _check(oracle, b200, d)
+    # padded frames: exactly zero gradient rows; valid rows sum to zero over classes
+    al = d["act_lens"].numpy()
+    for b in range(0, 64, 7):
+        assert np.all(grads[al[b]:, b, :] == 0.0)
+    assert np.abs(grads.sum(axis=2)).max() <= 2e-5
+
+
+def test_config2_no_repeats_and_device_lengths(oracle, b200):
+    d = _wl(b200, "headline_b64_t1500", no_repeats=True, seed=99)
+    _check(oracle, b200, d, device_lens=True)
+
+
+def test_config3_long(oracle, b200):
+    _check(oracle, b200, _wl(b200, "long_b32_t4000", B=8))
+
+
+def test_config3_long_peaky(oracle, b200):
+    _check(oracle, b200, _wl(b200, "long_b32_t4000", B=4, sigma=5.0, seed=5))
+
+
+def test_grad_scale_and_score_only(oracle, b200):
+    d = _wl(b200, "cpu_b16_t500")
+    _check(oracle, b200, d, grad_scale=1.0 / 16)
+    c1, _ = _run(b200, d, want_grads=False)
+    c2, _ = _run(b200, d, want_grads=True)
+    assert np.array_equal(c1, c2)
+
+
+def test_deterministic(b200):
+    d = _wl(b200, "cpu_b16_t500", seed=3)
+    c1, g1 = _run(b200, d)
+    c2, g2 = _run(b200, d)
+    assert np.array_equal(c1, c2) and np.array_equal(g1, g2)
+
+
+def test_edge_cases(oracle, b200):
+    # ragged: infeasible (L + repeats > T), L = 0, T_b = 1, tight T == L + repeats, repeated labels
+    C, T = 6, 40
+    g = torch.Generator().manual_seed(11)
+    acts = torch.randn(T, 6, C, generator=g)
+    targets = [[1, 1, 1, 1], [], [2], [3, 3, 4, 4, 5], [1, 2, 3, 4, 5, 1, 2, 3], [5] * 30]
+    act_lens = torch.tensor([6, 40, 1, 7, 8, 40], dtype=torch.int32)  # utt0: needs 7 > 6 -> infeasible; utt5: 59 > 40
+    labels, ll = b200.pack_targets(targets)
+    d = {"acts": acts, "labels": labels, "act_lens": act_lens, "label_lens": ll}
+    costs, grads = _check(oracle, b200, d, zero_infinity=True)
+    assert costs[0] == 0.0 and costs[5] == 0.0 and np.all(grads[:, 0] == 0) and np.all(grads[:, 5] == 0)
+    costs, grads = _run(b200, d, zero_infinity=False)
+    assert np.isinf(costs[0]) and np.isinf(costs[5]) and np.all(np.isfinite(grads)) and np.all(grads[:, 0] == 0)
+
+
+def test_uniform_logits_count(oracle, b200):
+    # uniform logits: cost = -log(#alignments / C^T)
+    C, T = 5, 12
+    label = [1, 2, 2, 3]
+    d = {"acts": torch.zeros(T, 1, C), "labels": torch.tensor(label, dtype=torch.int32),
+         "act_lens": torch.tensor([T], dtype=torch.int32), "label_lens": torch.tensor([len(label)], dtype=torch.int32)}
+    costs, _ = _run(b200, d)
+    want = -(np.log(oracle.count_alignments(T, label)) - T * np.log(C))
+    assert abs(costs[0] - want) <= 1e-5 * want
+
+
+def test_module_matches_reference_call(oracle, b200):
+    # the reference's train-step block (train.py:593-620): transpose view, criterion, /B, backward
+    w = b200.workloads.Workload("m", 8, 120, 30, 30, 0.05, 0.2)
+    d = b200.workloads.make(w, seed=21)
+    logits_btc = d["acts"].transpose(0, 1).contiguous().cuda().requires_grad_(True)  # model output [B,T,C]
+    crit = b200.CTCLoss()
+    loss = crit(logits_btc.transpose(0, 1), d["labels"], d["act_lens"], d["label_lens"])
+    loss = loss / w.B
+    loss = loss.to("cuda")
+    loss.backward()
+    oc, og = oracle.compute(d["acts"].numpy(), d["labels"].numpy(), d["act_lens"].numpy(), d["label_lens"].numpy())
+    assert loss.shape == (1,)
+    assert abs(loss.item() * w.B - oc.sum()) <= 1e-5 * oc.sum()
+    g = logits_btc.grad.transpose(0, 1).cpu().numpy().astype(np.float64) * w.B
+    assert np.abs(g - og).max() <= 1e-5
+    with torch.no_grad():  # eval call sites train.py:352,457: score only
+        l2 = crit(logits_btc.transpose(0, 1), d["labels"], d["act_lens"], d["label_lens"])
+    assert abs(l2.item() - oc.sum()) <= 1e-5 * oc.sum()
+    crit_avg = b200.CTCLoss(size_average=True, loss_on_cpu=True)
+    l3 = crit_avg(logits_btc.detach().transpose(0, 1), d["labels"], d["act_lens"], d["label_lens"])
+    assert not l3.is_cuda and abs(l3.item() * w.B - oc.sum()) <= 1e-5 * oc.sum()
+
+
+def test_errors(b200):
+    a = torch.randn(10, 2, 5)
+    with pytest.raises(ValueError):
+        b200.ctc_forward_backward(a, torch.tensor([1], dtype=torch.int32), torch.tensor([10, 10], dtype=torch.int32),
+                                  torch.tensor([1, 0], dtype=torch.int32))  # CPU acts: no fallback
+    with pytest.raises(RuntimeError):  # label == blank
+        b200.ctc_forward_backward(a.cuda(), torch.tensor([0], dtype=torch.int32),
+                                  torch.tensor([10, 10], dtype=torch.int32), torch.tensor([1, 0], dtype=torch.int32))
+    with pytest.raises(RuntimeError):  # act_len > T
+        b200.ctc_forward_backward(a.cuda(), torch.tensor([1], dtype=torch.int32),
+                                  torch.tensor([11, 10], dtype=torch.int32), torch.tensor([1, 0], dtype=torch.int32))

@@ -74,7 +74,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
 }
 
 template <int R>
-cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int *launches) {
+cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -88,11 +88,14 @@ cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const int engine_ctas = p.score_only ? p.B : 2 * p.B;
-    ctc_engine_kernel<kK, R><<<engine_ctas, (pl.nwl + 1) * 32, pl.smem_engine, st>>>(p);
-    ++*launches;
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    if (!p.score_only && p.T > 0) {
+    cudaError_t e = cudaSuccess;
+    if (!(phase_mask & 1)) {
+        ctc_engine_kernel<kK, R><<<engine_ctas, (pl.nwl + 1) * 32, pl.smem_engine, st>>>(p);
+        ++*launches;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (!p.score_only && p.T > 0 && !(phase_mask & 2)) {
         dim3 grid(pl.nblk, p.B);
         ctc_grad_kernel<kK, R><<<grid, pl.nwl * 32, pl.smem_grad, st>>>(p);
         ++*launches;
@@ -217,7 +220,7 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
     p.coff = reinterpret_cast<int *>(ws + pl.o_coff);
 
     int launches = 0;
-    cudaError_t e = (pl.R == 16) ? launch_all<16>(p, pl, st, &launches) : launch_all<8>(p, pl, st, &launches);
+    cudaError_t e = (pl.R == 16) ? launch_all<16>(p, pl, st, o.phase_mask, &launches) : launch_all<8>(p, pl, st, o.phase_mask, &launches);
     g_last_launches = launches;
     return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }

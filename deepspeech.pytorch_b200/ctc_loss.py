@@ -49,7 +49,8 @@ def _as_i32(x, name: str) -> torch.Tensor:
 
 def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank: int = 0,
                          zero_infinity: bool = True, grad_scale: float = 1.0, want_grads: bool = True,
-                         max_label_len: Optional[int] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+                         max_label_len: Optional[int] = None, phase_mask: int = 0,
+                         out_grads: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
 
     No host synchronisation happens here when labels/lengths are CUDA tensors (then `max_label_len` is required);
@@ -86,6 +87,7 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
             if max_label_len is not None:
                 lmax = max(lmax, int(max_label_len))
         opts.max_label_len = lmax
+        opts.phase_mask = int(phase_mask)
         nbytes = ctypes.c_size_t(0)
         _lib.check(lib.ctc_b200_workspace_size(T, B, C, lmax, ctypes.byref(opts), ctypes.byref(nbytes)),
                    "ctc_b200_workspace_size")
@@ -93,7 +95,7 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
         ws_ptr = (ws.data_ptr() + 255) & ~255
         ws_len = ws.numel() - (ws_ptr - ws.data_ptr())
         costs = torch.empty(B, dtype=torch.float32, device=dev)
-        grads = torch.empty_like(acts_c) if want_grads else None
+        grads = (out_grads if out_grads is not None else torch.empty_like(acts_c)) if want_grads else None
         st = lib.ctc_b200_compute(acts_c.data_ptr(), grads.data_ptr() if want_grads else None,
                                   labels.data_ptr() if labels.numel() else None, label_lens.data_ptr(),
                                   act_lens.data_ptr(), T, B, C, costs.data_ptr(), ws_ptr, ws_len, ctypes.byref(opts))

@@ -53,7 +53,10 @@ typedef struct {
     int lengths_on_device; /* 0: labels/label_lens/act_lens are HOST pointers (reference behaviour)
                               1: they are DEVICE pointers; max_label_len must then be given */
     int max_label_len;     /* upper bound on label_lens[b]; <=0 means "derive it" (host lengths only) */
-    int reserved[4];       /* must be zero */
+    int phase_mask;        /* profiling aid, 0 in production: bit0 = skip the recursion (engine) kernel, bit1 = skip
+                              the gradient kernel; a skipped phase reuses what the previous full call left in the
+                              workspace (bench.py times each kernel alone with CUDA events this way) */
+    int reserved[3];       /* must be zero */
 } ctcB200Options;
 
 /* replaces get_warpctc_version() */

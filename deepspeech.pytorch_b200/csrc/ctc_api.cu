@@ -28,9 +28,11 @@ struct Plan {
     int R;     // rows per checkpoint block (16 or 8)
     int nblk;  // ceil(T / R)
     int Lmax;
-    size_t smem_engine, smem_grad;
+    int Cp;    // emission-row pitch in floats (C rounded up to a multiple of 4, >= 32 words for C <= 32: rows are
+               // 16-byte multiples for TMA and gathers are bank-conflict-free)
+    size_t smem_prep, smem_engine, smem_grad;
     // workspace byte offsets
-    size_t o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_lpos, o_coff, o_labels, o_llen, o_alen;
+    size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_lpos, o_coff, o_labels, o_llen, o_alen;
     size_t total;
 };
 
@@ -44,18 +46,21 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     if (nwl > kMaxLatticeWarps) return false;  // label length > 1023
     pl->nwl = nwl;
     pl->Lmax = Lmax;
+    pl->Cp = C <= 32 ? 32 : (C <= 64 ? 64 : 128);
     const int NT = nwl * 32;
-    int R = 16;
-    if (grad_smem(C, Lmax, NT, kK, R).total > kSmemLimit) R = 8;
-    if (grad_smem(C, Lmax, NT, kK, R).total > kSmemLimit) return false;
+    // one checkpoint per group of 8 time steps: the grad kernel then never renormalises or re-settles exponents
+    const int R = kGroup;
+    if (grad_smem(C, pl->Cp, Lmax, NT, kK).total > kSmemLimit) return false;
     pl->R = R;
     pl->nblk = T > 0 ? (T + R - 1) / R : 1;
-    pl->smem_engine = engine_smem(C, Lmax, R).total;
-    pl->smem_grad = grad_smem(C, Lmax, NT, kK, R).total;
-    if (pl->smem_engine > kSmemLimit) return false;
+    pl->smem_prep = prep_smem(C);
+    pl->smem_engine = engine_smem(pl->Cp, nwl).total;
+    pl->smem_grad = grad_smem(C, pl->Cp, Lmax, NT, kK).total;
+    if (pl->smem_engine > kSmemLimit || pl->smem_prep > kSmemLimit) return false;
     size_t o = 0;
     const size_t ck = sizeof(double) * (size_t)B * pl->nblk * NT * kK;
     const size_t ckE = sizeof(int) * (size_t)B * pl->nblk * NT;
+    pl->o_y = o;      o = align256(o + sizeof(unsigned) * (size_t)T * B * 2 * pl->Cp);
     pl->o_ckA = o;    o = align256(o + ck);
     pl->o_ckB = o;    o = align256(o + ck);
     pl->o_ckAE = o;   o = align256(o + ckE);
@@ -73,35 +78,54 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     return true;
 }
 
-template <int R>
-cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
+template <int CP>
+cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(ctc_engine_kernel<kK, R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)kSmemLimit);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(ctc_grad_kernel<kK, R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        e = cudaFuncSetAttribute(ctc_engine_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_grad_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    const int engine_ctas = p.score_only ? p.B : 2 * p.B;
     cudaError_t e = cudaSuccess;
+    if (!(phase_mask & 4) && p.T > 0) {
+        const long long rows = (long long)p.T * p.B;
+        const int nrb = (int)((rows + kPrepRows - 1) / kPrepRows);
+        ctc_prep_kernel<<<nrb + p.B, kPrepRows, pl.smem_prep, st>>>(p);
+        ++*launches;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
     if (!(phase_mask & 1)) {
-        ctc_engine_kernel<kK, R><<<engine_ctas, (pl.nwl + 1) * 32, pl.smem_engine, st>>>(p);
+        const int engine_ctas = p.score_only ? p.B : 2 * p.B;
+        ctc_engine_kernel<kK, CP><<<engine_ctas, (pl.nwl + 1) * 32, pl.smem_engine, st>>>(p);
         ++*launches;
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
     if (!p.score_only && p.T > 0 && !(phase_mask & 2)) {
         dim3 grid(pl.nblk, p.B);
-        ctc_grad_kernel<kK, R><<<grid, pl.nwl * 32, pl.smem_grad, st>>>(p);
+        ctc_grad_kernel<kK, CP><<<grid, pl.nwl * 32, pl.smem_grad, st>>>(p);
         ++*launches;
         e = cudaGetLastError();
     }
     return e;
+}
+
+cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
+    switch (pl.Cp) {
+        case 32: return launch_all_cp<32>(p, pl, st, phase_mask, launches);
+        case 64: return launch_all_cp<64>(p, pl, st, phase_mask, launches);
+        default: return launch_all_cp<128>(p, pl, st, phase_mask, launches);
+    }
 }
 
 }  // namespace
@@ -204,10 +228,13 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
     p.blank = o.blank;
     p.zero_infinity = o.zero_infinity;
     p.grad_scale = o.grad_scale;
+    p.Cp = pl.Cp;
     p.nwl = pl.nwl;
+    p.R = pl.R;
     p.nblk = pl.nblk;
     p.Lmax = pl.Lmax;
     p.score_only = grads ? 0 : 1;
+    p.y = reinterpret_cast<unsigned *>(ws + pl.o_y);
     p.ckA = reinterpret_cast<double *>(ws + pl.o_ckA);
     p.ckB = reinterpret_cast<double *>(ws + pl.o_ckB);
     p.ckAE = reinterpret_cast<int *>(ws + pl.o_ckAE);
@@ -220,7 +247,7 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
     p.coff = reinterpret_cast<int *>(ws + pl.o_coff);
 
     int launches = 0;
-    cudaError_t e = (pl.R == 16) ? launch_all<16>(p, pl, st, o.phase_mask, &launches) : launch_all<8>(p, pl, st, o.phase_mask, &launches);
+    cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches);
     g_last_launches = launches;
     return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }

@@ -1,28 +1,30 @@
 // csrc/ctc_device.cuh -- device-side building blocks of the B200 CTC lattice kernels (sm_100a only).
 //
-// Numeric representation (validated on the CPU by tests/numeric_model.py against oracle/):
+// Numeric representation (modelled on the CPU by tests/numeric_model.py):
 //   alpha / beta live in the LINEAR domain.  Each lattice thread owns K adjacent states of the blank-extended
 //   label sequence l'  as fp64 mantissas plus ONE int exponent E: value = m * 2^E.
-//   Every kRenorm time steps a thread rescales its mantissas by an exact power of two so that its largest one
-//   lies in [1,2).  Inflow from the neighbouring thread is multiplied by 2^(E_nbr - E_me).
-//   B200 issues fp64 at half the fp32 rate (64 lanes/SM/clk), so a lattice cell costs 2-3 DADD/DFMA/DMUL and
-//   no transcendental; fp32 state cannot meet "grad abs <= 1e-5" (SURVEY.md 7.3).
+//   * every kGroup (= 8) time steps a thread rescales its own mantissas by an exact power of two so that the
+//     largest lies in [1,2) (thread-local, no communication); a thread whose mantissas are all zero is DEAD
+//     (E = kDeadE).  Emissions are clamped to >= 2^-126, so nothing can underflow within one group.
+//   * inflow from the neighbouring thread arrives as a (mantissa, exponent) pair taken at the same instant and is
+//     multiplied by 2^(E_nbr - E_me) on the RECEIVE side; if the neighbour sits more than 2^kLift above me (or I
+//     am dead) I first re-base onto its exponent (my content is negligible next to what is about to flow in).
+//   Measured on B200 (tools/ubench/lat.cu): DFMA latency 8 clk, 16 lanes/clk/SMSP; SHFL 27 clk; bar.sync (4 warps)
+//   39 clk.  A K=8 lattice step is ~20 fp64 instructions = ~40 clk of FP64 pipe per warp, so neighbour values are
+//   exchanged one step AHEAD of their use and block-wide synchronisation happens once per group, not per step.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace ctcb200 {
 
-constexpr int kRenorm = 8;      // time steps between renormalisations
-constexpr int kLift = 500;      // max exponent gap tolerated towards the inflow neighbour
-// R (template parameter of both kernels): time steps per checkpoint block == emission rows per smem tile;
-// a multiple of kRenorm so that checkpoints fall on freshly renormalised states.
-constexpr int kYStages = 3;     // emission tile ring depth (engine kernel)
-constexpr int kRawStages = 3;   // raw-logit tile ring depth (engine kernel)
-constexpr int kMaxSmallC = 128; // alphabet bound of the class-gather path
-constexpr int kMaxLatticeWarps = 8;
+constexpr int kGroup = 8;            // time steps per group == renormalisation period == emission rows per tile
+constexpr int kLift = 250;           // max exponent gap tolerated towards the inflow neighbour
+constexpr int kDeadE = -(1 << 30);   // exponent of a thread that holds only zeros
+constexpr int kMaxSmallC = 128;      // alphabet bound of the class-row (gather) emission path
+constexpr int kMaxLatticeWarps = 8;  // K=8: label length <= 1023
+constexpr int kRing = 16;            // boundary-slot ring between adjacent lattice warps (2 groups)
 constexpr unsigned kFull = 0xffffffffu;
-
 
 // ---------------------------------------------------------------- exponent helpers
 // 2^d as a double for d in [-1022, 1023]; smaller d gives 0 (flush), larger d clamps.
@@ -44,9 +46,6 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
@@ -67,147 +66,184 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// ---------------------------------------------------------------- async copies
-__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gmem_src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-// TMA: 2-D tiled tensor load global -> shared, completion on an mbarrier (SASS: UTMALDG)
-__device__ __forceinline__ void tma_load_2d(void *smem_dst, const void *tensor_map, int c0, int c1, uint64_t *bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-        ::"r"(smem_u32(smem_dst)), "l"(tensor_map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
-        : "memory");
+// ---------------------------------------------------------------- TMA bulk copy (SASS: UBLKCP)
+// global -> shared, `bytes` a multiple of 16, both addresses 16-byte aligned; completion counted on an mbarrier.
+__device__ __forceinline__ void tma_bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
 }
 
-// ---------------------------------------------------------------- softmax of emission rows (one warp)
-// raw: shared fp32 [nrows][raw_stride] logits; y: shared fp64 [nrows][y_stride] <- softmax probabilities.
-// 8 lanes per row, 4 rows per pass: float loads are conflict-free when raw_stride % 32 == 8.
-// y is clamped to >= 2^-126 so that a feasible alignment never gets probability exactly 0 from fp32 underflow.
-__device__ __forceinline__ void softmax_rows_warp(const float *raw, int raw_stride, double *y, int y_stride, int nrows,
-                                                  int C, int lane) {
-    const int sub = lane & 7, rloc = lane >> 3;
-    for (int r0 = 0; r0 < nrows; r0 += 4) {
-        const int r = min(r0 + rloc, nrows - 1);  // duplicate the last row instead of diverging
-        const float *x = raw + r * raw_stride;
-        double *yr = y + r * y_stride;
-        float m = -INFINITY;
-        for (int c = sub; c < C; c += 8) m = fmaxf(m, x[c]);
-        m = fmaxf(m, __shfl_xor_sync(kFull, m, 1));
-        m = fmaxf(m, __shfl_xor_sync(kFull, m, 2));
-        m = fmaxf(m, __shfl_xor_sync(kFull, m, 4));
-        float sum = 0.f;
-        for (int c = sub; c < C; c += 8) sum += expf(x[c] - m);
-        sum += __shfl_xor_sync(kFull, sum, 1);
-        sum += __shfl_xor_sync(kFull, sum, 2);
-        sum += __shfl_xor_sync(kFull, sum, 4);
-        const float inv = 1.0f / sum;
-        if (r0 + rloc < nrows)
-            for (int c = sub; c < C; c += 8) yr[c] = (double)fmaxf(expf(x[c] - m) * inv, 1.17549435e-38f);
-    }
-}
+// ---------------------------------------------------------------- lattice state of one thread
+template <int K>
+struct Cells {
+    double a[K];
+    int E;
+};
 
-// ---------------------------------------------------------------- renormalisation
-// Rescale the K mantissas of this thread and settle its exponent.  FWD: inflow comes from lane-1 (alpha),
-// otherwise from lane+1 (beta).  carryE/has_carry: exponent of the neighbouring WARP's boundary thread.
-//   live  thread : largest mantissa -> [1,2)
-//   dead  thread : (all zero/denormal) flush, adopt the exponent of the nearest live thread on the inflow side
-//   lift         : never let the inflow neighbour sit more than 2^kLift above (prefix-max scan), so that the
-//                  boundary factor 2^(E_nbr-E_me) cannot overflow between two renormalisations
-// Afterwards f = 2^(E_nbr - E_me) for the in-warp neighbour (the cross-warp lane recomputes it every step).
-template <int K, bool FWD>
-__device__ __forceinline__ void renorm(double (&a)[K], int &E, double &f, int lane, int carryE, bool has_carry) {
-    int hm = 0;
+// Thread-local renormalisation (end of every group): largest mantissa -> [1,2); all-zero thread -> dead.
+template <int K>
+__device__ __forceinline__ void renorm(Cells<K> &c) {
+    int h[K];
 #pragma unroll
-    for (int k = 0; k < K; ++k) hm = max(hm, __double2hiint(a[k]));
-    const int ex = hm >> 20;
+    for (int k = 0; k < K; ++k) h[k] = __double2hiint(c.a[k]);
+#pragma unroll
+    for (int w = 1; w < K; w <<= 1)
+#pragma unroll
+        for (int k = 0; k + w < K; k += 2 * w) h[k] = max(h[k], h[k + w]);
+    const int ex = h[0] >> 20;
     const bool live = ex != 0;
-    const int shift = live ? 1023 - ex : 0;
-    const int E1 = E - shift;
+    const double sc = live ? pow2i(1023 - ex) : 0.0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) c.a[k] *= sc;
+    c.E = live ? c.E - (1023 - ex) : kDeadE;
+}
+
+// Exponent settlement between two groups (after renorm), one warp, all lanes.  Exponents are then FIXED for the
+// whole next group, so the per-step path carries mantissas only and scales the inflow by a per-group constant f.
+//   * a dead thread adopts the exponent of the nearest live thread on its inflow side (ballot + one indexed
+//     shuffle; beyond the warp: E_edge, the settled exponent of the neighbouring warp's boundary thread, which ran
+//     this group one super-step earlier) -- so whatever flows into it during the group arrives in a valid scale;
+//   * a thread whose inflow neighbour sits more than 2^kLift above it re-bases onto the neighbour's exponent (its
+//     own content is negligible next to what is about to flow in); repeated while any lane re-based (rare).
+// UP = inflow comes from lane-1 (alpha); otherwise from lane+1 (beta).  Returns f = 2^(E_nbr - E_me).
+template <int K, bool UP>
+__device__ __forceinline__ double settle(Cells<K> &c, int E_edge, int lane) {
+    int E = c.E;
+    const bool live = E != kDeadE;
     const unsigned lm = __ballot_sync(kFull, live);
-    const unsigned side = FWD ? (lm & ((1u << lane) - 1u)) : (lane == 31 ? 0u : (lm & ~((2u << lane) - 1u)));
-    const int src = side ? (FWD ? 31 - __clz(side) : __ffs(side) - 1) : lane;
-    const int Es = __shfl_sync(kFull, E1, src);
-    const bool sourced = live || side != 0u || has_carry;
-    const int E2 = live ? E1 : (side ? Es : (has_carry ? carryE : E1));
-    int E3 = sourced ? E2 : -(1 << 28);  // threads with nothing flowing in must not lift anybody
+    const unsigned side = UP ? (lm & ((1u << lane) - 1u)) : (lane == 31 ? 0u : (lm & ~((2u << lane) - 1u)));
+    const int src = side ? (UP ? 31 - __clz(side) : __ffs(side) - 1) : lane;
+    const int Es = __shfl_sync(kFull, E, src);
+    if (!live) E = side ? Es : E_edge;
+    int En;
+    bool lifted;
+    do {
+        En = UP ? __shfl_up_sync(kFull, E, 1) : __shfl_down_sync(kFull, E, 1);
+        if (UP ? (lane == 0) : (lane == 31)) En = E_edge;
+        lifted = false;
+#ifndef CTC_EXP_NOLIFT
+        if (En != kDeadE && En - E > kLift) {  // E == kDeadE with a live neighbour cannot happen after adoption
+            const double s = pow2i(E - En);
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int o = FWD ? __shfl_up_sync(kFull, E3, d) : __shfl_down_sync(kFull, E3, d);
-        const bool ok = FWD ? (lane >= d) : (lane + d < 32);
-        if (ok) E3 = max(E3, o - d * kLift);
-    }
-    if (has_carry) E3 = max(E3, carryE - (FWD ? lane + 1 : 32 - lane) * kLift);
-    const int Enew = sourced ? E3 : E2;
-    const double sc = live ? pow2i(shift - (Enew - E2)) : 0.0;
-#pragma unroll
-    for (int k = 0; k < K; ++k) a[k] *= sc;
-    E = Enew;
-    const int En = FWD ? __shfl_up_sync(kFull, Enew, 1) : __shfl_down_sync(kFull, Enew, 1);
-    const bool edge = FWD ? (lane == 0) : (lane == 31);
-    f = edge ? 1.0 : pow2i(En - Enew);
+            for (int k = 0; k < K; ++k) c.a[k] *= s;
+            E = En;
+            lifted = true;
+        }
+#endif
+    } while (__any_sync(kFull, lifted));
+    c.E = E;
+    return (En == kDeadE) ? 0.0 : pow2i(En - E);
 }
 
 // ---------------------------------------------------------------- lattice cells
-// alpha_t(s) = y_t(l'_s) * (alpha_{t-1}(s) + alpha_{t-1}(s-1) + [skip] alpha_{t-1}(s-2))      (SURVEY.md 8(c))
-// Thread base state is even, so k even = blank, k odd = label.  p1 = alpha_{t-1}(base-1) in this thread's scale.
+// Emission values one thread needs for one time step, loaded from a shared-memory row one step AHEAD of use.
 template <int K>
-__device__ __forceinline__ void alpha_cells(double (&a)[K], double p1, const double *__restrict__ yrow, int blank_idx,
-                                            const int (&idx)[K / 2], const double (&skip)[K / 2]) {
-    const double yb = yrow[blank_idx];
+struct YRow {
+    double yb;         // y_t(blank)
+    double yl[K / 2];  // y_t(label of state 2h+1)
+};
+// Emission rows are stored PLANAR: CP high words then CP low words of the fp64 values (CP = 32 for C <= 32), so a
+// per-lane gather is two bank-conflict-free single-wavefront LDS.32 that land directly in a register pair.
+// (Measured, tools/ubench/lat3.cu: interleaved fp64 rows need 2-4 wavefronts per LDS.64 gather and make the step
+// LSU-bound, 78 vs 43 clk; fp32 rows + conversion cost either the FP64 pipe (cvt) or ~20 extra integer/move
+// instructions per step.)  Row r of a tile starts at word r * 2 * CP: all offsets fold into immediates.
+template <int K, int CP>
+__device__ __forceinline__ void load_y(YRow<K> &y, const unsigned *tile, int r, int blank_idx, const int (&idx)[K / 2]) {
+#ifdef CTC_EXP_NOY
+    y.yb = 0.9 + 1e-9 * blank_idx;
 #pragma unroll
-    for (int k = K - 1; k >= 0; --k) {
+    for (int h = 0; h < K / 2; ++h) y.yl[h] = 0.9 + 1e-9 * idx[h];
+    (void)tile; (void)r;
+#else
+    const unsigned *row = tile + r * 2 * CP;
+    y.yb = __hiloint2double((int)row[blank_idx], (int)row[CP + blank_idx]);
+#pragma unroll
+    for (int h = 0; h < K / 2; ++h) y.yl[h] = __hiloint2double((int)row[idx[h]], (int)row[CP + idx[h]]);
+#endif
+}
+// exact fp32 -> planar fp64 words (positive normal floats only: y is clamped to >= 2^-126) and back
+__device__ __forceinline__ unsigned y_hi_word(float x) { return (__float_as_uint(x) >> 3) + 0x38000000u; }
+__device__ __forceinline__ unsigned y_lo_word(float x) { return __float_as_uint(x) << 29; }
+__device__ __forceinline__ float y_from_words(unsigned hi, unsigned lo) {
+    return __uint_as_float(((hi - 0x38000000u) << 3) | (lo >> 29));
+}
+
+// alpha_t(s) = y_t(l'_s) * (alpha_{t-1}(s) + alpha_{t-1}(s-1) + [skip] alpha_{t-1}(s-2))      (SURVEY.md 8(c))
+// Thread base state is even, so k even = blank, k odd = label.  The step is split so that the value the next
+// thread needs (new a[K-1], which does not depend on this step's inflow when K >= 4) is produced first and can be
+// shuffled while the remaining cells are computed; the inflow p1 = alpha_{t-1}(base-1) is consumed last.
+template <int K>
+__device__ __forceinline__ double alpha_top(const double (&a)[K], const YRow<K> &y, const double (&skip)[K / 2]) {
+    static_assert(K >= 4, "K >= 4");
+    return fma(skip[K / 2 - 1], a[K - 3], a[K - 1] + a[K - 2]) * y.yl[K / 2 - 1];
+}
+template <int K>
+__device__ __forceinline__ void alpha_rest(double (&a)[K], double top, double p1, const YRow<K> &y,
+                                           const double (&skip)[K / 2]) {
+#pragma unroll
+    for (int k = K - 2; k >= 0; --k) {
         const double prev1 = (k >= 1) ? a[k - 1] : p1;
         if (k & 1) {
             const double prev2 = (k >= 2) ? a[k - 2] : p1;
-            a[k] = fma(skip[k >> 1], prev2, a[k] + prev1) * yrow[idx[k >> 1]];
+            a[k] = fma(skip[k >> 1], prev2, a[k] + prev1) * y.yl[k >> 1];
         } else {
-            a[k] = (a[k] + prev1) * yb;
+            a[k] = (a[k] + prev1) * y.yb;
         }
     }
+    a[K - 1] = top;
 }
 
 // betabar_t(s) = beta_{t+1}(s) + beta_{t+1}(s+1) + [skip] beta_{t+1}(s+2);  beta_t(s) = y_t(l'_s) * betabar_t(s)
-// n1/n2 = beta_{t+1}(base+K), beta_{t+1}(base+K+1) in this thread's scale.  bb receives betabar_t.
+// Bottom two cells first (what the previous thread needs); n1/n2 = beta_{t+1}(base+K), beta_{t+1}(base+K+1) in
+// this thread's scale are consumed last.  bb receives betabar_t.
 template <int K>
-__device__ __forceinline__ void beta_cells(double (&a)[K], double (&bb)[K], double n1, double n2,
-                                           const double *__restrict__ yrow, int blank_idx, const int (&idx)[K / 2],
-                                           const double (&skip)[K / 2]) {
-    const double yb = yrow[blank_idx];
+__device__ __forceinline__ void beta_bottom(const double (&a)[K], const YRow<K> &y, const double (&skip)[K / 2],
+                                            double &b0, double &b1, double &n0, double &n1v) {
+    static_assert(K >= 4, "K >= 4");
+    b0 = a[0] + a[1];
+    b1 = fma(skip[0], a[3], a[1] + a[2]);
+    n0 = b0 * y.yb;
+    n1v = b1 * y.yl[0];
+}
+template <int K>
+__device__ __forceinline__ void beta_rest(double (&a)[K], double (&bb)[K], double b0, double b1, double n0, double n1v,
+                                          double n1, double n2, const YRow<K> &y, const double (&skip)[K / 2]) {
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
+    for (int k = 2; k < K; ++k) {
         const double nx1 = (k + 1 < K) ? a[k + 1] : n1;
         if (k & 1) {
             const double nx2 = (k + 2 < K) ? a[k + 2] : n2;
             bb[k] = fma(skip[k >> 1], nx2, a[k] + nx1);
-            a[k] = bb[k] * yrow[idx[k >> 1]];
+            a[k] = bb[k] * y.yl[k >> 1];
         } else {
             bb[k] = a[k] + nx1;
-            a[k] = bb[k] * yb;
+            a[k] = bb[k] * y.yb;
         }
     }
+    bb[0] = b0;
+    bb[1] = b1;
+    a[0] = n0;
+    a[1] = n1v;
 }
 
 // Per-thread constants of the blank-extended sequence: emission index and skip masks of the K/2 label states.
-// slab: shared int [L] labels of this utterance.  Invalid (padding) label states point at `pad_idx`.
+// lab: int [L] labels of this utterance (shared or global).  Invalid (padding) label states point at `blank`.
 template <int K>
-__device__ __forceinline__ void thread_labels(const int *slab, int L, int thread, int C, int blank,
+__device__ __forceinline__ void thread_labels(const int *lab, int L, int thread, int C, int blank,
                                               int (&idx)[K / 2], double (&skipA)[K / 2], double (&skipB)[K / 2],
                                               int (&lab_i)[K / 2]) {
 #pragma unroll
     for (int h = 0; h < K / 2; ++h) {
         const int i = (thread * K) / 2 + h;  // label position of state thread*K + 2h+1
         const bool valid = i < L;
-        int c = valid ? slab[i] : blank;
+        int c = valid ? lab[i] : blank;
         c = min(max(c, 0), C - 1);
         idx[h] = c;
         lab_i[h] = valid ? i : -1;
-        skipA[h] = (valid && (i == 0 || min(max(slab[i - 1], 0), C - 1) != c)) ? 1.0 : 0.0;
-        skipB[h] = (valid && i + 1 < L && min(max(slab[i + 1], 0), C - 1) != c) ? 1.0 : 0.0;
+        skipA[h] = (valid && (i == 0 || min(max(lab[i - 1], 0), C - 1) != c)) ? 1.0 : 0.0;
+        skipB[h] = (valid && i + 1 < L && min(max(lab[i + 1], 0), C - 1) != c) ? 1.0 : 0.0;
     }
 }
 

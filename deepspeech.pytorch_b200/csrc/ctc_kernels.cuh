@@ -1,22 +1,26 @@
-// csrc/ctc_kernels.cuh -- the two kernels of the B200 CTC loss (sm_100a).
+// csrc/ctc_kernels.cuh -- the three kernels of the B200 CTC loss (sm_100a), small-alphabet (class-row) path.
 //
+//   ctc_prep_kernel   : grid ceil(T*B/128) + B.  Row blocks: fused softmax over C per (t,b) -- coalesced float4 loads
+//                       of 128 consecutive rows into shared memory, one thread per row for max / sum, coalesced
+//                       stores of the fp32 emission rows y[b,t,0:Cp] (utterance-major, 16-byte-multiple pitch: the 8
+//                       rows of a group are ONE TMA bulk copy).  Utterance blocks: label offsets and the class-sorted label order.
 //   ctc_engine_kernel : grid 2B (score-only: B).  CTA 2b runs the alpha recursion of utterance b forwards in time,
 //                       CTA 2b+1 the beta recursion backwards, concurrently on different SMs.  Lattice warps hold
-//                       K states per thread in registers; a dedicated producer warp streams logit rows into a
-//                       shared-memory ring (cp.async / TMA) and turns them into fp64 softmax rows, handing tiles
-//                       over through mbarriers.  Every R steps the state is checkpointed to the workspace.
-//                       The alpha CTA finishes with P = p(l|x) -> costs[b].
-//   ctc_grad_kernel   : grid (ceil(T/R), B).  One CTA per (utterance, block of R time steps): recomputes
-//                       the alpha rows of the block from its checkpoint into shared memory, sweeps beta backwards
-//                       from the beta checkpoint, forms posteriors alpha*betabar/P, reduces them per class in
-//                       shared memory and writes grad = scale * (softmax - occupancy) once, one coalesced row
-//                       segment per (t,b).  Rows t >= act_lens[b] are written as zeros by the same kernel.
+//                       K states per thread in registers and form a SYSTOLIC pipeline over groups of 8 time steps:
+//                       in super-step i, warp q works on group i-q, so boundary values cross warps through a
+//                       shared-memory ring one group late and the CTA synchronises once per group (not per step).
+//                       A producer warp TMA-prefetches the emission rows of the coming groups into a ring.
+//                       Every R steps the state is checkpointed.  The alpha CTA ends with P = p(l|x) -> costs[b].
+//   ctc_grad_kernel   : grid (ceil(T/R), B).  One CTA per (utterance, block of R time steps): recomputes the alpha
+//                       rows of the block from its checkpoint into shared memory, sweeps beta backwards from the
+//                       beta checkpoint, forms posteriors alpha*betabar/P, reduces them per class in shared memory
+//                       and writes grad = scale * (softmax - occupancy) once, one coalesced row segment per (t,b).
+//                       Rows t >= act_lens[b] are written as zeros by the same kernel.
 //
 // Replaces the arithmetic behind `criterion(logits, targets, output_sizes.cpu(), target_sizes)`
 // (/root/reference/train.py:600; eval :352,:457), i.e. warp-ctc's softmax + compute_alpha + compute_betas_and_grad
 // stages [external], with a different algorithm: linear-domain fp64 block-exponent recursion, bidirectional
-// engines, checkpoint + recompute instead of an S x T lattice in global memory (which at B=64,T=1500 would be
-// 256 MB of traffic against 22 MB of algorithmic bytes).
+// engines, checkpoint + recompute instead of an S x T lattice in global memory.
 #pragma once
 #include "ctc_device.cuh"
 
@@ -29,13 +33,16 @@ struct CtcParams {
     const int *labels;      // device, flat
     const int *label_lens;  // device [B]
     const int *act_lens;    // device [B]
-    int T, B, C, blank, zero_infinity;
+    int T, B, C, Cp, blank, zero_infinity;
     float grad_scale;
-    int nwl;   // lattice warps per CTA
+    int nwl;   // lattice warps per CTA (from Lmax)
+    int R;     // time steps per checkpoint block (8 or 16)
     int nblk;  // ceil(T / R)
-    int Lmax;  // max label length (sizes the shared label array)
+    int Lmax;  // max label length
     int score_only;
     // workspace
+    unsigned *y;        // [B][T][2*Cp] softmax rows, planar fp64: Cp high words then Cp low words (exact widening
+                        // of the fp32 softmax, clamped to >= 2^-126)
     double *ckA, *ckB;  // [B][nblk][nwl*32*K] mantissas
     int *ckAE, *ckBE;   // [B][nblk][nwl*32]   exponents
     double *Pm;         // [B] mantissa of p(l|x) in [1,2)
@@ -44,43 +51,41 @@ struct CtcParams {
     int *laboff;        // [B] offset of utterance b in `labels`
     int *lpos;          // [B][Lmax] position of label i in class-sorted order
     int *coff;          // [B][C+1]  class segment offsets in that order
+#ifdef CTC_PROFILE
+    long long *dbg;     // [ctas][16 warps][8] clock counters (tools/ubench/engine_bench.cu only)
+#endif
 };
 
-struct Slot {
+#ifdef CTC_PROFILE
+__device__ __forceinline__ long long prof_clk() { long long c; asm volatile("mov.u64 %0, %%clock64;" : "=l"(c)); return c; }
+#define PROF(x) x
+#else
+#define PROF(x)
+#endif
+
+struct __align__(8) Slot {
     double m0, m1;
     int E;
     int pad;
 };
 
-__host__ __device__ inline int raw_stride_of(int C) { return ((C + 31) / 32) * 32 + 8; }
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-// ------------------------------------------------------------------------------------------------ engine
-struct EngineSmem {
-    size_t ytile, raw, slab, cnt, slots, bars, misc, total;
-};
-__host__ __device__ inline EngineSmem engine_smem(int C, int Lmax, int R) {
-    EngineSmem s;
-    size_t o = 0;
-    s.ytile = o; o = align16(o + sizeof(double) * kYStages * R * C);
-    s.raw = o;   o = align16(o + sizeof(float) * kRawStages * R * raw_stride_of(C));
-    s.slab = o;  o = align16(o + sizeof(int) * (Lmax > 0 ? Lmax : 1));
-    s.cnt = o;   o = align16(o + sizeof(int) * C);
-    s.slots = o; o = align16(o + sizeof(Slot) * 2 * kMaxLatticeWarps);
-    s.bars = o;  o = align16(o + sizeof(uint64_t) * 2 * kYStages);
-    s.misc = o;  o = align16(o + 64);
-    s.total = o;
-    return s;
+// ================================================================================================ prep
+constexpr int kPrepRows = 128;
+
+__host__ __device__ inline size_t prep_smem(int C) {
+    return align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows + sizeof(int) * (C + 1) + 64;
 }
 
 // Class-sorted positions of the labels of one utterance (one warp): lpos[i] = rank of label i when labels are
 // stably sorted by class; coff[c] = first position of class c.  Lets the grad kernel reduce posteriors per class
 // over contiguous shared-memory segments, deterministically.
-__device__ __forceinline__ void sort_labels_warp(const int *slab, int L, int C, int *cnt, int *lpos_g, int *coff_g,
+__device__ __forceinline__ void sort_labels_warp(const int *lab, int L, int C, int *cnt, int *lpos_g, int *coff_g,
                                                  int lane) {
     for (int c = lane; c < C; c += 32) cnt[c] = 0;
     __syncwarp();
-    for (int i = lane; i < L; i += 32) atomicAdd(&cnt[min(max(slab[i], 0), C - 1)], 1);
+    for (int i = lane; i < L; i += 32) atomicAdd(&cnt[min(max(lab[i], 0), C - 1)], 1);
     __syncwarp();
     if (lane == 0) {
         int run = 0;
@@ -96,7 +101,7 @@ __device__ __forceinline__ void sort_labels_warp(const int *slab, int L, int C, 
     for (int base = 0; base < L; base += 32) {
         const int i = base + lane;
         const bool act = i < L;
-        const int c = act ? min(max(slab[i], 0), C - 1) : (-1 - lane);
+        const int c = act ? min(max(lab[i], 0), C - 1) : (-1 - lane);
         const unsigned m = __match_any_sync(kFull, c);
         const int rank = __popc(m & ((1u << lane) - 1u));
         const int start = act ? cnt[c] : 0;
@@ -107,283 +112,442 @@ __device__ __forceinline__ void sort_labels_warp(const int *slab, int L, int C, 
     }
 }
 
-template <int K, int R>
-__global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel(const CtcParams p) {
-    static_assert(R % kRenorm == 0 && K % 2 == 0, "bad tile shape");
+__global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const int b = p.score_only ? blockIdx.x : (blockIdx.x >> 1);
-    const bool fwd = p.score_only ? true : !(blockIdx.x & 1);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nwl = p.nwl, C = p.C;
-    const int NT = nwl * 32;
-    const EngineSmem lay = engine_smem(C, p.Lmax, R);
-    double *ytile = reinterpret_cast<double *>(smem + lay.ytile);
-    float *raw = reinterpret_cast<float *>(smem + lay.raw);
-    int *slab = reinterpret_cast<int *>(smem + lay.slab);
-    int *cnt = reinterpret_cast<int *>(smem + lay.cnt);
-    Slot *slots = reinterpret_cast<Slot *>(smem + lay.slots);
-    uint64_t *y_full = reinterpret_cast<uint64_t *>(smem + lay.bars);
-    uint64_t *y_empty = y_full + kYStages;
-    double *pm = reinterpret_cast<double *>(smem + lay.misc);  // [2]
-    int *pe = reinterpret_cast<int *>(smem + lay.misc + 16);   // [2]
-    int *s_off = reinterpret_cast<int *>(smem + lay.misc + 32);
+    const int C = p.C, Cp = p.Cp;
+    const long long nrows_total = (long long)p.T * p.B;
+    const int nrb = (int)((nrows_total + kPrepRows - 1) / kPrepRows);
+    float *xs = reinterpret_cast<float *>(smem);
+    float *s_m = reinterpret_cast<float *>(smem + align16(sizeof(float) * kPrepRows * C));
+    float *s_inv = s_m + kPrepRows;
+    int *cnt = reinterpret_cast<int *>(s_inv + kPrepRows);
 
-    const int Tb = min(max(p.act_lens[b], 0), p.T);
-    const int L = min(max(p.label_lens[b], 0), p.Lmax);
-    const int S = 2 * L + 1;
-    const int nwa = min(nwl, (S + 32 * K - 1) / (32 * K));  // lattice warps this utterance needs
-    const int RS = raw_stride_of(C);
-
-    // ---- label offset (prefix sum of label_lens) and labels -> shared
-    if (tid == 0) {
-        *s_off = 0;
-        for (int i = 0; i < kYStages; ++i) {
-            mbar_init(&y_full[i], 1);
-            mbar_init(&y_empty[i], nwa);
-        }
-        fence_mbar_init();
-    }
-    __syncthreads();
-    {
+    if ((int)blockIdx.x >= nrb) {
+        // ------------------------------------------------ utterance block: label offset + class-sorted order
+        const int b = blockIdx.x - nrb;
+        int *s_off = cnt + C;
+        if (tid == 0) *s_off = 0;
+        __syncthreads();
         int part = 0;
         for (int i = tid; i < b; i += blockDim.x) part += max(p.label_lens[i], 0);
 #pragma unroll
         for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(kFull, part, d);
         if (lane == 0 && part) atomicAdd(s_off, part);
+        __syncthreads();
+        const int off = *s_off;
+        if (tid == 0) p.laboff[b] = off;
+        if (warp == 0 && !p.score_only) {
+            const int L = min(max(p.label_lens[b], 0), p.Lmax);
+            sort_labels_warp(p.labels + off, L, C, cnt, p.lpos + (size_t)b * p.Lmax, p.coff + (size_t)b * (C + 1),
+                             lane);
+        }
+        return;
+    }
+    // ---------------------------------------------------- row block: softmax of 128 consecutive (t,b) rows
+    const long long row0 = (long long)blockIdx.x * kPrepRows;
+    const int nrows = (int)min((long long)kPrepRows, nrows_total - row0);
+    const float *src = p.acts + row0 * C;
+    const int n = nrows * C;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        const float4 *s4 = reinterpret_cast<const float4 *>(src);
+        float4 *d4 = reinterpret_cast<float4 *>(xs);
+        const int n4 = n >> 2;
+        for (int i = tid; i < n4; i += kPrepRows) d4[i] = __ldg(s4 + i);
+        for (int i = (n4 << 2) + tid; i < n; i += kPrepRows) xs[i] = __ldg(src + i);
+    } else {
+        for (int i = tid; i < n; i += kPrepRows) xs[i] = __ldg(src + i);
     }
     __syncthreads();
-    const int off = *s_off;
-    for (int i = tid; i < L; i += blockDim.x) slab[i] = p.labels[off + i];
-    if (tid < 2 * kMaxLatticeWarps) {
-        slots[tid].m0 = 0.0;
-        slots[tid].m1 = 0.0;
-        slots[tid].E = 0;
+    {
+        float inv = -1.f, m = 0.f;
+        if (tid < nrows) {
+            const long long row = row0 + tid;
+            const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
+            if (t < min(max(p.act_lens[b], 0), p.T)) {
+                const float *x = xs + tid * C;
+                m = x[0];
+                for (int c = 1; c < C; ++c) m = fmaxf(m, x[c]);
+                float sum = 0.f;
+                for (int c = 0; c < C; ++c) sum += expf(x[c] - m);
+                inv = 1.0f / sum;
+            }
+        }
+        s_m[tid] = m;
+        s_inv[tid] = inv;
     }
     __syncthreads();
+    for (int r = warp; r < nrows; r += kPrepRows / 32) {
+        const float inv = s_inv[r];
+        if (inv < 0.f) continue;  // padding frame: never read by the lattice kernels
+        const float m = s_m[r];
+        const long long row = row0 + r;
+        const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
+        unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * Cp;  // utterance-major: a tile of rows is one bulk copy
+        for (int c = lane; c < Cp; c += 32) {
+            // y clamped to >= 2^-126: a feasible alignment never gets probability exactly 0 from fp32 underflow
+            const float v = fmaxf(c < C ? expf(xs[r * C + c] - m) * inv : 0.f, 1.17549435e-38f);
+            ydst[c] = y_hi_word(v);
+            ydst[Cp + c] = y_lo_word(v);
+        }
+    }
+}
+
+// ================================================================================================ engine
+constexpr int kLookAhead = 4;  // emission tiles in flight ahead of the first lattice warp
+
+struct EngineSmem {
+    size_t ytile, bars, slots, misc, total;
+    int nstage;
+};
+__host__ __device__ inline EngineSmem engine_smem(int Cp, int nwl) {
+    EngineSmem s;
+    s.nstage = nwl + kLookAhead + 1;
+    size_t o = 0;
+    s.ytile = o; o = align16(o + sizeof(unsigned) * s.nstage * kGroup * 2 * Cp);
+    s.bars = o;  o = align16(o + sizeof(uint64_t) * s.nstage);
+    s.slots = o; o = align16(o + sizeof(Slot) * kMaxLatticeWarps * kRing);
+    s.misc = o;  o = align16(o + 64);
+    s.total = o;
+    return s;
+}
+
+
+// One group (<= 8 time steps) of the alpha recursion for one lattice warp.  Exponents are fixed during a group, so a
+// step moves mantissas only: the inflow (pr0, from the thread below) is scaled by the per-group constant f.
+// Neighbour values are exchanged one step AHEAD of use (shuffle in-warp, shared-memory slot across warps) and are
+// consumed at the END of the next step; emission values are loaded one step ahead.  After the last step the thread
+// renormalises, the warp settles its exponents (-> new f) and only then sends the boundary mantissa.
+#ifdef CTC_PROFILE
+struct ProfAcc { long long steps, ren, settle, send; };
+#define PROF_ARG , ProfAcc &pa
+#define PROF_PASS , pa
+#else
+#define PROF_ARG
+#define PROF_PASS
+#endif
+template <int K, int CP, bool FULL>
+__device__ __forceinline__ void alpha_group(Cells<K> &c, double &pr0, double &f, const unsigned *yt, int nr,
+                                            int t0, int blank, const int (&idx)[K / 2], const double (&skipA)[K / 2],
+                                            int lane, bool has_lower, bool has_upper, Slot *slot_mine,
+                                            const Slot *slot_in PROF_ARG) {
+    YRow<K> y;
+    load_y<K, CP>(y, yt, 0, blank, idx);
+    PROF(long long q0 = prof_clk();)
+#pragma unroll
+    for (int r = 0; r < kGroup; ++r) {
+        if (FULL || r < nr) {
+            const bool last = FULL ? (r == kGroup - 1) : (r == nr - 1);
+            const int t = t0 + r;
+            YRow<K> yn;
+            load_y<K, CP>(yn, yt, FULL ? min(r + 1, kGroup - 1) : min(r + 1, nr - 1), blank, idx);
+            const double p1 = pr0 * f;
+            const double top = alpha_top<K>(c.a, y, skipA);
+            double sh = 0.0;
+            if (!last) {
+                sh = __shfl_up_sync(kFull, top, 1);
+#ifndef CTC_EXP_NOSLOT
+                if (lane == 31 && has_upper) slot_mine[t & (kRing - 1)].m0 = top;
+#endif
+            }
+            alpha_rest<K>(c.a, top, p1, y, skipA);
+            if (!last) {
+                pr0 = sh;
+#ifndef CTC_EXP_NOSLOT
+                if (lane == 0) pr0 = has_lower ? slot_in[t & (kRing - 1)].m0 : 0.0;
+#endif
+            }
+            y = yn;
+        }
+    }
+    const int tl = (t0 + nr - 1) & (kRing - 1);
+    PROF(long long q1 = prof_clk();)
+    renorm<K>(c);
+    PROF(long long q2 = prof_clk();)
+    f = settle<K, true>(c, has_lower ? slot_in[tl].E : kDeadE, lane);
+    PROF(long long q3 = prof_clk(); pa.steps += q1 - q0; pa.ren += q2 - q1; pa.settle += q3 - q2;)
+    pr0 = __shfl_up_sync(kFull, c.a[K - 1], 1);
+    if (lane == 31 && has_upper) {
+        slot_mine[tl].m0 = c.a[K - 1];
+        slot_mine[tl].E = c.E;
+    }
+    if (lane == 0) pr0 = has_lower ? slot_in[tl].m0 : 0.0;
+}
+
+// Mirror image for beta: rows are visited t0+nr-1 down to t0, inflow (two values) comes from the thread above.
+template <int K, int CP, bool FULL>
+__device__ __forceinline__ void beta_group(Cells<K> &c, double &pr0, double &pr1, double &f, const unsigned *yt,
+                                           int nr, int t0, int blank, const int (&idx)[K / 2],
+                                           const double (&skipB)[K / 2], int lane, bool has_lower, bool has_upper,
+                                           Slot *slot_mine, const Slot *slot_in) {
+    YRow<K> y;
+    load_y<K, CP>(y, yt, nr - 1, blank, idx);
+#pragma unroll
+    for (int rr = 0; rr < kGroup; ++rr) {
+        const int r = (FULL ? kGroup : nr) - 1 - rr;
+        if (FULL || r >= 0) {
+            const bool last = (r == 0);
+            const int t = t0 + r;
+            YRow<K> yn;
+            load_y<K, CP>(yn, yt, max(r - 1, 0), blank, idx);
+            const double n1 = pr0 * f, n2 = pr1 * f;
+            double b0, b1, s0, s1v;
+            beta_bottom<K>(c.a, y, skipB, b0, b1, s0, s1v);
+            double sh0 = 0.0, sh1 = 0.0;
+            if (!last) {
+                sh0 = __shfl_down_sync(kFull, s0, 1);
+                sh1 = __shfl_down_sync(kFull, s1v, 1);
+                if (lane == 0 && has_lower) {
+                    slot_mine[t & (kRing - 1)].m0 = s0;
+                    slot_mine[t & (kRing - 1)].m1 = s1v;
+                }
+            }
+            double bb[K];
+            beta_rest<K>(c.a, bb, b0, b1, s0, s1v, n1, n2, y, skipB);
+            if (!last) {
+                pr0 = sh0;
+                pr1 = sh1;
+                if (lane == 31) {
+                    pr0 = has_upper ? slot_in[t & (kRing - 1)].m0 : 0.0;
+                    pr1 = has_upper ? slot_in[t & (kRing - 1)].m1 : 0.0;
+                }
+            }
+            y = yn;
+        }
+    }
+    const int tl = t0 & (kRing - 1);
+    renorm<K>(c);
+    f = settle<K, false>(c, has_upper ? slot_in[tl].E : kDeadE, lane);
+    pr0 = __shfl_down_sync(kFull, c.a[0], 1);
+    pr1 = __shfl_down_sync(kFull, c.a[1], 1);
+    if (lane == 0 && has_lower) {
+        slot_mine[tl].m0 = c.a[0];
+        slot_mine[tl].m1 = c.a[1];
+        slot_mine[tl].E = c.E;
+    }
+    if (lane == 31) {
+        pr0 = has_upper ? slot_in[tl].m0 : 0.0;
+        pr1 = has_upper ? slot_in[tl].m1 : 0.0;
+    }
+}
+
+template <int K, int CP>
+__global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel(const CtcParams p) {
+    static_assert(K % 2 == 0 && K >= 4, "K must be even and >= 4");
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int b = p.score_only ? blockIdx.x : (blockIdx.x >> 1);
+    const bool fwd = p.score_only ? true : !(blockIdx.x & 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nwl = p.nwl, C = p.C;
+    constexpr int Cp = CP;
+    const int NT = nwl * 32;
+    const EngineSmem lay = engine_smem(Cp, nwl);
+    const int NS = lay.nstage;
+    unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
+    uint64_t *y_full = reinterpret_cast<uint64_t *>(smem + lay.bars);
+    Slot *slots = reinterpret_cast<Slot *>(smem + lay.slots);
+    double *pm = reinterpret_cast<double *>(smem + lay.misc);  // [2]
+    int *pe = reinterpret_cast<int *>(smem + lay.misc + 16);   // [2]
+
+    const int Tb = min(max(p.act_lens[b], 0), p.T);
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
+    const int S = 2 * L + 1;
+    const int nwa = min(nwl, (S + 32 * K - 1) / (32 * K));  // lattice warps this utterance needs
 
     if (Tb == 0) {  // nothing to recurse over
         if (fwd && tid == 0) {
             const bool ok = (L == 0);
             p.feas[b] = ok;
-            p.laboff[b] = off;
             p.Pm[b] = 1.0;
             p.Pe[b] = 0;
             p.costs[b] = ok ? 0.f : (p.zero_infinity ? 0.f : INFINITY);
         }
         return;
     }
+    if (warp >= nwa && warp != nwl) return;  // lattice warps beyond this utterance's S
 
-    const int ntiles = (Tb + R - 1) / R;
+    const int ngroups = (Tb + kGroup - 1) / kGroup;
+    const int nsuper = ngroups + nwa - 1;
+    const int nbar = (nwa + 1) * 32;
 
     if (warp == nwl) {
-        // =========================================================== producer warp
-        if (fwd) {
-            if (!p.score_only)
-                sort_labels_warp(slab, L, C, cnt, p.lpos + (size_t)b * p.Lmax, p.coff + (size_t)b * (C + 1), lane);
-            if (lane == 0) p.laboff[b] = off;
+        // =========================================================== producer warp: TMA emission-tile prefetch
+        // y is utterance-major, so the <= 8 rows of a group are contiguous: ONE bulk copy per tile.
+        if (lane == 0) {
+            for (int i = 0; i < NS; ++i) mbar_init(&y_full[i], 1);
+            fence_mbar_init();
         }
-        const float *abase = p.acts + (size_t)b * C;
-        const size_t rowstride = (size_t)p.B * C;
-        auto issue = [&](int tile) {
-            if (tile < ntiles) {
-                float *dst = raw + (tile % kRawStages) * R * RS;
-                const int n0 = tile * R;
-                const int nr = min(R, Tb - n0);
-                for (int r = 0; r < nr; ++r) {
-                    const int t = fwd ? (n0 + r) : (Tb - 1 - n0 - r);
-                    const float *src = abase + (size_t)t * rowstride;
-                    for (int c = lane; c < C; c += 32) cp_async4(dst + r * RS + c, src + c);
-                }
+        __syncwarp();
+        const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
+        const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
+        auto issue = [&](int j) {
+            if (j < ngroups && lane == 0) {
+                const int G = fwd ? j : (ngroups - 1 - j);
+                const int t0 = G * kGroup;
+                const int nr = min(kGroup, Tb - t0);
+                const int st = j % NS;
+                mbar_arrive_expect_tx(&y_full[st], rowbytes * nr);
+                tma_bulk_g2s(ytile + (size_t)(st * kGroup) * 2 * Cp, ybase + (size_t)t0 * 2 * Cp, rowbytes * nr,
+                             &y_full[st]);
             }
-            cp_async_commit();
         };
-        issue(0);
-        issue(1);
-        for (int tile = 0; tile < ntiles; ++tile) {
-            issue(tile + 2);
-            cp_async_wait<2>();
-            __syncwarp();
-            const int ys = tile % kYStages;
-            mbar_wait(&y_empty[ys], ((tile / kYStages) & 1) ^ 1);
-            const int nr = min(R, Tb - tile * R);
-            softmax_rows_warp(raw + (tile % kRawStages) * R * RS, RS, ytile + ys * R * C, C, nr, C,
-                              lane);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&y_full[ys]);
+        PROF(long long tp0 = prof_clk(); long long t_work = 0; long long t_bar = 0;)
+        for (int j = 0; j <= kLookAhead; ++j) issue(j);
+        mbar_wait(&y_full[0], 0);
+        named_bar_sync(1, nbar);
+        for (int i = 0; i < nsuper; ++i) {
+            PROF(long long ta = prof_clk();)
+            fence_proxy_async();
+            issue(i + kLookAhead + 1);
+            if (i + 1 < ngroups) mbar_wait(&y_full[(i + 1) % NS], ((i + 1) / NS) & 1);
+            PROF(long long tb = prof_clk();)
+            named_bar_sync(1, nbar);
+            PROF(long long tc = prof_clk(); t_work += tb - ta; t_bar += tc - tb;)
         }
-        cp_async_wait<0>();
+        PROF(if (lane == 0 && blockIdx.x < 2) { long long *d = p.dbg + (blockIdx.x * 16 + warp) * 8; d[0] = prof_clk() - tp0; d[1] = t_work; d[2] = t_bar; d[3] = nsuper; })
         return;
     }
-    if (warp >= nwa) return;  // lattice warps beyond this utterance's S
 
     // =============================================================== lattice warps
     const int thread = warp * 32 + lane;  // lattice thread index; owns states [thread*K, thread*K+K)
+    const int off = p.laboff[b];
     int idx[K / 2], lab_i[K / 2];
     double skipA[K / 2], skipB[K / 2];
-    thread_labels<K>(slab, L, thread, C, p.blank, idx, skipA, skipB, lab_i);
+    thread_labels<K>(p.labels + off, L, thread, C, p.blank, idx, skipA, skipB, lab_i);
     (void)lab_i;
 
-    double a[K];
+    // initial state: everything in scale 2^0 (f = 1); the first settlement happens after the first group
+    Cells<K> c;
 #pragma unroll
-    for (int k = 0; k < K; ++k) a[k] = 0.0;
-    int E = 0;
-    double f = 1.0;
-    const int nbar = nwa * 32;
+    for (int k = 0; k < K; ++k) c.a[k] = 0.0;
+    c.E = 0;
+    double f = 1.0, pr0 = 0.0, pr1 = 0.0;
     double *ck = (fwd ? p.ckA : p.ckB) + (size_t)b * p.nblk * NT * K;
     int *ckE = (fwd ? p.ckAE : p.ckBE) + (size_t)b * p.nblk * NT;
-
-    if (!fwd) {  // virtual beta_T: 1 at state S-1
-        const int s1 = S - 1;
-#pragma unroll
-        for (int k = 0; k < K; ++k)
-            if (thread * K + k == s1) a[k] = 1.0;
-        // publish the initial boundary state: step 0 of the warp below reads it (S-1 may sit alone in a warp)
-        if (lane == 0 && warp > 0) {
-            slots[warp].m0 = a[0];
-            slots[warp].m1 = a[1];
-            slots[warp].E = 0;
-        }
-        if (nwa > 1) named_bar_sync(1, nbar);
-    }
-
-    for (int n = 0; n < Tb; ++n) {
-        const int r = n % R, tile = n / R, ys = tile % kYStages;
-        if (r == 0) mbar_wait(&y_full[ys], (tile / kYStages) & 1);
-        const double *yrow = ytile + (ys * R + r) * C;
-        const Slot *rd = slots + (n & 1) * kMaxLatticeWarps;
-        Slot *wr = slots + ((n + 1) & 1) * kMaxLatticeWarps;
-        if (fwd) {
-            double p1 = __shfl_up_sync(kFull, a[K - 1], 1) * f;
-            int carryE = 0;
-            if (lane == 0) {
-                if (warp == 0) {
-                    p1 = (n == 0) ? 1.0 : 0.0;
-                } else {
-                    const Slot s = rd[warp - 1];
-                    carryE = s.E;
-                    p1 = s.m0 * pow2i(s.E - E);
-                }
-            }
-            alpha_cells<K>(a, p1, yrow, p.blank, idx, skipA);
-            if (((n + 1) % kRenorm) == 0) {
-                carryE = __shfl_sync(kFull, carryE, 0);
-                renorm<K, true>(a, E, f, lane, carryE, warp > 0);
-            }
-            if (lane == 31 && warp + 1 < nwa) {
-                wr[warp].m0 = a[K - 1];
-                wr[warp].E = E;
-            }
-            const int t1 = n + 1;
-            if ((t1 % R) == 0 && t1 < Tb && !p.score_only) {
-                double *dst = ck + ((size_t)(t1 / R) * NT + thread) * K;
-#pragma unroll
-                for (int k = 0; k < K; k += 2) *reinterpret_cast<double2 *>(dst + k) = make_double2(a[k], a[k + 1]);
-                ckE[(size_t)(t1 / R) * NT + thread] = E;
-            }
-        } else {
-            const int t = Tb - 1 - n;
-            double n1 = __shfl_down_sync(kFull, a[0], 1) * f;
-            double n2 = __shfl_down_sync(kFull, a[1], 1) * f;
-            int carryE = 0;
-            const bool has_up = warp + 1 < nwa;
-            if (lane == 31) {
-                if (!has_up) {
-                    n1 = 0.0;
-                    n2 = 0.0;
-                } else {
-                    const Slot s = rd[warp + 1];
-                    carryE = s.E;
-                    const double fs = pow2i(s.E - E);
-                    n1 = s.m0 * fs;
-                    n2 = s.m1 * fs;
-                }
-            }
-            double bb[K];
-            beta_cells<K>(a, bb, n1, n2, yrow, p.blank, idx, skipB);
-            if ((t % kRenorm) == 0) {
-                carryE = __shfl_sync(kFull, carryE, 31);
-                renorm<K, false>(a, E, f, lane, carryE, has_up);
-            }
-            if (lane == 0 && warp > 0) {
-                wr[warp].m0 = a[0];
-                wr[warp].m1 = a[1];
-                wr[warp].E = E;
-            }
-            if ((t % R) == 0 && t > 0) {  // beta_t for the block that ends at row t-1
-                const int kb = t / R - 1;
-                double *dst = ck + ((size_t)kb * NT + thread) * K;
-#pragma unroll
-                for (int k = 0; k < K; k += 2) *reinterpret_cast<double2 *>(dst + k) = make_double2(a[k], a[k + 1]);
-                ckE[(size_t)kb * NT + thread] = E;
-            }
-        }
-        if (r == R - 1 || n == Tb - 1) {
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&y_empty[ys]);
-        }
-        if (nwa > 1) named_bar_sync(1, nbar);
-    }
+    const int q = fwd ? warp : (nwa - 1 - warp);  // position in the systolic pipeline
+    const bool has_lower = warp > 0, has_upper = warp + 1 < nwa;
+    Slot *slot_mine = slots + warp * kRing;
+    const Slot *slot_in = slots + (fwd ? warp - 1 : warp + 1) * kRing;
 
     if (fwd) {
-        // ---- P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2)
-        const int s1 = S - 1, s2 = S - 2;
+        if (thread == 0) pr0 = 1.0;  // virtual alpha_{-1}(-1) = 1
+    } else {
+        const int s1 = S - 1;  // virtual beta_T: 1 at state S-1
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-            if (thread * K + k == s1) { pm[0] = a[k]; pe[0] = E; }
-            if (thread * K + k == s2) { pm[1] = a[k]; pe[1] = E; }
+        for (int k = 0; k < K; ++k)
+            if (thread * K + k == s1) c.a[k] = 1.0;
+        pr0 = __shfl_down_sync(kFull, c.a[0], 1);
+        pr1 = __shfl_down_sync(kFull, c.a[1], 1);
+        if (lane == 31) {
+            pr0 = ((thread + 1) * K == s1) ? 1.0 : 0.0;  // S-1 is state 0 of the next thread
+            pr1 = 0.0;
         }
-        if (nwa > 1) named_bar_sync(1, nbar); else __syncwarp();
-        if (thread == 0) {
-            double m = pm[0];
-            int e = pe[0];
-            if (S > 1) {
-                const int e2 = pe[1];
-                const int em = max(e, e2);
-                m = pm[0] * pow2i(e - em) + pm[1] * pow2i(e2 - em);
-                e = em;
+    }
+    named_bar_sync(1, nbar);
+    PROF(long long tp0 = prof_clk(); long long t_work = 0; long long t_bar = 0; long long ngr = 0; long long t_loop = 0; ProfAcc pa; pa.steps = 0; pa.ren = 0; pa.settle = 0; pa.send = 0;)
+
+    for (int i = 0; i < nsuper; ++i) {
+        const int j = i - q;
+        PROF(long long ta = prof_clk();)
+        if (j >= 0 && j < ngroups) {
+            PROF(++ngr;)
+            const int G = fwd ? j : (ngroups - 1 - j);
+            const int t0 = G * kGroup;
+            const int nr = min(kGroup, Tb - t0);
+            const unsigned *yt = ytile + (size_t)((j % NS) * kGroup) * 2 * Cp;
+            PROF(long long tl0 = prof_clk();)
+            if (fwd) {
+                if (nr == kGroup)
+                    alpha_group<K, CP, true>(c, pr0, f, yt, nr, t0, p.blank, idx, skipA, lane, has_lower, has_upper,
+                                         slot_mine, slot_in PROF_PASS);
+                else
+                    alpha_group<K, CP, false>(c, pr0, f, yt, nr, t0, p.blank, idx, skipA, lane, has_lower, has_upper,
+                                          slot_mine, slot_in PROF_PASS);
+            } else {
+                if (nr == kGroup)
+                    beta_group<K, CP, true>(c, pr0, pr1, f, yt, nr, t0, p.blank, idx, skipB, lane, has_lower,
+                                        has_upper, slot_mine, slot_in);
+                else
+                    beta_group<K, CP, false>(c, pr0, pr1, f, yt, nr, t0, p.blank, idx, skipB, lane, has_lower,
+                                         has_upper, slot_mine, slot_in);
             }
-            const int ex = expo_field(m);
-            const bool ok = ex != 0 && ex != 2047;
-            if (ok) {
-                m *= pow2i(1023 - ex);
-                e += ex - 1023;
+            PROF(t_loop += prof_clk() - tl0;)
+            // checkpoint (renormalised, settled): alpha after row t0+7 -> block G+1 ; beta_{t0} -> block G-1
+            const int cb = fwd ? G + 1 : G - 1;
+            if (!p.score_only && cb >= 0 && cb * kGroup < Tb) {
+                double *dst = ck + ((size_t)cb * NT + thread) * K;
+#pragma unroll
+                for (int k = 0; k < K; k += 2)
+                    *reinterpret_cast<double2 *>(dst + k) = make_double2(c.a[k], c.a[k + 1]);
+                ckE[(size_t)cb * NT + thread] = c.E;
             }
-            p.feas[b] = ok;
-            p.Pm[b] = ok ? m : 1.0;
-            p.Pe[b] = ok ? e : 0;
-            const double cost = -(log(m) + (double)e * 0.69314718055994530942);
-            p.costs[b] = ok ? (float)cost : (p.zero_infinity ? 0.f : INFINITY);
+            if (fwd && j == ngroups - 1) {
+                // ---- P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2): the owning threads publish (mantissa, exponent)
+                const int s1 = S - 1, s2 = S - 2;
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    if (thread * K + k == s1) { pm[0] = c.a[k]; pe[0] = c.E; }
+                    if (thread * K + k == s2) { pm[1] = c.a[k]; pe[1] = c.E; }
+                }
+            }
         }
+        PROF(long long tb = prof_clk();)
+        named_bar_sync(1, nbar);
+        PROF(long long tc = prof_clk(); t_work += tb - ta; t_bar += tc - tb;)
+    }
+    PROF(if (lane == 0 && blockIdx.x < 2) { long long *d = p.dbg + (blockIdx.x * 16 + warp) * 8; d[0] = prof_clk() - tp0; d[1] = t_work; d[2] = t_bar; d[3] = ngr; d[4] = t_loop; d[5] = pa.steps; d[6] = pa.ren; d[7] = pa.settle; })
+
+    if (fwd && thread == 0) {
+        double m = pm[0];
+        int e = pe[0];
+        if (S > 1) {
+            const int e2 = pe[1];
+            const int em = max(e, e2);
+            m = pm[0] * pow2i(e - em) + pm[1] * pow2i(e2 - em);
+            e = em;
+        }
+        const int ex = expo_field(m);
+        const bool ok = ex != 0 && ex != 2047 && e > kDeadE / 2;
+        if (ok) {
+            m *= pow2i(1023 - ex);
+            e += ex - 1023;
+        }
+        p.feas[b] = ok;
+        p.Pm[b] = ok ? m : 1.0;
+        p.Pe[b] = ok ? e : 0;
+        const double cost = -(log(m) + (double)e * 0.69314718055994530942);
+        p.costs[b] = ok ? (float)cost : (p.zero_infinity ? 0.f : INFINITY);
     }
 }
 
-
-// ------------------------------------------------------------------------------------------------ grad
+// ================================================================================================ grad
+// One CTA per (utterance, group of 8 time steps).  The checkpoints are renormalised and exponent-settled, so inside
+// the block every thread works with ONE alpha exponent and ONE beta exponent: no renormalisation, no settlement.
 struct GradSmem {
-    size_t ytile, raw, slab, arow, Ea, psort, bpart, coff, slots, total;
+    size_t ytile, arow, psort, bpart, coff, slots, bar, total;
 };
-__host__ __device__ inline GradSmem grad_smem(int C, int Lmax, int NT, int K, int R) {
+__host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int NT, int K) {
     GradSmem s;
     size_t o = 0;
-    s.ytile = o; o = align16(o + sizeof(double) * R * C);
-    s.raw = o;   o = align16(o + sizeof(float) * R * raw_stride_of(C));
-    s.slab = o;  o = align16(o + sizeof(int) * (Lmax > 0 ? Lmax : 1));
-    s.arow = o;  o = align16(o + sizeof(double) * R * NT * K);
-    s.Ea = o;    o = align16(o + sizeof(int) * R * NT);
-    s.psort = o; o = align16(o + sizeof(float) * R * (Lmax > 0 ? Lmax : 1));
-    s.bpart = o; o = align16(o + sizeof(float) * R * NT);
+    s.ytile = o; o = align16(o + sizeof(unsigned) * kGroup * 2 * Cp);
+    s.arow = o;  o = align16(o + sizeof(double) * kGroup * NT * K);
+    s.psort = o; o = align16(o + sizeof(float) * kGroup * (Lmax > 0 ? Lmax : 1));
+    s.bpart = o; o = align16(o + sizeof(float) * kGroup * NT);
     s.coff = o;  o = align16(o + sizeof(int) * (C + 1));
     s.slots = o; o = align16(o + sizeof(Slot) * 2 * kMaxLatticeWarps);
+    s.bar = o;   o = align16(o + 16);
     s.total = o;
     return s;
 }
 
-template <int K, int R>
+template <int K, int CP>
 __global__ void __launch_bounds__(kMaxLatticeWarps * 32) ctc_grad_kernel(const CtcParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int R = kGroup;
     const int blk = blockIdx.x, b = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nwl = p.nwl, C = p.C, NT = nwl * 32;
+    constexpr int Cp = CP;
     const int Tb = min(max(p.act_lens[b], 0), p.T);
     const int t0 = blk * R;
     const int rows_out = min(R, p.T - t0);  // rows this CTA must write
@@ -399,182 +563,174 @@ __global__ void __launch_bounds__(kMaxLatticeWarps * 32) ctc_grad_kernel(const C
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
     const int S = 2 * L + 1;
     const int nwa = min(nwl, (S + 32 * K - 1) / (32 * K));
-    const int RS = raw_stride_of(C);
-    const GradSmem lay = grad_smem(C, p.Lmax, NT, K, R);
-    double *ytile = reinterpret_cast<double *>(smem + lay.ytile);
-    float *raw = reinterpret_cast<float *>(smem + lay.raw);
-    int *slab = reinterpret_cast<int *>(smem + lay.slab);
+    const GradSmem lay = grad_smem(C, Cp, p.Lmax, NT, K);
+    unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
     double *arow = reinterpret_cast<double *>(smem + lay.arow);
-    int *Ea = reinterpret_cast<int *>(smem + lay.Ea);
     float *psort = reinterpret_cast<float *>(smem + lay.psort);
     float *bpart = reinterpret_cast<float *>(smem + lay.bpart);
     int *coff = reinterpret_cast<int *>(smem + lay.coff);
     Slot *slots = reinterpret_cast<Slot *>(smem + lay.slots);
+    uint64_t *ybar = reinterpret_cast<uint64_t *>(smem + lay.bar);
     const int Lp = p.Lmax > 0 ? p.Lmax : 1;
 
-    // ---- stage 1: logits rows (cp.async), labels, class offsets -> shared
+    // ---- stage 1: emission rows (one TMA bulk copy), class offsets -> shared
+    if (tid == 0) {
+        mbar_init(ybar, 1);
+        fence_mbar_init();
+        const uint32_t bytes = (uint32_t)(2 * Cp * sizeof(unsigned)) * nrow;
+        mbar_arrive_expect_tx(ybar, bytes);
+        tma_bulk_g2s(ytile, p.y + ((size_t)b * p.T + t0) * 2 * Cp, bytes, ybar);
+    }
     {
-        const float *abase = p.acts + ((size_t)t0 * p.B + b) * C;
-        for (int r = warp; r < nrow; r += nwl)
-            for (int c = lane; c < C; c += 32) cp_async4(raw + r * RS + c, abase + (size_t)r * rowstride + c);
-        cp_async_commit();
-        const int off = p.laboff[b];
-        for (int i = tid; i < L; i += blockDim.x) slab[i] = p.labels[off + i];
         const int *cg = p.coff + (size_t)b * (C + 1);
         for (int c = tid; c <= C; c += blockDim.x) coff[c] = cg[c];
-        if (tid < 2 * kMaxLatticeWarps) {
-            slots[tid].m0 = 0.0;
-            slots[tid].m1 = 0.0;
-            slots[tid].E = 0;
-        }
-        cp_async_wait<0>();
     }
-    __syncthreads();
-    // ---- stage 2: softmax rows -> fp64 emission tile
-    for (int r0 = warp * 4; r0 < nrow; r0 += nwl * 4)
-        softmax_rows_warp(raw + r0 * RS, RS, ytile + r0 * C, C, min(4, nrow - r0), C, lane);
-    __syncthreads();
+    __syncthreads();  // mbarrier init visible before anybody waits on it
 
     const int thread = warp * 32 + lane;
     const int nbar = nwa * 32;
     if (warp < nwa) {
+        const int off = p.laboff[b];
         int idx[K / 2], lab_i[K / 2], lpos[K / 2];
         double skipA[K / 2], skipB[K / 2];
-        thread_labels<K>(slab, L, thread, C, p.blank, idx, skipA, skipB, lab_i);
+        thread_labels<K>(p.labels + off, L, thread, C, p.blank, idx, skipA, skipB, lab_i);
         {
             const int *lg = p.lpos + (size_t)b * p.Lmax;
 #pragma unroll
             for (int h = 0; h < K / 2; ++h) lpos[h] = lab_i[h] >= 0 ? lg[lab_i[h]] : -1;
         }
-        double a[K];
-        int E = 0;
-        double f = 1.0;
-        // ---- stage 3: recompute alpha rows t0 .. t0+nrow-1 from the checkpoint "after row t0-1"
+        const bool has_lower = warp > 0, has_upper = warp + 1 < nwa;
+        const size_t cb = ((size_t)b * p.nblk + blk) * NT;
+        Cells<K> c;
+        double pr0 = 0.0, pr1 = 0.0, f = 1.0;
+        // ---- stage 2: recompute alpha rows t0 .. t0+nrow-1 from the checkpoint "after row t0-1"
         if (blk == 0) {
 #pragma unroll
-            for (int k = 0; k < K; ++k) a[k] = 0.0;
+            for (int k = 0; k < K; ++k) c.a[k] = 0.0;
+            c.E = 0;
+            if (thread == 0) pr0 = 1.0;
         } else {
-            const double *src = p.ckA + (((size_t)b * p.nblk + blk) * NT + thread) * K;
+            const double *src = p.ckA + (cb + thread) * K;
 #pragma unroll
             for (int k = 0; k < K; k += 2) {
                 const double2 v = *reinterpret_cast<const double2 *>(src + k);
-                a[k] = v.x;
-                a[k + 1] = v.y;
+                c.a[k] = v.x;
+                c.a[k + 1] = v.y;
             }
-            E = p.ckAE[((size_t)b * p.nblk + blk) * NT + thread];
-            const int En = __shfl_up_sync(kFull, E, 1);
-            f = lane == 0 ? 1.0 : pow2i(En - E);
-            if (lane == 31 && warp + 1 < nwa) {
-                slots[warp].m0 = a[K - 1];
-                slots[warp].E = E;
-            }
-        }
-        if (nwa > 1) named_bar_sync(1, nbar);
-        for (int r = 0; r < nrow; ++r) {
-            const int t = t0 + r;
-            const Slot *rd = slots + (r & 1) * kMaxLatticeWarps;
-            Slot *wr = slots + ((r + 1) & 1) * kMaxLatticeWarps;
-            double p1 = __shfl_up_sync(kFull, a[K - 1], 1) * f;
-            int carryE = 0;
+            c.E = p.ckAE[cb + thread];
+            pr0 = __shfl_up_sync(kFull, c.a[K - 1], 1);
+            int En = __shfl_up_sync(kFull, c.E, 1);
             if (lane == 0) {
-                if (warp == 0) {
-                    p1 = (t == 0) ? 1.0 : 0.0;
-                } else {
-                    const Slot s = rd[warp - 1];
-                    carryE = s.E;
-                    p1 = s.m0 * pow2i(s.E - E);
-                }
+                pr0 = has_lower ? p.ckA[(cb + thread - 1) * K + K - 1] : 0.0;
+                En = has_lower ? p.ckAE[cb + thread - 1] : kDeadE;
             }
-            alpha_cells<K>(a, p1, ytile + r * C, p.blank, idx, skipA);
-            if (((t + 1) % kRenorm) == 0) {
-                carryE = __shfl_sync(kFull, carryE, 0);
-                renorm<K, true>(a, E, f, lane, carryE, warp > 0);
-            }
-            if (lane == 31 && warp + 1 < nwa) {
-                wr[warp].m0 = a[K - 1];
-                wr[warp].E = E;
-            }
-            double *ar = arow + (size_t)r * NT * K;
-#pragma unroll
-            for (int h = 0; h < K / 2; ++h)
-                *reinterpret_cast<double2 *>(ar + ((size_t)h * NT + thread) * 2) = make_double2(a[2 * h], a[2 * h + 1]);
-            Ea[r * NT + thread] = E;
-            if (nwa > 1) named_bar_sync(1, nbar);
+            f = (En == kDeadE) ? 0.0 : pow2i(En - c.E);
         }
-        // ---- stage 4: beta sweep backwards over the block, posteriors
+        const int Ea = c.E;
+        mbar_wait(ybar, 0);
+        {
+            YRow<K> y;
+            load_y<K, CP>(y, ytile, 0, p.blank, idx);
+            for (int r = 0; r < nrow; ++r) {
+                YRow<K> yn;
+                load_y<K, CP>(yn, ytile, min(r + 1, nrow - 1), p.blank, idx);
+                const double p1 = pr0 * f;
+                const double top = alpha_top<K>(c.a, y, skipA);
+                pr0 = __shfl_up_sync(kFull, top, 1);
+                Slot *sl = slots + (r & 1) * kMaxLatticeWarps;
+                if (lane == 31 && has_upper) sl[warp].m0 = top;
+                alpha_rest<K>(c.a, top, p1, y, skipA);
+                double *ar = arow + (size_t)r * NT * K;
+#pragma unroll
+                for (int h = 0; h < K / 2; ++h)
+                    *reinterpret_cast<double2 *>(ar + ((size_t)h * NT + thread) * 2) =
+                        make_double2(c.a[2 * h], c.a[2 * h + 1]);
+                if (nwa > 1) named_bar_sync(1, nbar);
+                if (lane == 0) pr0 = has_lower ? sl[warp - 1].m0 : 0.0;
+                y = yn;
+            }
+        }
+        // ---- stage 3: beta sweep backwards over the block, posteriors
         const double invP = 1.0 / p.Pm[b];
         const int eP = p.Pe[b];
-        E = 0;
         f = 1.0;
-        if (t0 + nrow == Tb) {  // virtual beta_T: 1 at state S-1
+        if (t0 + nrow == Tb) {  // virtual beta_T: 1 at state S-1, everything in scale 2^0
+            const int s1 = S - 1;
+            c.E = 0;
 #pragma unroll
-            for (int k = 0; k < K; ++k) a[k] = (thread * K + k == S - 1) ? 1.0 : 0.0;
+            for (int k = 0; k < K; ++k) c.a[k] = (thread * K + k == s1) ? 1.0 : 0.0;
+            pr0 = __shfl_down_sync(kFull, c.a[0], 1);
+            pr1 = __shfl_down_sync(kFull, c.a[1], 1);
+            if (lane == 31) {
+                pr0 = ((thread + 1) * K == s1) ? 1.0 : 0.0;
+                pr1 = 0.0;
+            }
         } else {
-            const double *src = p.ckB + (((size_t)b * p.nblk + blk) * NT + thread) * K;
+            const double *src = p.ckB + (cb + thread) * K;
 #pragma unroll
             for (int k = 0; k < K; k += 2) {
                 const double2 v = *reinterpret_cast<const double2 *>(src + k);
-                a[k] = v.x;
-                a[k + 1] = v.y;
+                c.a[k] = v.x;
+                c.a[k + 1] = v.y;
             }
-            E = p.ckBE[((size_t)b * p.nblk + blk) * NT + thread];
-            const int En = __shfl_down_sync(kFull, E, 1);
-            f = lane == 31 ? 1.0 : pow2i(En - E);
-        }
-        if (lane == 0 && warp > 0) {
-            slots[warp].m0 = a[0];
-            slots[warp].m1 = a[1];
-            slots[warp].E = E;
-        }
-        if (nwa > 1) named_bar_sync(1, nbar);
-        for (int q = 0; q < nrow; ++q) {
-            const int r = nrow - 1 - q, t = t0 + r;
-            const Slot *rd = slots + (q & 1) * kMaxLatticeWarps;
-            Slot *wr = slots + ((q + 1) & 1) * kMaxLatticeWarps;
-            double n1 = __shfl_down_sync(kFull, a[0], 1) * f;
-            double n2 = __shfl_down_sync(kFull, a[1], 1) * f;
-            int carryE = 0;
-            const bool has_up = warp + 1 < nwa;
+            c.E = p.ckBE[cb + thread];
+            pr0 = __shfl_down_sync(kFull, c.a[0], 1);
+            pr1 = __shfl_down_sync(kFull, c.a[1], 1);
+            int En = __shfl_down_sync(kFull, c.E, 1);
             if (lane == 31) {
-                if (!has_up) {
-                    n1 = 0.0;
-                    n2 = 0.0;
-                } else {
-                    const Slot s = rd[warp + 1];
-                    carryE = s.E;
-                    const double fs = pow2i(s.E - E);
-                    n1 = s.m0 * fs;
-                    n2 = s.m1 * fs;
-                }
+                pr0 = has_upper ? p.ckB[(cb + thread + 1) * K] : 0.0;
+                pr1 = has_upper ? p.ckB[(cb + thread + 1) * K + 1] : 0.0;
+                En = has_upper ? p.ckBE[cb + thread + 1] : kDeadE;
             }
-            double bb[K];
-            beta_cells<K>(a, bb, n1, n2, ytile + r * C, p.blank, idx, skipB);
-            // posterior(t,s) = alpha_t(s) * betabar_t(s) / P
-            const double g = pow2i(min(Ea[r * NT + thread] + E - eP, 1000)) * invP;
-            const double *ar = arow + (size_t)r * NT * K;
-            double bsum = 0.0;
-#pragma unroll
-            for (int h = 0; h < K / 2; ++h) {
-                const double2 av = *reinterpret_cast<const double2 *>(ar + ((size_t)h * NT + thread) * 2);
-                bsum = fma(av.x, bb[2 * h], bsum);
-                const double pl = av.y * bb[2 * h + 1] * g;
-                if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
-            }
-            bpart[r * NT + thread] = (float)(bsum * g);
-            if ((t % kRenorm) == 0) {
-                carryE = __shfl_sync(kFull, carryE, 31);
-                renorm<K, false>(a, E, f, lane, carryE, has_up);
-            }
-            if (lane == 0 && warp > 0) {
-                wr[warp].m0 = a[0];
-                wr[warp].m1 = a[1];
-                wr[warp].E = E;
-            }
-            if (nwa > 1) named_bar_sync(1, nbar);
+            f = (En == kDeadE) ? 0.0 : pow2i(En - c.E);
         }
+        {
+            // posterior(t,s) = alpha_t(s) * betabar_t(s) / P ; both exponents are constant over the block
+            const double g = pow2i(min(max(Ea, -(1 << 28)) + max(c.E, -(1 << 28)) - eP, 1000)) * invP;
+            YRow<K> y;
+            load_y<K, CP>(y, ytile, nrow - 1, p.blank, idx);
+            for (int qq = 0; qq < nrow; ++qq) {
+                const int r = nrow - 1 - qq;
+                YRow<K> yn;
+                load_y<K, CP>(yn, ytile, max(r - 1, 0), p.blank, idx);
+                const double *ar = arow + (size_t)r * NT * K;
+                double2 av[K / 2];
+#pragma unroll
+                for (int h = 0; h < K / 2; ++h)
+                    av[h] = *reinterpret_cast<const double2 *>(ar + ((size_t)h * NT + thread) * 2);
+                const double n1 = pr0 * f, n2 = pr1 * f;
+                double b0, b1, s0, s1v;
+                beta_bottom<K>(c.a, y, skipB, b0, b1, s0, s1v);
+                pr0 = __shfl_down_sync(kFull, s0, 1);
+                pr1 = __shfl_down_sync(kFull, s1v, 1);
+                Slot *sl = slots + (qq & 1) * kMaxLatticeWarps;
+                if (lane == 0 && has_lower) {
+                    sl[warp].m0 = s0;
+                    sl[warp].m1 = s1v;
+                }
+                double bb[K];
+                beta_rest<K>(c.a, bb, b0, b1, s0, s1v, n1, n2, y, skipB);
+                double bsum = 0.0;
+#pragma unroll
+                for (int h = 0; h < K / 2; ++h) {
+                    bsum = fma(av[h].x, bb[2 * h], bsum);
+                    const double pl = av[h].y * bb[2 * h + 1] * g;
+                    if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
+                }
+                bpart[r * NT + thread] = (float)(bsum * g);
+                if (nwa > 1) named_bar_sync(1, nbar);
+                if (lane == 31) {
+                    pr0 = has_upper ? sl[warp + 1].m0 : 0.0;
+                    pr1 = has_upper ? sl[warp + 1].m1 : 0.0;
+                }
+                y = yn;
+            }
+        }
+    } else {
+        mbar_wait(ybar, 0);
     }
     __syncthreads();
-    // ---- stage 5: per-class occupancy, gradient rows written once
+    // ---- stage 4: per-class occupancy, gradient rows written once
     const float scale = p.grad_scale;
     const int nthr_a = nwa * 32;
     for (int r = warp; r < rows_out; r += nwl) {
@@ -595,7 +751,7 @@ __global__ void __launch_bounds__(kMaxLatticeWarps * 32) ctc_grad_kernel(const C
                 const int q1 = coff[c + 1];
                 for (int q = coff[c]; q < q1; ++q) occ += psort[r * Lp + q];
             }
-            grow[c] = scale * ((float)ytile[r * C + c] - occ);
+            grow[c] = scale * (y_from_words(ytile[r * 2 * Cp + c], ytile[r * 2 * Cp + Cp + c]) - occ);
         }
     }
 }

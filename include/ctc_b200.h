@@ -54,8 +54,9 @@ typedef struct {
                               1: they are DEVICE pointers; max_label_len must then be given */
     int max_label_len;     /* upper bound on label_lens[b]; <=0 means "derive it" (host lengths only) */
     int phase_mask;        /* profiling aid, 0 in production: bit0 = skip the recursion (engine) kernel, bit1 = skip
-                              the gradient kernel; a skipped phase reuses what the previous full call left in the
-                              workspace (bench.py times each kernel alone with CUDA events this way) */
+                              the gradient kernel, bit2 = skip the softmax/prep kernel; a skipped phase reuses what
+                              the previous full call left in the workspace (bench.py times each kernel alone with
+                              CUDA events this way) */
     int reserved[3];       /* must be zero */
 } ctcB200Options;
 

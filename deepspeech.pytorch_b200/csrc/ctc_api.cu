@@ -32,7 +32,9 @@ struct Plan {
                // 16-byte multiples for TMA and gathers are bank-conflict-free)
     size_t smem_prep, smem_engine, smem_grad;
     // workspace byte offsets
-    size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_lpos, o_coff, o_labels, o_llen, o_alen;
+    int nqmax;   // grad kernel warps per CTA
+    int nsplit;  // grad kernel CTAs per utterance
+    size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_tlab, o_coff, o_labels, o_llen, o_alen;
     size_t total;
 };
 
@@ -50,12 +52,22 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     const int NT = nwl * 32;
     // one checkpoint per group of 8 time steps: the grad kernel then never renormalises or re-settles exponents
     const int R = kGroup;
-    if (grad_smem(C, pl->Cp, Lmax, NT, kK).total > kSmemLimit) return false;
+    pl->nqmax = (S + kK * kCoreThreads - 1) / (kK * kCoreThreads);
+    if (pl->nqmax > kMaxGradWarps) return false;
+    if (grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK).total > kSmemLimit) return false;
     pl->R = R;
     pl->nblk = T > 0 ? (T + R - 1) / R : 1;
-    pl->smem_prep = prep_smem(C);
+    pl->smem_prep = prep_smem(C, Lmax);
     pl->smem_engine = engine_smem(pl->Cp, nwl).total;
-    pl->smem_grad = grad_smem(C, pl->Cp, Lmax, NT, kK).total;
+    pl->smem_grad = grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK).total;
+    {
+        // deal the time groups of an utterance to enough CTAs to fill the machine about twice over
+        const int resident = (int)(kSmemLimit / pl->smem_grad) > 0 ? (int)(kSmemLimit / pl->smem_grad) : 1;
+        int ns = (2 * 148 * resident + B - 1) / B;
+        if (ns > pl->nblk) ns = pl->nblk;
+        if (ns < 1) ns = 1;
+        pl->nsplit = ns;
+    }
     if (pl->smem_engine > kSmemLimit || pl->smem_prep > kSmemLimit) return false;
     size_t o = 0;
     const size_t ck = sizeof(double) * (size_t)B * pl->nblk * NT * kK;
@@ -69,7 +81,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->o_Pe = o;     o = align256(o + sizeof(int) * B);
     pl->o_feas = o;   o = align256(o + sizeof(int) * B);
     pl->o_laboff = o; o = align256(o + sizeof(int) * B);
-    pl->o_lpos = o;   o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
+    pl->o_tlab = o;   o = align256(o + sizeof(uint4) * (size_t)B * NT);
     pl->o_coff = o;   o = align256(o + sizeof(int) * (size_t)B * (C + 1));
     pl->o_labels = o; o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
     pl->o_llen = o;   o = align256(o + sizeof(int) * B);
@@ -112,8 +124,8 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         if (e != cudaSuccess) return e;
     }
     if (!p.score_only && p.T > 0 && !(phase_mask & 2)) {
-        dim3 grid(pl.nblk, p.B);
-        ctc_grad_kernel<kK, CP><<<grid, pl.nwl * 32, pl.smem_grad, st>>>(p);
+        dim3 grid(pl.nsplit, p.B);
+        ctc_grad_kernel<kK, CP><<<grid, pl.nqmax * 32, pl.smem_grad, st>>>(p);
         ++*launches;
         e = cudaGetLastError();
     }
@@ -243,7 +255,9 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
     p.Pe = reinterpret_cast<int *>(ws + pl.o_Pe);
     p.feas = reinterpret_cast<int *>(ws + pl.o_feas);
     p.laboff = reinterpret_cast<int *>(ws + pl.o_laboff);
-    p.lpos = reinterpret_cast<int *>(ws + pl.o_lpos);
+    p.tlab = reinterpret_cast<uint4 *>(ws + pl.o_tlab);
+    p.nsplit = pl.nsplit;
+    p.nqmax = pl.nqmax;
     p.coff = reinterpret_cast<int *>(ws + pl.o_coff);
 
     int launches = 0;

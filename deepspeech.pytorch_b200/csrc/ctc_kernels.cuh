@@ -49,8 +49,10 @@ struct CtcParams {
     int *Pe;            // [B] exponent of p(l|x)
     int *feas;          // [B] 1 = feasible
     int *laboff;        // [B] offset of utterance b in `labels`
-    int *lpos;          // [B][Lmax] position of label i in class-sorted order
     int *coff;          // [B][C+1]  class segment offsets in that order
+    uint4 *tlab;        // [B][nwl*32] per lattice thread (K = 8): packed label classes, skip/valid bits, lpos
+    int nsplit;         // grad kernel: time blocks are dealt round-robin to this many CTAs per utterance
+    int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
 #ifdef CTC_PROFILE
     long long *dbg;     // [ctas][16 warps][8] clock counters (tools/ubench/engine_bench.cu only)
 #endif
@@ -74,8 +76,10 @@ __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t
 // ================================================================================================ prep
 constexpr int kPrepRows = 128;
 
-__host__ __device__ inline size_t prep_smem(int C) {
-    return align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows + sizeof(int) * (C + 1) + 64;
+__host__ __device__ inline size_t prep_smem(int C, int Lmax) {
+    const size_t rows = align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows;
+    const size_t utt = sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1);  // class-sorted positions of one utterance
+    return (rows > utt ? rows : utt) + sizeof(int) * (C + 1) + 64;
 }
 
 // Class-sorted positions of the labels of one utterance (one warp): lpos[i] = rank of label i when labels are
@@ -118,14 +122,15 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     const int C = p.C, Cp = p.Cp;
     const long long nrows_total = (long long)p.T * p.B;
     const int nrb = (int)((nrows_total + kPrepRows - 1) / kPrepRows);
-    float *xs = reinterpret_cast<float *>(smem);
-    float *s_m = reinterpret_cast<float *>(smem + align16(sizeof(float) * kPrepRows * C));
-    float *s_inv = s_m + kPrepRows;
-    int *cnt = reinterpret_cast<int *>(s_inv + kPrepRows);
+    const size_t rows_bytes = align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows;
+    const size_t utt_bytes = sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
+    int *cnt = reinterpret_cast<int *>(smem + (rows_bytes > utt_bytes ? rows_bytes : utt_bytes));
 
     if ((int)blockIdx.x >= nrb) {
-        // ------------------------------------------------ utterance block: label offset + class-sorted order
+        // ------------------------------------------------ utterance block: label offset, class-sorted order and the
+        // per-lattice-thread label table (K = 8: thread e owns labels 4e .. 4e+3)
         const int b = blockIdx.x - nrb;
+        int *lps = reinterpret_cast<int *>(smem);  // [Lmax] class-sorted positions
         int *s_off = cnt + C;
         if (tid == 0) *s_off = 0;
         __syncthreads();
@@ -137,14 +142,35 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
         __syncthreads();
         const int off = *s_off;
         if (tid == 0) p.laboff[b] = off;
-        if (warp == 0 && !p.score_only) {
-            const int L = min(max(p.label_lens[b], 0), p.Lmax);
-            sort_labels_warp(p.labels + off, L, C, cnt, p.lpos + (size_t)b * p.Lmax, p.coff + (size_t)b * (C + 1),
-                             lane);
+        const int L = min(max(p.label_lens[b], 0), p.Lmax);
+        const int *lab = p.labels + off;
+        if (warp == 0) sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
+        __syncthreads();
+        const int NT = p.nwl * 32;
+        for (int e = tid; e < NT; e += blockDim.x) {
+            unsigned cls = 0, bits = 0, lp[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+                const int i = 4 * e + h;
+                const bool valid = i < L;
+                int c = valid ? lab[i] : p.blank;
+                c = min(max(c, 0), C - 1);
+                cls |= (unsigned)c << (8 * h);
+                if (valid) {
+                    bits |= 1u << (8 + h);
+                    if (i == 0 || min(max(lab[i - 1], 0), C - 1) != c) bits |= 1u << h;                // skip into s
+                    if (i + 1 < L && min(max(lab[i + 1], 0), C - 1) != c) bits |= 1u << (4 + h);      // skip out of s
+                    lp[h] = (unsigned)lps[i];
+                }
+            }
+            p.tlab[(size_t)b * NT + e] = make_uint4(cls, bits, lp[0] | (lp[1] << 16), lp[2] | (lp[3] << 16));
         }
         return;
     }
     // ---------------------------------------------------- row block: softmax of 128 consecutive (t,b) rows
+    float *xs = reinterpret_cast<float *>(smem);
+    float *s_m = reinterpret_cast<float *>(smem + align16(sizeof(float) * kPrepRows * C));
+    float *s_inv = s_m + kPrepRows;
     const long long row0 = (long long)blockIdx.x * kPrepRows;
     const int nrows = (int)min((long long)kPrepRows, nrows_total - row0);
     const float *src = p.acts + row0 * C;
@@ -179,9 +205,14 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     __syncthreads();
     for (int r = warp; r < nrows; r += kPrepRows / 32) {
         const float inv = s_inv[r];
-        if (inv < 0.f) continue;  // padding frame: never read by the lattice kernels
-        const float m = s_m[r];
         const long long row = row0 + r;
+        if (inv < 0.f) {
+            // padding frame (t >= act_lens[b]): never read by the lattice kernels; its gradient row is zero
+            if (p.grads)
+                for (int c = lane; c < C; c += 32) p.grads[row * C + c] = 0.f;
+            continue;
+        }
+        const float m = s_m[r];
         const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
         unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * Cp;  // utterance-major: a tile of rows is one bulk copy
         for (int c = lane; c < Cp; c += 32) {
@@ -521,193 +552,216 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
 }
 
 // ================================================================================================ grad
-// One CTA per (utterance, group of 8 time steps).  The checkpoints are renormalised and exponent-settled, so inside
-// the block every thread works with ONE alpha exponent and ONE beta exponent: no renormalisation, no settlement.
+// One CTA per (utterance, every nsplit-th group of 8 time steps).  Warp q owns the 224 lattice states
+// [224q, 224q+224) (28 core threads) and recomputes a HALO of 16 states (2 threads) on either side, which is exactly
+// how far information travels in 8 steps (2 states per step): the warps of a CTA never exchange boundary values and
+// synchronise only twice per group, around the per-class reduction.  The checkpoints are renormalised and
+// exponent-settled, so inside a group every thread works with ONE alpha exponent and ONE beta exponent.
+// The next group's checkpoints (registers) and emission tile (TMA, double buffer) are prefetched during the
+// current one.
+constexpr int kCoreThreads = 28;
+constexpr int kMaxGradWarps = 10;  // ceil((2*1023+1) / 224)
+
 struct GradSmem {
-    size_t ytile, arow, psort, bpart, coff, slots, bar, total;
+    size_t ytile, bar, coff, psort, arow, bpart, total;
 };
-__host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int NT, int K) {
+__host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, int K) {
     GradSmem s;
     size_t o = 0;
-    s.ytile = o; o = align16(o + sizeof(unsigned) * kGroup * 2 * Cp);
-    s.arow = o;  o = align16(o + sizeof(double) * kGroup * NT * K);
-    s.psort = o; o = align16(o + sizeof(float) * kGroup * (Lmax > 0 ? Lmax : 1));
-    s.bpart = o; o = align16(o + sizeof(float) * kGroup * NT);
+    s.ytile = o; o = align16(o + sizeof(unsigned) * 2 * kGroup * 2 * Cp);
+    s.bar = o;   o = align16(o + 2 * sizeof(uint64_t));
     s.coff = o;  o = align16(o + sizeof(int) * (C + 1));
-    s.slots = o; o = align16(o + sizeof(Slot) * 2 * kMaxLatticeWarps);
-    s.bar = o;   o = align16(o + 16);
+    s.psort = o; o = align16(o + sizeof(float) * kGroup * (Lmax > 0 ? Lmax : 1));
+    s.arow = o;  o = align16(o + sizeof(double) * (size_t)nq * kGroup * 32 * K);
+    s.bpart = o; o = align16(o + sizeof(float) * (size_t)nq * kGroup * 32);
     s.total = o;
     return s;
 }
 
 template <int K, int CP>
-__global__ void __launch_bounds__(kMaxLatticeWarps * 32) ctc_grad_kernel(const CtcParams p) {
+__global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcParams p) {
+    static_assert(K == 8, "the label table and the 224-state chunking are laid out for K = 8");
     extern __shared__ __align__(16) unsigned char smem[];
-    constexpr int R = kGroup;
-    const int blk = blockIdx.x, b = blockIdx.y;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nwl = p.nwl, C = p.C, NT = nwl * 32;
-    constexpr int Cp = CP;
+    constexpr int R = kGroup, Cp = CP;
+    const int z = blockIdx.x, b = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
+    const int C = p.C, NT = p.nwl * 32;
     const int Tb = min(max(p.act_lens[b], 0), p.T);
-    const int t0 = blk * R;
-    const int rows_out = min(R, p.T - t0);  // rows this CTA must write
-    float *gbase = p.grads + ((size_t)t0 * p.B + b) * C;
+    const int nblk_b = (Tb + R - 1) / R;
+    if (z >= nblk_b) return;  // padding frames were zero-filled by the prep kernel
     const size_t rowstride = (size_t)p.B * C;
-
-    if (t0 >= Tb || !p.feas[b]) {  // padding frames / infeasible utterance: zeros, written once
-        for (int r = warp; r < rows_out; r += nwl)
-            for (int c = lane; c < C; c += 32) gbase[(size_t)r * rowstride + c] = 0.f;
+    if (!p.feas[b]) {  // infeasible utterance: zero gradient
+        for (int blk = z; blk < nblk_b; blk += p.nsplit)
+            for (int r = q; r < min(R, Tb - blk * R); r += blockDim.x / 32)
+                for (int c = lane; c < C; c += 32) p.grads[((size_t)(blk * R + r) * p.B + b) * C + c] = 0.f;
         return;
     }
-    const int nrow = min(R, Tb - t0);  // valid rows
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
     const int S = 2 * L + 1;
-    const int nwa = min(nwl, (S + 32 * K - 1) / (32 * K));
-    const GradSmem lay = grad_smem(C, Cp, p.Lmax, NT, K);
+    const int nq = (S + K * kCoreThreads - 1) / (K * kCoreThreads);  // <= p.nqmax == blockDim.x / 32
+    const GradSmem lay = grad_smem(C, Cp, p.Lmax, p.nqmax, K);
     unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
-    double *arow = reinterpret_cast<double *>(smem + lay.arow);
-    float *psort = reinterpret_cast<float *>(smem + lay.psort);
-    float *bpart = reinterpret_cast<float *>(smem + lay.bpart);
-    int *coff = reinterpret_cast<int *>(smem + lay.coff);
-    Slot *slots = reinterpret_cast<Slot *>(smem + lay.slots);
     uint64_t *ybar = reinterpret_cast<uint64_t *>(smem + lay.bar);
+    int *coff = reinterpret_cast<int *>(smem + lay.coff);
+    float *psort = reinterpret_cast<float *>(smem + lay.psort);
+    double *arow = reinterpret_cast<double *>(smem + lay.arow) + (size_t)q * R * 32 * K;
+    float *bpart = reinterpret_cast<float *>(smem + lay.bpart);
     const int Lp = p.Lmax > 0 ? p.Lmax : 1;
+    const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
+    const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
 
-    // ---- stage 1: emission rows (one TMA bulk copy), class offsets -> shared
     if (tid == 0) {
-        mbar_init(ybar, 1);
+        mbar_init(&ybar[0], 1);
+        mbar_init(&ybar[1], 1);
         fence_mbar_init();
-        const uint32_t bytes = (uint32_t)(2 * Cp * sizeof(unsigned)) * nrow;
-        mbar_arrive_expect_tx(ybar, bytes);
-        tma_bulk_g2s(ytile, p.y + ((size_t)b * p.T + t0) * 2 * Cp, bytes, ybar);
+        const int nr0 = min(R, Tb - z * R);
+        mbar_arrive_expect_tx(&ybar[0], rowbytes * nr0);
+        tma_bulk_g2s(ytile, ybase + (size_t)(z * R) * 2 * Cp, rowbytes * nr0, &ybar[0]);
     }
     {
         const int *cg = p.coff + (size_t)b * (C + 1);
         for (int c = tid; c <= C; c += blockDim.x) coff[c] = cg[c];
     }
-    __syncthreads();  // mbarrier init visible before anybody waits on it
+    __syncthreads();  // mbarrier init + coff visible
+    if (q >= nq) return;  // warps beyond this utterance's states
+    const int nbar = nq * 32;
 
-    const int thread = warp * 32 + lane;
-    const int nbar = nwa * 32;
-    if (warp < nwa) {
-        const int off = p.laboff[b];
-        int idx[K / 2], lab_i[K / 2], lpos[K / 2];
-        double skipA[K / 2], skipB[K / 2];
-        thread_labels<K>(p.labels + off, L, thread, C, p.blank, idx, skipA, skipB, lab_i);
-        {
-            const int *lg = p.lpos + (size_t)b * p.Lmax;
+    // ---- per-thread constants: engine thread e = 28q - 2 + lane owns states [8e, 8e+8)
+    const int e = kCoreThreads * q - 2 + lane;
+    // the engine runs (and checkpoints) only the warps this utterance needs: threads beyond them hold no state
+    const int ne = min(p.nwl, (S + 32 * K - 1) / (32 * K)) * 32;
+    const bool valid_e = e >= 0 && e < ne;
+    const bool core = valid_e && lane >= 2 && lane < 2 + kCoreThreads;
+    int idx[K / 2], lpos[K / 2];
+    double skipA[K / 2], skipB[K / 2];
+    {
+        uint4 tl = make_uint4(0x01010101u * (unsigned)p.blank, 0u, 0u, 0u);
+        if (valid_e) tl = p.tlab[(size_t)b * NT + e];
 #pragma unroll
-            for (int h = 0; h < K / 2; ++h) lpos[h] = lab_i[h] >= 0 ? lg[lab_i[h]] : -1;
+        for (int h = 0; h < K / 2; ++h) {
+            idx[h] = (tl.x >> (8 * h)) & 0xff;
+            skipA[h] = ((tl.y >> h) & 1) ? 1.0 : 0.0;
+            skipB[h] = ((tl.y >> (4 + h)) & 1) ? 1.0 : 0.0;
+            const unsigned lw = (h < 2) ? tl.z : tl.w;
+            lpos[h] = (core && ((tl.y >> (8 + h)) & 1)) ? (int)((lw >> (16 * (h & 1))) & 0xffff) : -1;
         }
-        const bool has_lower = warp > 0, has_upper = warp + 1 < nwa;
+    }
+    const double invP = 1.0 / p.Pm[b];
+    const int eP = p.Pe[b];
+    const int s_last = S - 1;
+
+    // checkpoint registers of the NEXT group to process (prefetched one group ahead)
+    double nA[K], nB[K];
+    int nEa = 0, nEb = 0;
+    auto fetch = [&](int blk) {
         const size_t cb = ((size_t)b * p.nblk + blk) * NT;
+        const bool hasA = valid_e && blk > 0, hasB = valid_e && (blk + 1) * R < Tb;
+#pragma unroll
+        for (int k = 0; k < K; k += 2) {
+            double2 va = make_double2(0.0, 0.0), vb = make_double2(0.0, 0.0);
+            if (hasA) va = *reinterpret_cast<const double2 *>(p.ckA + (cb + e) * K + k);
+            if (hasB) vb = *reinterpret_cast<const double2 *>(p.ckB + (cb + e) * K + k);
+            nA[k] = va.x; nA[k + 1] = va.y;
+            nB[k] = vb.x; nB[k + 1] = vb.y;
+        }
+        nEa = hasA ? p.ckAE[cb + e] : 0;
+        nEb = hasB ? p.ckBE[cb + e] : 0;
+    };
+    fetch(z);
+
+    int it = 0;
+    for (int blk = z; blk < nblk_b; blk += p.nsplit, ++it) {
+        const int cur = it & 1;
+        const int t0 = blk * R;
+        const int nrow = min(R, Tb - t0);
+        const unsigned *yt = ytile + (size_t)cur * R * 2 * Cp;
+        // ---- current checkpoints out of the prefetch registers, then prefetch the next group
         Cells<K> c;
-        double pr0 = 0.0, pr1 = 0.0, f = 1.0;
-        // ---- stage 2: recompute alpha rows t0 .. t0+nrow-1 from the checkpoint "after row t0-1"
-        if (blk == 0) {
+        double bsave[K];
 #pragma unroll
-            for (int k = 0; k < K; ++k) c.a[k] = 0.0;
-            c.E = 0;
-            if (thread == 0) pr0 = 1.0;
-        } else {
-            const double *src = p.ckA + (cb + thread) * K;
-#pragma unroll
-            for (int k = 0; k < K; k += 2) {
-                const double2 v = *reinterpret_cast<const double2 *>(src + k);
-                c.a[k] = v.x;
-                c.a[k + 1] = v.y;
+        for (int k = 0; k < K; ++k) { c.a[k] = nA[k]; bsave[k] = nB[k]; }
+        c.E = nEa;
+        const int Eb0 = nEb;
+        const int nblk_next = blk + p.nsplit;
+        if (nblk_next < nblk_b) {
+            if (tid == 0) {
+                const int nrn = min(R, Tb - nblk_next * R);
+                fence_proxy_async();
+                mbar_arrive_expect_tx(&ybar[cur ^ 1], rowbytes * nrn);
+                tma_bulk_g2s(ytile + (size_t)(cur ^ 1) * R * 2 * Cp, ybase + (size_t)(nblk_next * R) * 2 * Cp,
+                             rowbytes * nrn, &ybar[cur ^ 1]);
             }
-            c.E = p.ckAE[cb + thread];
+            fetch(nblk_next);
+        }
+        // ---- alpha rows t0 .. t0+nrow-1 from the checkpoint "after row t0-1"
+        double pr0, pr1 = 0.0, f;
+        {
+            const int En = __shfl_up_sync(kFull, c.E, 1);
             pr0 = __shfl_up_sync(kFull, c.a[K - 1], 1);
-            int En = __shfl_up_sync(kFull, c.E, 1);
-            if (lane == 0) {
-                pr0 = has_lower ? p.ckA[(cb + thread - 1) * K + K - 1] : 0.0;
-                En = has_lower ? p.ckAE[cb + thread - 1] : kDeadE;
-            }
             f = (En == kDeadE) ? 0.0 : pow2i(En - c.E);
+            if (lane == 0) pr0 = 0.0;
+            if (blk == 0) {  // everything in scale 2^0; virtual alpha_{-1}(-1) = 1 flows into state 0
+                f = 1.0;
+                pr0 = (e == 0) ? 1.0 : 0.0;
+            }
         }
         const int Ea = c.E;
-        mbar_wait(ybar, 0);
+        mbar_wait(&ybar[cur], (it >> 1) & 1);
         {
             YRow<K> y;
-            load_y<K, CP>(y, ytile, 0, p.blank, idx);
+            load_y<K, CP>(y, yt, 0, p.blank, idx);
             for (int r = 0; r < nrow; ++r) {
                 YRow<K> yn;
-                load_y<K, CP>(yn, ytile, min(r + 1, nrow - 1), p.blank, idx);
+                load_y<K, CP>(yn, yt, min(r + 1, nrow - 1), p.blank, idx);
                 const double p1 = pr0 * f;
                 const double top = alpha_top<K>(c.a, y, skipA);
                 pr0 = __shfl_up_sync(kFull, top, 1);
-                Slot *sl = slots + (r & 1) * kMaxLatticeWarps;
-                if (lane == 31 && has_upper) sl[warp].m0 = top;
+                if (lane == 0) pr0 = 0.0;
                 alpha_rest<K>(c.a, top, p1, y, skipA);
-                double *ar = arow + (size_t)r * NT * K;
+                double *ar = arow + (size_t)r * 32 * K;
 #pragma unroll
                 for (int h = 0; h < K / 2; ++h)
-                    *reinterpret_cast<double2 *>(ar + ((size_t)h * NT + thread) * 2) =
+                    *reinterpret_cast<double2 *>(ar + ((size_t)h * 32 + lane) * 2) =
                         make_double2(c.a[2 * h], c.a[2 * h + 1]);
-                if (nwa > 1) named_bar_sync(1, nbar);
-                if (lane == 0) pr0 = has_lower ? sl[warp - 1].m0 : 0.0;
                 y = yn;
             }
         }
-        // ---- stage 3: beta sweep backwards over the block, posteriors
-        const double invP = 1.0 / p.Pm[b];
-        const int eP = p.Pe[b];
-        f = 1.0;
+        // ---- beta sweep backwards over the group, posteriors
         if (t0 + nrow == Tb) {  // virtual beta_T: 1 at state S-1, everything in scale 2^0
-            const int s1 = S - 1;
             c.E = 0;
 #pragma unroll
-            for (int k = 0; k < K; ++k) c.a[k] = (thread * K + k == s1) ? 1.0 : 0.0;
-            pr0 = __shfl_down_sync(kFull, c.a[0], 1);
-            pr1 = __shfl_down_sync(kFull, c.a[1], 1);
-            if (lane == 31) {
-                pr0 = ((thread + 1) * K == s1) ? 1.0 : 0.0;
-                pr1 = 0.0;
-            }
+            for (int k = 0; k < K; ++k) c.a[k] = (valid_e && e * K + k == s_last) ? 1.0 : 0.0;
+            f = 1.0;
         } else {
-            const double *src = p.ckB + (cb + thread) * K;
 #pragma unroll
-            for (int k = 0; k < K; k += 2) {
-                const double2 v = *reinterpret_cast<const double2 *>(src + k);
-                c.a[k] = v.x;
-                c.a[k + 1] = v.y;
-            }
-            c.E = p.ckBE[cb + thread];
-            pr0 = __shfl_down_sync(kFull, c.a[0], 1);
-            pr1 = __shfl_down_sync(kFull, c.a[1], 1);
-            int En = __shfl_down_sync(kFull, c.E, 1);
-            if (lane == 31) {
-                pr0 = has_upper ? p.ckB[(cb + thread + 1) * K] : 0.0;
-                pr1 = has_upper ? p.ckB[(cb + thread + 1) * K + 1] : 0.0;
-                En = has_upper ? p.ckBE[cb + thread + 1] : kDeadE;
-            }
+            for (int k = 0; k < K; ++k) c.a[k] = bsave[k];
+            c.E = Eb0;
+            const int En = __shfl_down_sync(kFull, c.E, 1);
             f = (En == kDeadE) ? 0.0 : pow2i(En - c.E);
         }
+        pr0 = __shfl_down_sync(kFull, c.a[0], 1);
+        pr1 = __shfl_down_sync(kFull, c.a[1], 1);
+        if (lane == 31) { pr0 = 0.0; pr1 = 0.0; }
         {
-            // posterior(t,s) = alpha_t(s) * betabar_t(s) / P ; both exponents are constant over the block
+            // posterior(t,s) = alpha_t(s) * betabar_t(s) / P ; both exponents are constant over the group
             const double g = pow2i(min(max(Ea, -(1 << 28)) + max(c.E, -(1 << 28)) - eP, 1000)) * invP;
             YRow<K> y;
-            load_y<K, CP>(y, ytile, nrow - 1, p.blank, idx);
+            load_y<K, CP>(y, yt, nrow - 1, p.blank, idx);
             for (int qq = 0; qq < nrow; ++qq) {
                 const int r = nrow - 1 - qq;
                 YRow<K> yn;
-                load_y<K, CP>(yn, ytile, max(r - 1, 0), p.blank, idx);
-                const double *ar = arow + (size_t)r * NT * K;
+                load_y<K, CP>(yn, yt, max(r - 1, 0), p.blank, idx);
+                const double *ar = arow + (size_t)r * 32 * K;
                 double2 av[K / 2];
 #pragma unroll
                 for (int h = 0; h < K / 2; ++h)
-                    av[h] = *reinterpret_cast<const double2 *>(ar + ((size_t)h * NT + thread) * 2);
+                    av[h] = *reinterpret_cast<const double2 *>(ar + ((size_t)h * 32 + lane) * 2);
                 const double n1 = pr0 * f, n2 = pr1 * f;
                 double b0, b1, s0, s1v;
                 beta_bottom<K>(c.a, y, skipB, b0, b1, s0, s1v);
                 pr0 = __shfl_down_sync(kFull, s0, 1);
                 pr1 = __shfl_down_sync(kFull, s1v, 1);
-                Slot *sl = slots + (qq & 1) * kMaxLatticeWarps;
-                if (lane == 0 && has_lower) {
-                    sl[warp].m0 = s0;
-                    sl[warp].m1 = s1v;
-                }
+                if (lane == 31) { pr0 = 0.0; pr1 = 0.0; }
                 double bb[K];
                 beta_rest<K>(c.a, bb, b0, b1, s0, s1v, n1, n2, y, skipB);
                 double bsum = 0.0;
@@ -717,43 +771,33 @@ __global__ void __launch_bounds__(kMaxLatticeWarps * 32) ctc_grad_kernel(const C
                     const double pl = av[h].y * bb[2 * h + 1] * g;
                     if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
                 }
-                bpart[r * NT + thread] = (float)(bsum * g);
-                if (nwa > 1) named_bar_sync(1, nbar);
-                if (lane == 31) {
-                    pr0 = has_upper ? sl[warp + 1].m0 : 0.0;
-                    pr1 = has_upper ? sl[warp + 1].m1 : 0.0;
-                }
+                bpart[(q * R + r) * 32 + lane] = core ? (float)(bsum * g) : 0.f;
                 y = yn;
             }
         }
-    } else {
-        mbar_wait(ybar, 0);
-    }
-    __syncthreads();
-    // ---- stage 4: per-class occupancy, gradient rows written once
-    const float scale = p.grad_scale;
-    const int nthr_a = nwa * 32;
-    for (int r = warp; r < rows_out; r += nwl) {
-        float *grow = gbase + (size_t)r * rowstride;
-        if (r >= nrow) {
-            for (int c = lane; c < C; c += 32) grow[c] = 0.f;
-            continue;
-        }
-        float ob = 0.f;
-        for (int j = lane; j < nthr_a; j += 32) ob += bpart[r * NT + j];
+        named_bar_sync(1, nbar);
+        // ---- per-class occupancy, gradient rows written once
+        const float scale = p.grad_scale;
+        for (int r = q; r < nrow; r += nq) {
+            float *grow = p.grads + ((size_t)(t0 + r) * p.B + b) * C;
+            float ob = 0.f;
+            for (int j = 0; j < nq; ++j) ob += bpart[(j * R + r) * 32 + lane];
 #pragma unroll
-        for (int d = 16; d; d >>= 1) ob += __shfl_xor_sync(kFull, ob, d);
-        for (int c = lane; c < C; c += 32) {
-            float occ = 0.f;
-            if (c == p.blank) {
-                occ = ob;
-            } else {
-                const int q1 = coff[c + 1];
-                for (int q = coff[c]; q < q1; ++q) occ += psort[r * Lp + q];
+            for (int d = 16; d; d >>= 1) ob += __shfl_xor_sync(kFull, ob, d);
+            for (int cc = lane; cc < C; cc += 32) {
+                float occ = 0.f;
+                if (cc == p.blank) {
+                    occ = ob;
+                } else {
+                    const int q1 = coff[cc + 1];
+                    for (int qi = coff[cc]; qi < q1; ++qi) occ += psort[r * Lp + qi];
+                }
+                grow[cc] = scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) - occ);
             }
-            grow[c] = scale * (y_from_words(ytile[r * 2 * Cp + c], ytile[r * 2 * Cp + Cp + c]) - occ);
         }
+        named_bar_sync(1, nbar);  // psort / bpart / emission buffer are reused by the next group
     }
+    (void)rowstride;
 }
 
 }  // namespace ctcb200

@@ -45,15 +45,18 @@ int main(int argc, char **argv) {
     size_t ck = sizeof(double) * (size_t)B * p.nblk * NT * kK, ckE = sizeof(int) * (size_t)B * p.nblk * NT;
     CK(cudaMalloc(&p.ckA, ck)); CK(cudaMalloc(&p.ckB, ck)); CK(cudaMalloc(&p.ckAE, ckE)); CK(cudaMalloc(&p.ckBE, ckE));
     CK(cudaMalloc(&p.Pm, 8 * B)); CK(cudaMalloc(&p.Pe, 4 * B)); CK(cudaMalloc(&p.feas, 4 * B)); CK(cudaMalloc(&p.laboff, 4 * B));
-    CK(cudaMalloc(&p.lpos, 4 * (size_t)B * Lmax)); CK(cudaMalloc(&p.coff, 4 * (size_t)B * (C + 1)));
+    CK(cudaMalloc(&p.tlab, 16 * (size_t)B * NT)); CK(cudaMalloc(&p.coff, 4 * (size_t)B * (C + 1)));
 #ifdef CTC_PROFILE
     CK(cudaMalloc(&p.dbg, 8 * 2 * B * 16 * 8)); CK(cudaMemset(p.dbg, 0, 8 * 2 * B * 16 * 8));
 #endif
-    size_t s_prep = prep_smem(C), s_eng = engine_smem(p.Cp, p.nwl).total, s_grad = grad_smem(C, p.Cp, Lmax, NT, kK).total;
+    p.nqmax = (2 * Lmax + 1 + 223) / 224;
+    size_t s_prep = prep_smem(C, Lmax), s_eng = engine_smem(p.Cp, p.nwl).total, s_grad = grad_smem(C, p.Cp, Lmax, p.nqmax, kK).total;
+    { int resident = (int)(227 * 1024 / s_grad); if (resident < 1) resident = 1; p.nsplit = (2 * 148 * resident + B - 1) / B; if (p.nsplit > p.nblk) p.nsplit = p.nblk; if (argc > 5) p.nsplit = atoi(argv[5]); }
     CK(cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     CK(cudaFuncSetAttribute(ctc_engine_kernel<kK, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     CK(cudaFuncSetAttribute(ctc_grad_kernel<kK, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     if (s_eng < eng_pad) s_eng = eng_pad;
+    printf("nqmax %d nsplit %d\n", p.nqmax, p.nsplit);
     printf("B=%d T=%d C=%d Lmax=%d nwl=%d R=%d smem prep %zu engine %zu grad %zu\n", B, T, C, Lmax, p.nwl, R, s_prep, s_eng, s_grad);
     cudaEvent_t e[4];
     for (auto &x : e) cudaEventCreate(&x);
@@ -65,7 +68,8 @@ int main(int argc, char **argv) {
         cudaEventRecord(e[1]);
         ctc_engine_kernel<kK, 32><<<2 * B, (p.nwl + 1) * 32, s_eng>>>(p);
         cudaEventRecord(e[2]);
-        ctc_grad_kernel<kK, 32><<<dim3(p.nblk, B), p.nwl * 32, s_grad>>>(p);
+        if (getenv("SCORE_ONLY")) { CtcParams q = p; q.score_only = 1; cudaEventRecord(e[1]); ctc_engine_kernel<kK, 32><<<B, (p.nwl + 1) * 32, s_eng>>>(q); cudaEventRecord(e[2]); }
+        ctc_grad_kernel<kK, 32><<<dim3(p.nsplit, B), p.nqmax * 32, s_grad>>>(p);
         cudaEventRecord(e[3]);
         CK(cudaDeviceSynchronize());
         for (int k = 0; k < 3; ++k) { float ms; cudaEventElapsedTime(&ms, e[k], e[k + 1]); best[k] = std::min(best[k], ms); }

@@ -578,6 +578,73 @@ __host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, i
     return s;
 }
 
+// alpha rows of one group recomputed into shared memory (thread-private slots, conflict-free 16-byte accesses)
+template <int K, int CP, bool FULL>
+__device__ __forceinline__ void grad_alpha_rows(Cells<K> &c, double pr0, double f, const unsigned *yt, int nrow,
+                                                int blank, const int (&idx)[K / 2], const double (&skipA)[K / 2],
+                                                int lane, double *arow) {
+    YRow<K> y;
+    load_y<K, CP>(y, yt, 0, blank, idx);
+#pragma unroll
+    for (int r = 0; r < kGroup; ++r) {
+        if (FULL || r < nrow) {
+            YRow<K> yn;
+            load_y<K, CP>(yn, yt, FULL ? min(r + 1, kGroup - 1) : min(r + 1, nrow - 1), blank, idx);
+            const double p1 = pr0 * f;
+            const double top = alpha_top<K>(c.a, y, skipA);
+            pr0 = __shfl_up_sync(kFull, top, 1);
+            if (lane == 0) pr0 = 0.0;
+            alpha_rest<K>(c.a, top, p1, y, skipA);
+            double *ar = arow + (size_t)r * 32 * K;
+#pragma unroll
+            for (int h = 0; h < K / 2; ++h)
+                *reinterpret_cast<double2 *>(ar + ((size_t)h * 32 + lane) * 2) = make_double2(c.a[2 * h], c.a[2 * h + 1]);
+            y = yn;
+        }
+    }
+}
+
+// beta sweep over one group with posteriors: label-state posteriors -> psort (class-sorted slots), blank-state
+// posteriors summed per thread -> bpart
+template <int K, int CP, bool FULL>
+__device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double pr1, double f, double g,
+                                               const unsigned *yt, int nrow, int blank, const int (&idx)[K / 2],
+                                               const double (&skipB)[K / 2], const int (&lpos)[K / 2], bool core,
+                                               int lane, const double *arow, float *psort, int Lp, float *bpart_w) {
+    YRow<K> y;
+    load_y<K, CP>(y, yt, nrow - 1, blank, idx);
+#pragma unroll
+    for (int qq = 0; qq < kGroup; ++qq) {
+        const int r = (FULL ? kGroup : nrow) - 1 - qq;
+        if (FULL || r >= 0) {
+            YRow<K> yn;
+            load_y<K, CP>(yn, yt, max(r - 1, 0), blank, idx);
+            const double *ar = arow + (size_t)r * 32 * K;
+            double2 av[K / 2];
+#pragma unroll
+            for (int h = 0; h < K / 2; ++h)
+                av[h] = *reinterpret_cast<const double2 *>(ar + ((size_t)h * 32 + lane) * 2);
+            const double n1 = pr0 * f, n2 = pr1 * f;
+            double b0, b1, s0, s1v;
+            beta_bottom<K>(c.a, y, skipB, b0, b1, s0, s1v);
+            pr0 = __shfl_down_sync(kFull, s0, 1);
+            pr1 = __shfl_down_sync(kFull, s1v, 1);
+            if (lane == 31) { pr0 = 0.0; pr1 = 0.0; }
+            double bb[K];
+            beta_rest<K>(c.a, bb, b0, b1, s0, s1v, n1, n2, y, skipB);
+            double bsum = 0.0;
+#pragma unroll
+            for (int h = 0; h < K / 2; ++h) {
+                bsum = fma(av[h].x, bb[2 * h], bsum);
+                const double pl = av[h].y * bb[2 * h + 1] * g;
+                if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
+            }
+            bpart_w[r * 32 + lane] = core ? (float)(bsum * g) : 0.f;
+            y = yn;
+        }
+    }
+}
+
 template <int K, int CP>
 __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcParams p) {
     static_assert(K == 8, "the label table and the 224-state chunking are laid out for K = 8");
@@ -669,8 +736,10 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
     };
     fetch(z);
 
+    PROF(long long g0 = prof_clk(); long long ga = 0; long long gb = 0; long long gw = 0; long long gr = 0; long long gs = 0; long long gb1 = 0; long long gb2 = 0;)
     int it = 0;
     for (int blk = z; blk < nblk_b; blk += p.nsplit, ++it) {
+        PROF(long long h0 = prof_clk();)
         const int cur = it & 1;
         const int t0 = blk * R;
         const int nrow = min(R, Tb - t0);
@@ -706,27 +775,13 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
             }
         }
         const int Ea = c.E;
+        PROF(long long h1 = prof_clk();)
         mbar_wait(&ybar[cur], (it >> 1) & 1);
-        {
-            YRow<K> y;
-            load_y<K, CP>(y, yt, 0, p.blank, idx);
-            for (int r = 0; r < nrow; ++r) {
-                YRow<K> yn;
-                load_y<K, CP>(yn, yt, min(r + 1, nrow - 1), p.blank, idx);
-                const double p1 = pr0 * f;
-                const double top = alpha_top<K>(c.a, y, skipA);
-                pr0 = __shfl_up_sync(kFull, top, 1);
-                if (lane == 0) pr0 = 0.0;
-                alpha_rest<K>(c.a, top, p1, y, skipA);
-                double *ar = arow + (size_t)r * 32 * K;
-#pragma unroll
-                for (int h = 0; h < K / 2; ++h)
-                    *reinterpret_cast<double2 *>(ar + ((size_t)h * 32 + lane) * 2) =
-                        make_double2(c.a[2 * h], c.a[2 * h + 1]);
-                y = yn;
-            }
-        }
+        PROF(long long h2 = prof_clk();)
+        if (nrow == R) grad_alpha_rows<K, CP, true>(c, pr0, f, yt, nrow, p.blank, idx, skipA, lane, arow);
+        else grad_alpha_rows<K, CP, false>(c, pr0, f, yt, nrow, p.blank, idx, skipA, lane, arow);
         // ---- beta sweep backwards over the group, posteriors
+        PROF(long long h3 = prof_clk();)
         if (t0 + nrow == Tb) {  // virtual beta_T: 1 at state S-1, everything in scale 2^0
             c.E = 0;
 #pragma unroll
@@ -745,58 +800,64 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
         {
             // posterior(t,s) = alpha_t(s) * betabar_t(s) / P ; both exponents are constant over the group
             const double g = pow2i(min(max(Ea, -(1 << 28)) + max(c.E, -(1 << 28)) - eP, 1000)) * invP;
-            YRow<K> y;
-            load_y<K, CP>(y, yt, nrow - 1, p.blank, idx);
-            for (int qq = 0; qq < nrow; ++qq) {
-                const int r = nrow - 1 - qq;
-                YRow<K> yn;
-                load_y<K, CP>(yn, yt, max(r - 1, 0), p.blank, idx);
-                const double *ar = arow + (size_t)r * 32 * K;
-                double2 av[K / 2];
-#pragma unroll
-                for (int h = 0; h < K / 2; ++h)
-                    av[h] = *reinterpret_cast<const double2 *>(ar + ((size_t)h * 32 + lane) * 2);
-                const double n1 = pr0 * f, n2 = pr1 * f;
-                double b0, b1, s0, s1v;
-                beta_bottom<K>(c.a, y, skipB, b0, b1, s0, s1v);
-                pr0 = __shfl_down_sync(kFull, s0, 1);
-                pr1 = __shfl_down_sync(kFull, s1v, 1);
-                if (lane == 31) { pr0 = 0.0; pr1 = 0.0; }
-                double bb[K];
-                beta_rest<K>(c.a, bb, b0, b1, s0, s1v, n1, n2, y, skipB);
-                double bsum = 0.0;
-#pragma unroll
-                for (int h = 0; h < K / 2; ++h) {
-                    bsum = fma(av[h].x, bb[2 * h], bsum);
-                    const double pl = av[h].y * bb[2 * h + 1] * g;
-                    if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
-                }
-                bpart[(q * R + r) * 32 + lane] = core ? (float)(bsum * g) : 0.f;
-                y = yn;
-            }
+            float *bpart_w = bpart + (size_t)q * R * 32;
+            if (nrow == R)
+                grad_beta_rows<K, CP, true>(c, pr0, pr1, f, g, yt, nrow, p.blank, idx, skipB, lpos, core, lane, arow,
+                                            psort, Lp, bpart_w);
+            else
+                grad_beta_rows<K, CP, false>(c, pr0, pr1, f, g, yt, nrow, p.blank, idx, skipB, lpos, core, lane, arow,
+                                             psort, Lp, bpart_w);
         }
+        PROF(long long h4 = prof_clk();)
         named_bar_sync(1, nbar);
+        PROF(long long h4b = prof_clk(); gb1 += h4b - h4;)
         // ---- per-class occupancy, gradient rows written once
+        // lane = (class slot lane>>3, row lane&7): the 8 lanes of a class walk the same segment of the class-sorted
+        // posteriors (equal trip counts), 4 independent loads in flight; warp q takes classes q*4+slot, +4*nq, ...
         const float scale = p.grad_scale;
-        for (int r = q; r < nrow; r += nq) {
-            float *grow = p.grads + ((size_t)(t0 + r) * p.B + b) * C;
-            float ob = 0.f;
-            for (int j = 0; j < nq; ++j) ob += bpart[(j * R + r) * 32 + lane];
+        {
+            const int r = lane & 7;
+            for (int cc = q * 4 + (lane >> 3); cc < C; cc += 4 * nq) {
+                float o = 0.f;
+                if (r < nrow) {
+                    if (cc == p.blank) {
+                        const float *bp = bpart + r * 32;
+                        float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
+                        for (int j = 0; j < nq; ++j) {
+                            const float *bj = bp + (size_t)j * R * 32;
 #pragma unroll
-            for (int d = 16; d; d >>= 1) ob += __shfl_xor_sync(kFull, ob, d);
-            for (int cc = lane; cc < C; cc += 32) {
-                float occ = 0.f;
-                if (cc == p.blank) {
-                    occ = ob;
-                } else {
-                    const int q1 = coff[cc + 1];
-                    for (int qi = coff[cc]; qi < q1; ++qi) occ += psort[r * Lp + qi];
+                            for (int l = 0; l < 32; l += 4) {
+                                o0 += bj[l];
+                                o1 += bj[l + 1];
+                                o2 += bj[l + 2];
+                                o3 += bj[l + 3];
+                            }
+                        }
+                        o = (o0 + o1) + (o2 + o3);
+                    } else {
+                        const float *ps = psort + r * Lp;
+                        int qi = coff[cc];
+                        const int q1 = coff[cc + 1];
+                        float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
+                        for (; qi + 3 < q1; qi += 4) {
+                            o0 += ps[qi];
+                            o1 += ps[qi + 1];
+                            o2 += ps[qi + 2];
+                            o3 += ps[qi + 3];
+                        }
+                        for (; qi < q1; ++qi) o0 += ps[qi];
+                        o = (o0 + o1) + (o2 + o3);
+                    }
+                    p.grads[((size_t)(t0 + r) * p.B + b) * C + cc] =
+                        scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) - o);
                 }
-                grow[cc] = scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) - occ);
             }
         }
+        PROF(long long h5 = prof_clk();)
         named_bar_sync(1, nbar);  // psort / bpart / emission buffer are reused by the next group
+        PROF(long long h6 = prof_clk(); gs += h1 - h0; gw += h2 - h1; ga += h3 - h2; gb += h4 - h3; gr += h5 - h4b; gb2 += h6 - h5;)
     }
+    PROF(if (lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) { long long *d = p.dbg + (32 + q) * 8; d[0] = prof_clk() - g0; d[1] = gs; d[2] = gw; d[3] = ga; d[4] = gb; d[5] = gr; d[6] = it; d[7] = gb1 * 1000000 + gb2; })
     (void)rowstride;
 }
 

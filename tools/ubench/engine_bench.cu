@@ -47,7 +47,7 @@ int main(int argc, char **argv) {
     CK(cudaMalloc(&p.Pm, 8 * B)); CK(cudaMalloc(&p.Pe, 4 * B)); CK(cudaMalloc(&p.feas, 4 * B)); CK(cudaMalloc(&p.laboff, 4 * B));
     CK(cudaMalloc(&p.tlab, 16 * (size_t)B * NT)); CK(cudaMalloc(&p.coff, 4 * (size_t)B * (C + 1)));
 #ifdef CTC_PROFILE
-    CK(cudaMalloc(&p.dbg, 8 * 2 * B * 16 * 8)); CK(cudaMemset(p.dbg, 0, 8 * 2 * B * 16 * 8));
+    CK(cudaMalloc(&p.dbg, 8 * 2 * B * 16 * 8 + 8192)); CK(cudaMemset(p.dbg, 0, 8 * 2 * B * 16 * 8 + 8192));
 #endif
     p.nqmax = (2 * Lmax + 1 + 223) / 224;
     size_t s_prep = prep_smem(C, Lmax), s_eng = engine_smem(p.Cp, p.nwl).total, s_grad = grad_smem(C, p.Cp, Lmax, p.nqmax, kK).total;
@@ -80,13 +80,19 @@ int main(int argc, char **argv) {
     double s = 0; for (float c : costs) s += c;
     printf("sum costs %.4f  cost[0] %.4f (T=%d L=%d)\n", s, costs[0], al[0], ll[0]);
 #ifdef CTC_PROFILE
-    std::vector<long long> dbg(2 * B * 16 * 8);
+    std::vector<long long> dbg(2 * B * 16 * 8 + 1024);
     CK(cudaMemcpy(dbg.data(), p.dbg, dbg.size() * 8, cudaMemcpyDeviceToHost));
     for (int cta = 0; cta < 2; ++cta)
         for (int w = 0; w < p.nwl + 1; ++w) {
             long long *d = &dbg[(cta * 16 + w) * 8];
             printf("cta %d warp %d: total %lld  work %lld  barrier %lld  groups %lld  loop %lld steps %lld renorm %lld settle %lld\n", cta, w, d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);
         }
+#endif
+#ifdef CTC_PROFILE
+    for (int w = 0; w < p.nqmax; ++w) {
+        long long *d = &dbg[(32 + w) * 8];
+        printf("grad cta(0,0) warp %d: total %lld setup %lld ywait %lld alpha %lld beta %lld reduce %lld items %lld bar1 %lld bar2 %lld\n", w, d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7] / 1000000, d[7] % 1000000);
+    }
 #endif
     return 0;
 }

@@ -34,6 +34,8 @@ struct Plan {
     // workspace byte offsets
     int nqmax;   // grad kernel warps per CTA
     int nsplit;  // grad kernel CTAs per utterance
+    int big;     // large-alphabet path (C > kMaxSmallC)
+    size_t o_rowstat, o_occpos, o_order;
     size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_tlab, o_coff, o_labels, o_llen, o_alen;
     size_t total;
 };
@@ -42,13 +44,15 @@ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 // Shape -> launch plan.  Returns false if the shape is outside what this build supports.
 bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
-    if (T < 0 || B < 1 || C < 2 || C > kMaxSmallC || Lmax < 0) return false;
+    if (T < 0 || B < 1 || C < 2 || Lmax < 0) return false;
+    pl->big = C > kMaxSmallC;
+    if (pl->big && Lmax > 255) return false;  // position-indexed emission rows: 1 + L <= 256 (this build)
     const int S = 2 * Lmax + 1;
     const int nwl = (S + 32 * kK - 1) / (32 * kK);
     if (nwl > kMaxLatticeWarps) return false;  // label length > 1023
     pl->nwl = nwl;
     pl->Lmax = Lmax;
-    pl->Cp = C <= 32 ? 32 : (C <= 64 ? 64 : 128);
+    pl->Cp = pl->big ? 256 : (C <= 32 ? 32 : (C <= 64 ? 64 : 128));
     const int NT = nwl * 32;
     // one checkpoint per group of 8 time steps: the grad kernel then never renormalises or re-settles exponents
     const int R = kGroup;
@@ -57,7 +61,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     if (grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK).total > kSmemLimit) return false;
     pl->R = R;
     pl->nblk = T > 0 ? (T + R - 1) / R : 1;
-    pl->smem_prep = prep_smem(C, Lmax);
+    pl->smem_prep = pl->big ? prep_big_smem(C, Lmax) : prep_smem(C, Lmax);
     pl->smem_engine = engine_smem(pl->Cp, nwl).total;
     pl->smem_grad = grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK).total;
     {
@@ -82,6 +86,9 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->o_feas = o;   o = align256(o + sizeof(int) * B);
     pl->o_laboff = o; o = align256(o + sizeof(int) * B);
     pl->o_tlab = o;   o = align256(o + sizeof(uint4) * (size_t)B * NT);
+    pl->o_rowstat = o; if (pl->big) o = align256(o + sizeof(float2) * (size_t)T * B);
+    pl->o_occpos = o;  if (pl->big) o = align256(o + sizeof(float) * (size_t)T * B * pl->Cp);
+    pl->o_order = o;   if (pl->big) o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
     pl->o_coff = o;   o = align256(o + sizeof(int) * (size_t)B * (C + 1));
     pl->o_labels = o; o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
     pl->o_llen = o;   o = align256(o + sizeof(int) * B);
@@ -102,7 +109,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         e = cudaFuncSetAttribute(ctc_engine_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(ctc_grad_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        e = cudaFuncSetAttribute(ctc_grad_kernel<kK, CP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
@@ -125,7 +132,52 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
     }
     if (!p.score_only && p.T > 0 && !(phase_mask & 2)) {
         dim3 grid(pl.nsplit, p.B);
-        ctc_grad_kernel<kK, CP><<<grid, pl.nqmax * 32, pl.smem_grad, st>>>(p);
+        ctc_grad_kernel<kK, CP, false><<<grid, pl.nqmax * 32, pl.smem_grad, st>>>(p);
+        ++*launches;
+        e = cudaGetLastError();
+    }
+    return e;
+}
+
+cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
+    constexpr int CP = 256;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(ctc_prep_utt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_engine_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_grad_kernel<kK, CP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    cudaError_t e = cudaSuccess;
+    const long long rows = (long long)p.T * p.B;
+    if (!(phase_mask & 4) && p.T > 0) {
+        ctc_prep_utt_kernel<<<p.B, kPrepRows, pl.smem_prep, st>>>(p);
+        ++*launches;
+        ctc_prep_big_kernel<CP><<<(unsigned)rows, kBigThreads, 256, st>>>(p);
+        ++*launches;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (!(phase_mask & 1)) {
+        const int engine_ctas = p.score_only ? p.B : 2 * p.B;
+        ctc_engine_kernel<kK, CP><<<engine_ctas, (pl.nwl + 1) * 32, pl.smem_engine, st>>>(p);
+        ++*launches;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (!p.score_only && p.T > 0 && !(phase_mask & 2)) {
+        dim3 grid(pl.nsplit, p.B);
+        ctc_grad_kernel<kK, CP, true><<<grid, pl.nqmax * 32, pl.smem_grad, st>>>(p);
+        ++*launches;
+        ctc_final_big_kernel<CP><<<(unsigned)rows, kBigThreads, 0, st>>>(p);
         ++*launches;
         e = cudaGetLastError();
     }
@@ -133,6 +185,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
 }
 
 cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
+    if (pl.big) return launch_big(p, pl, st, phase_mask, launches);
     switch (pl.Cp) {
         case 32: return launch_all_cp<32>(p, pl, st, phase_mask, launches);
         case 64: return launch_all_cp<64>(p, pl, st, phase_mask, launches);
@@ -256,6 +309,11 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
     p.feas = reinterpret_cast<int *>(ws + pl.o_feas);
     p.laboff = reinterpret_cast<int *>(ws + pl.o_laboff);
     p.tlab = reinterpret_cast<uint4 *>(ws + pl.o_tlab);
+    p.big = pl.big;
+    p.bpos = pl.big ? 0 : o.blank;
+    p.rowstat = reinterpret_cast<float2 *>(ws + pl.o_rowstat);
+    p.occpos = reinterpret_cast<float *>(ws + pl.o_occpos);
+    p.order = reinterpret_cast<int *>(ws + pl.o_order);
     p.nsplit = pl.nsplit;
     p.nqmax = pl.nqmax;
     p.coff = reinterpret_cast<int *>(ws + pl.o_coff);

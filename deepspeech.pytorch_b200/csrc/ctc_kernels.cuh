@@ -51,6 +51,11 @@ struct CtcParams {
     int *laboff;        // [B] offset of utterance b in `labels`
     int *coff;          // [B][C+1]  class segment offsets in that order
     uint4 *tlab;        // [B][nwl*32] per lattice thread (K = 8): packed label classes, skip/valid bits, lpos
+    int bpos;           // index of the blank inside an emission row (class rows: blank; position rows: 0)
+    int big;            // 1: large-alphabet path (emission rows indexed by label POSITION, see ctc_prep_big_kernel)
+    float2 *rowstat;    // big: [T*B] (row max, 1/sum) of the softmax
+    float *occpos;      // big: [B][T][Cp] occupancies by position (0: blank, 1+i: label i)
+    int *order;         // big: [B][Lmax] label index at class-sorted position j
     int nsplit;         // grad kernel: time blocks are dealt round-robin to this many CTAs per utterance
     int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
 #ifdef CTC_PROFILE
@@ -116,6 +121,50 @@ __device__ __forceinline__ void sort_labels_warp(const int *lab, int L, int C, i
     }
 }
 
+// Utterance block of the prep kernels (128 threads): label offset, class-sorted order and the per-lattice-thread
+// label table (K = 8: thread e owns labels 4e .. 4e+3).  lps: shared int [Lmax]; cnt: shared int [C + 1].
+__device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *lps, int *cnt) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int C = p.C;
+    int *s_off = cnt + C;
+    if (tid == 0) *s_off = 0;
+    __syncthreads();
+    int part = 0;
+    for (int i = tid; i < b; i += blockDim.x) part += max(p.label_lens[i], 0);
+#pragma unroll
+    for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(kFull, part, d);
+    if (lane == 0 && part) atomicAdd(s_off, part);
+    __syncthreads();
+    const int off = *s_off;
+    if (tid == 0) p.laboff[b] = off;
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
+    const int *lab = p.labels + off;
+    if (warp == 0) sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
+    __syncthreads();
+    if (p.big)
+        for (int i = tid; i < L; i += blockDim.x) p.order[(size_t)b * p.Lmax + lps[i]] = i;
+    const int NT = p.nwl * 32;
+    for (int e = tid; e < NT; e += blockDim.x) {
+        unsigned cls = 0, bits = 0, lp[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+            const int i = 4 * e + h;
+            const bool valid = i < L;
+            int c = valid ? lab[i] : p.blank;
+            c = min(max(c, 0), C - 1);
+            // emission-row index: the class itself, or (large alphabets) the label's own position 1 + i
+            cls |= (unsigned)(p.big ? (valid ? 1 + i : 0) : c) << (8 * h);
+            if (valid) {
+                bits |= 1u << (8 + h);
+                if (i == 0 || min(max(lab[i - 1], 0), C - 1) != c) bits |= 1u << h;            // skip into s
+                if (i + 1 < L && min(max(lab[i + 1], 0), C - 1) != c) bits |= 1u << (4 + h);  // skip out of s
+                lp[h] = (unsigned)(p.big ? i : lps[i]);
+            }
+        }
+        p.tlab[(size_t)b * NT + e] = make_uint4(cls, bits, lp[0] | (lp[1] << 16), lp[2] | (lp[3] << 16));
+    }
+}
+
 __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -127,44 +176,7 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     int *cnt = reinterpret_cast<int *>(smem + (rows_bytes > utt_bytes ? rows_bytes : utt_bytes));
 
     if ((int)blockIdx.x >= nrb) {
-        // ------------------------------------------------ utterance block: label offset, class-sorted order and the
-        // per-lattice-thread label table (K = 8: thread e owns labels 4e .. 4e+3)
-        const int b = blockIdx.x - nrb;
-        int *lps = reinterpret_cast<int *>(smem);  // [Lmax] class-sorted positions
-        int *s_off = cnt + C;
-        if (tid == 0) *s_off = 0;
-        __syncthreads();
-        int part = 0;
-        for (int i = tid; i < b; i += blockDim.x) part += max(p.label_lens[i], 0);
-#pragma unroll
-        for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(kFull, part, d);
-        if (lane == 0 && part) atomicAdd(s_off, part);
-        __syncthreads();
-        const int off = *s_off;
-        if (tid == 0) p.laboff[b] = off;
-        const int L = min(max(p.label_lens[b], 0), p.Lmax);
-        const int *lab = p.labels + off;
-        if (warp == 0) sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
-        __syncthreads();
-        const int NT = p.nwl * 32;
-        for (int e = tid; e < NT; e += blockDim.x) {
-            unsigned cls = 0, bits = 0, lp[4] = {0, 0, 0, 0};
-#pragma unroll
-            for (int h = 0; h < 4; ++h) {
-                const int i = 4 * e + h;
-                const bool valid = i < L;
-                int c = valid ? lab[i] : p.blank;
-                c = min(max(c, 0), C - 1);
-                cls |= (unsigned)c << (8 * h);
-                if (valid) {
-                    bits |= 1u << (8 + h);
-                    if (i == 0 || min(max(lab[i - 1], 0), C - 1) != c) bits |= 1u << h;                // skip into s
-                    if (i + 1 < L && min(max(lab[i + 1], 0), C - 1) != c) bits |= 1u << (4 + h);      // skip out of s
-                    lp[h] = (unsigned)lps[i];
-                }
-            }
-            p.tlab[(size_t)b * NT + e] = make_uint4(cls, bits, lp[0] | (lp[1] << 16), lp[2] | (lp[3] << 16));
-        }
+        prep_utterance(p, blockIdx.x - nrb, reinterpret_cast<int *>(smem), cnt);
         return;
     }
     // ---------------------------------------------------- row block: softmax of 128 consecutive (t,b) rows
@@ -221,6 +233,21 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
             ydst[c] = y_hi_word(v);
             ydst[Cp + c] = y_lo_word(v);
         }
+    }
+}
+
+// Decode one entry of the prep kernels' label table.
+template <int K>
+__device__ __forceinline__ void decode_tlab(const uint4 tl, int (&idx)[K / 2], double (&skipA)[K / 2],
+                                            double (&skipB)[K / 2], int (&lpos)[K / 2], bool want_lpos) {
+    static_assert(K == 8, "label table is laid out for K = 8");
+#pragma unroll
+    for (int h = 0; h < K / 2; ++h) {
+        idx[h] = (tl.x >> (8 * h)) & 0xff;
+        skipA[h] = ((tl.y >> h) & 1) ? 1.0 : 0.0;
+        skipB[h] = ((tl.y >> (4 + h)) & 1) ? 1.0 : 0.0;
+        const unsigned lw = (h < 2) ? tl.z : tl.w;
+        lpos[h] = (want_lpos && ((tl.y >> (8 + h)) & 1)) ? (int)((lw >> (16 * (h & 1))) & 0xffff) : -1;
     }
 }
 
@@ -441,11 +468,11 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
 
     // =============================================================== lattice warps
     const int thread = warp * 32 + lane;  // lattice thread index; owns states [thread*K, thread*K+K)
-    const int off = p.laboff[b];
     int idx[K / 2], lab_i[K / 2];
     double skipA[K / 2], skipB[K / 2];
-    thread_labels<K>(p.labels + off, L, thread, C, p.blank, idx, skipA, skipB, lab_i);
+    decode_tlab<K>(p.tlab[(size_t)b * NT + thread], idx, skipA, skipB, lab_i, false);
     (void)lab_i;
+    (void)C;
 
     // initial state: everything in scale 2^0 (f = 1); the first settlement happens after the first group
     Cells<K> c;
@@ -489,17 +516,17 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
             PROF(long long tl0 = prof_clk();)
             if (fwd) {
                 if (nr == kGroup)
-                    alpha_group<K, CP, true>(c, pr0, f, yt, nr, t0, p.blank, idx, skipA, lane, has_lower, has_upper,
+                    alpha_group<K, CP, true>(c, pr0, f, yt, nr, t0, p.bpos, idx, skipA, lane, has_lower, has_upper,
                                          slot_mine, slot_in PROF_PASS);
                 else
-                    alpha_group<K, CP, false>(c, pr0, f, yt, nr, t0, p.blank, idx, skipA, lane, has_lower, has_upper,
+                    alpha_group<K, CP, false>(c, pr0, f, yt, nr, t0, p.bpos, idx, skipA, lane, has_lower, has_upper,
                                           slot_mine, slot_in PROF_PASS);
             } else {
                 if (nr == kGroup)
-                    beta_group<K, CP, true>(c, pr0, pr1, f, yt, nr, t0, p.blank, idx, skipB, lane, has_lower,
+                    beta_group<K, CP, true>(c, pr0, pr1, f, yt, nr, t0, p.bpos, idx, skipB, lane, has_lower,
                                         has_upper, slot_mine, slot_in);
                 else
-                    beta_group<K, CP, false>(c, pr0, pr1, f, yt, nr, t0, p.blank, idx, skipB, lane, has_lower,
+                    beta_group<K, CP, false>(c, pr0, pr1, f, yt, nr, t0, p.bpos, idx, skipB, lane, has_lower,
                                          has_upper, slot_mine, slot_in);
             }
             PROF(t_loop += prof_clk() - tl0;)
@@ -645,7 +672,7 @@ __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double p
     }
 }
 
-template <int K, int CP>
+template <int K, int CP, bool BIG>
 __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcParams p) {
     static_assert(K == 8, "the label table and the 224-state chunking are laid out for K = 8");
     extern __shared__ __align__(16) unsigned char smem[];
@@ -657,7 +684,8 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
     const int nblk_b = (Tb + R - 1) / R;
     if (z >= nblk_b) return;  // padding frames were zero-filled by the prep kernel
     const size_t rowstride = (size_t)p.B * C;
-    if (!p.feas[b]) {  // infeasible utterance: zero gradient
+    if (!p.feas[b]) {  // infeasible utterance: zero gradient (large alphabets: written by the final kernel)
+        if (BIG) return;
         for (int blk = z; blk < nblk_b; blk += p.nsplit)
             for (int r = q; r < min(R, Tb - blk * R); r += blockDim.x / 32)
                 for (int c = lane; c < C; c += 32) p.grads[((size_t)(blk * R + r) * p.B + b) * C + c] = 0.f;
@@ -702,16 +730,9 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
     int idx[K / 2], lpos[K / 2];
     double skipA[K / 2], skipB[K / 2];
     {
-        uint4 tl = make_uint4(0x01010101u * (unsigned)p.blank, 0u, 0u, 0u);
+        uint4 tl = make_uint4(0x01010101u * (unsigned)p.bpos, 0u, 0u, 0u);
         if (valid_e) tl = p.tlab[(size_t)b * NT + e];
-#pragma unroll
-        for (int h = 0; h < K / 2; ++h) {
-            idx[h] = (tl.x >> (8 * h)) & 0xff;
-            skipA[h] = ((tl.y >> h) & 1) ? 1.0 : 0.0;
-            skipB[h] = ((tl.y >> (4 + h)) & 1) ? 1.0 : 0.0;
-            const unsigned lw = (h < 2) ? tl.z : tl.w;
-            lpos[h] = (core && ((tl.y >> (8 + h)) & 1)) ? (int)((lw >> (16 * (h & 1))) & 0xffff) : -1;
-        }
+        decode_tlab<K>(tl, idx, skipA, skipB, lpos, core);
     }
     const double invP = 1.0 / p.Pm[b];
     const int eP = p.Pe[b];
@@ -778,8 +799,8 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
         PROF(long long h1 = prof_clk();)
         mbar_wait(&ybar[cur], (it >> 1) & 1);
         PROF(long long h2 = prof_clk();)
-        if (nrow == R) grad_alpha_rows<K, CP, true>(c, pr0, f, yt, nrow, p.blank, idx, skipA, lane, arow);
-        else grad_alpha_rows<K, CP, false>(c, pr0, f, yt, nrow, p.blank, idx, skipA, lane, arow);
+        if (nrow == R) grad_alpha_rows<K, CP, true>(c, pr0, f, yt, nrow, p.bpos, idx, skipA, lane, arow);
+        else grad_alpha_rows<K, CP, false>(c, pr0, f, yt, nrow, p.bpos, idx, skipA, lane, arow);
         // ---- beta sweep backwards over the group, posteriors
         PROF(long long h3 = prof_clk();)
         if (t0 + nrow == Tb) {  // virtual beta_T: 1 at state S-1, everything in scale 2^0
@@ -802,20 +823,33 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
             const double g = pow2i(min(max(Ea, -(1 << 28)) + max(c.E, -(1 << 28)) - eP, 1000)) * invP;
             float *bpart_w = bpart + (size_t)q * R * 32;
             if (nrow == R)
-                grad_beta_rows<K, CP, true>(c, pr0, pr1, f, g, yt, nrow, p.blank, idx, skipB, lpos, core, lane, arow,
+                grad_beta_rows<K, CP, true>(c, pr0, pr1, f, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
                                             psort, Lp, bpart_w);
             else
-                grad_beta_rows<K, CP, false>(c, pr0, pr1, f, g, yt, nrow, p.blank, idx, skipB, lpos, core, lane, arow,
+                grad_beta_rows<K, CP, false>(c, pr0, pr1, f, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
                                              psort, Lp, bpart_w);
         }
         PROF(long long h4 = prof_clk();)
         named_bar_sync(1, nbar);
         PROF(long long h4b = prof_clk(); gb1 += h4b - h4;)
         // ---- per-class occupancy, gradient rows written once
-        // lane = (class slot lane>>3, row lane&7): the 8 lanes of a class walk the same segment of the class-sorted
-        // posteriors (equal trip counts), 4 independent loads in flight; warp q takes classes q*4+slot, +4*nq, ...
-        const float scale = p.grad_scale;
-        {
+        if (BIG) {
+            // large alphabets: occupancies stay indexed by POSITION (0: blank, 1+i: label i); ctc_final_big_kernel
+            // folds them into the dense softmax rows
+            for (int r = q; r < nrow; r += nq) {
+                float *dst = p.occpos + ((size_t)b * p.T + t0 + r) * Cp;
+                float ob = 0.f;
+                for (int j = 0; j < nq; ++j) ob += bpart[(j * R + r) * 32 + lane];
+#pragma unroll
+                for (int d = 16; d; d >>= 1) ob += __shfl_xor_sync(kFull, ob, d);
+                if (lane == 0) dst[0] = ob;
+                for (int i = lane; i < L; i += 32) dst[1 + i] = psort[r * Lp + i];
+            }
+        } else {
+            // lane = (class slot lane>>3, row lane&7): the 8 lanes of a class walk the same segment of the
+            // class-sorted posteriors (equal trip counts), 4 independent loads in flight; warp q takes classes
+            // q*4+slot, +4*nq, ...
+            const float scale = p.grad_scale;
             const int r = lane & 7;
             for (int cc = q * 4 + (lane >> 3); cc < C; cc += 4 * nq) {
                 float o = 0.f;
@@ -859,6 +893,143 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
     }
     PROF(if (lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) { long long *d = p.dbg + (32 + q) * 8; d[0] = prof_clk() - g0; d[1] = gs; d[2] = gw; d[3] = ga; d[4] = gb; d[5] = gr; d[6] = it; d[7] = gb1 * 1000000 + gb2; })
     (void)rowstride;
+}
+
+
+// ================================================================================================ large alphabets
+// C > 128 (BPE-style vocabularies): the softmax is the HBM-bound part (the row is C floats, the lattice touches only
+// 1 + L of them).  ctc_prep_big_kernel streams each (t,b) row once -- float4 coalesced loads, warp-shuffle + shared
+// memory max / sum reductions -- keeps (max, 1/sum) and gathers the 1 + L emissions the lattice needs into a compact
+// POSITION-indexed row (0: blank, 1+i: label i), so the lattice kernels run unchanged with pitch 256 (L <= 255).
+// ctc_final_big_kernel streams the row a second time and writes grad = scale * (softmax - occupancy) once.
+constexpr int kBigThreads = 256;
+
+__device__ __forceinline__ float block_reduce(float v, float *red, bool is_max) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        const float o = __shfl_xor_sync(kFull, v, d);
+        v = is_max ? fmaxf(v, o) : v + o;
+    }
+    __syncthreads();  // red may still be read by the previous reduction
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float r = red[0];
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) r = is_max ? fmaxf(r, red[w]) : r + red[w];
+    return r;
+}
+
+__host__ __device__ inline size_t prep_big_smem(int C, int Lmax) {
+    const size_t utt = sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1) + sizeof(int) * (C + 1) + 64;
+    return utt > 256 ? utt : 256;
+}
+
+// label tables only (one CTA per utterance); the large-alphabet path runs it ahead of the row kernel
+__global__ void __launch_bounds__(kPrepRows) ctc_prep_utt_kernel(const CtcParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    int *lps = reinterpret_cast<int *>(smem);
+    prep_utterance(p, blockIdx.x, lps, lps + (p.Lmax > 0 ? p.Lmax : 1));
+}
+
+template <int CP>
+__global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x;
+    const int C = p.C;
+    const long long nrows_total = (long long)p.T * p.B;
+    float *red = reinterpret_cast<float *>(smem);
+    const long long row = blockIdx.x;
+    const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
+    const float *x = p.acts + row * C;
+    if (t >= min(max(p.act_lens[b], 0), p.T)) {  // padding frame: zero gradient row, nothing else
+        if (p.grads) {
+            float *g = p.grads + row * C;
+            for (int c = tid; c < C; c += kBigThreads) g[c] = 0.f;
+        }
+        return;
+    }
+    const bool vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+    const int n4 = vec ? (C >> 2) : 0;
+    float m = -INFINITY;
+    for (int i = tid; i < n4; i += kBigThreads) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
+        m = fmaxf(fmaxf(m, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+    }
+    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) m = fmaxf(m, __ldg(x + c));
+    m = block_reduce(m, red, true);
+    float sum = 0.f;
+    for (int i = tid; i < n4; i += kBigThreads) {  // second pass hits L1/L2
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
+        sum += (expf(v.x - m) + expf(v.y - m)) + (expf(v.z - m) + expf(v.w - m));
+    }
+    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) sum += expf(__ldg(x + c) - m);
+    sum = block_reduce(sum, red, false);
+    const float inv = 1.0f / sum;
+    if (tid == 0) p.rowstat[row] = make_float2(m, inv);
+    // compact emission row, planar fp64 words
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
+    const int *lab = p.labels;
+    const int off = p.laboff[b];  // written by ctc_prep_utt_kernel, launched before this kernel
+    unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * CP;
+    for (int j = tid; j < CP; j += kBigThreads) {
+        float v = 1.17549435e-38f;
+        if (j <= L) {
+            const int c = (j == 0) ? p.blank : min(max(lab[off + j - 1], 0), C - 1);
+            v = fmaxf(expf(__ldg(x + c) - m) * inv, 1.17549435e-38f);
+        }
+        ydst[j] = y_hi_word(v);
+        ydst[CP + j] = y_lo_word(v);
+    }
+}
+
+// One CTA per valid (t,b) row: dense softmax gradient streamed out (float4), then the <= 1 + L occupancies are
+// subtracted in place, one thread per distinct class (class-sorted order => deterministic sums for repeated classes).
+template <int CP>
+__global__ void __launch_bounds__(kBigThreads) ctc_final_big_kernel(const CtcParams p) {
+    const int tid = threadIdx.x;
+    const int C = p.C;
+    const long long row = blockIdx.x;
+    const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
+    if (t >= min(max(p.act_lens[b], 0), p.T)) return;  // zero-filled by the prep kernel
+    float *g = p.grads + row * C;
+    if (!p.feas[b]) {
+        for (int c = tid; c < C; c += kBigThreads) g[c] = 0.f;
+        return;
+    }
+    const float *x = p.acts + row * C;
+    const float2 st = p.rowstat[row];
+    const float m = st.x, inv = st.y, scale = p.grad_scale;
+    const bool vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
+    const int n4 = vec ? (C >> 2) : 0;
+    for (int i = tid; i < n4; i += kBigThreads) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
+        float4 o;
+        o.x = scale * fmaxf(expf(v.x - m) * inv, 1.17549435e-38f);
+        o.y = scale * fmaxf(expf(v.y - m) * inv, 1.17549435e-38f);
+        o.z = scale * fmaxf(expf(v.z - m) * inv, 1.17549435e-38f);
+        o.w = scale * fmaxf(expf(v.w - m) * inv, 1.17549435e-38f);
+        reinterpret_cast<float4 *>(g)[i] = o;
+    }
+    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads)
+        g[c] = scale * fmaxf(expf(__ldg(x + c) - m) * inv, 1.17549435e-38f);
+    __syncthreads();  // this CTA's own global writes are visible to it after the barrier
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
+    const int *lab = p.labels + p.laboff[b];
+    const int *ord = p.order + (size_t)b * p.Lmax;
+    const float *occ = p.occpos + ((size_t)b * p.T + t) * CP;
+    for (int j = tid; j <= L; j += kBigThreads) {
+        if (j == L) {  // blank
+            g[p.blank] -= scale * occ[0];
+        } else {
+            const int i0 = ord[j];
+            const int c = lab[i0];
+            if (j == 0 || lab[ord[j - 1]] != c) {  // first position of this class in sorted order
+                float sum = occ[1 + i0];
+                for (int jj = j + 1; jj < L && lab[ord[jj]] == c; ++jj) sum += occ[1 + ord[jj]];
+                g[c] -= scale * sum;
+            }
+        }
+    }
 }
 
 }  // namespace ctcb200

@@ -93,6 +93,31 @@ def test_config3_long_peaky(oracle, b200):
     _check(oracle, b200, _wl(b200, "long_b32_t4000", B=4, sigma=5.0, seed=5))
 
 
+def test_config4_large_alphabet(oracle, b200):
+    # BPE-style vocabulary: the position-indexed emission path (C > 128)
+    d = _wl(b200, "bigc_b64_t1000_c5000", B=4)
+    costs, grads = _check(oracle, b200, d)
+    al = d["act_lens"].numpy()
+    for b in range(4):
+        assert np.all(grads[al[b]:, b, :] == 0.0)
+    assert np.abs(grads.sum(axis=2)).max() <= 5e-5  # 5000 fp32 terms per row
+
+
+def test_large_alphabet_edges(oracle, b200):
+    # C just above the class-row limit, C not a multiple of 4 (unaligned rows), repeated labels, infeasible, L = 0
+    for C in (129, 203):
+        T = 30
+        g = torch.Generator().manual_seed(C)
+        acts = torch.randn(T, 5, C, generator=g) * 2.0
+        targets = [[5, 5, 5, 7, 7, 128], [], [100] * 20, [1, 2, 3, 1, 2, 3, 1, 2, 3], [C - 1]]
+        act_lens = torch.tensor([30, 12, 30, 9, 1], dtype=torch.int32)  # utt2: 20 + 19 repeats > 30 -> infeasible
+        labels, ll = b200.pack_targets(targets)
+        d = {"acts": acts, "labels": labels, "act_lens": act_lens, "label_lens": ll}
+        costs, grads = _check(oracle, b200, d, zero_infinity=True)
+        assert costs[2] == 0.0 and np.all(grads[:, 2] == 0)
+        _check(oracle, b200, d, device_lens=True, grad_scale=0.25)
+
+
 def test_grad_scale_and_score_only(oracle, b200):
     d = _wl(b200, "cpu_b16_t500")
     _check(oracle, b200, d, grad_scale=1.0 / 16)

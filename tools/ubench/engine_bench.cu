@@ -31,7 +31,7 @@ int main(int argc, char **argv) {
     std::normal_distribution<float> N(0, 1);
     for (auto &v : acts) v = N(rng);
     CtcParams p{};
-    p.T = T; p.B = B; p.C = C; p.Cp = 32; p.blank = 0; p.zero_infinity = 1; p.grad_scale = 1.f; p.Lmax = Lmax;
+    p.T = T; p.B = B; p.C = C; p.Cp = 32; p.blank = 0; p.bpos = 0; p.big = 0; p.zero_infinity = 1; p.grad_scale = 1.f; p.Lmax = Lmax;
     p.nwl = (2 * Lmax + 1 + 32 * kK - 1) / (32 * kK); p.R = R; p.nblk = (T + R - 1) / R; p.score_only = 0;
     const int NT = p.nwl * 32;
     float *d_acts, *d_grads, *d_costs; int *d_lab, *d_ll, *d_al;
@@ -54,7 +54,7 @@ int main(int argc, char **argv) {
     { int resident = (int)(227 * 1024 / s_grad); if (resident < 1) resident = 1; p.nsplit = (2 * 148 * resident + B - 1) / B; if (p.nsplit > p.nblk) p.nsplit = p.nblk; if (argc > 5) p.nsplit = atoi(argv[5]); }
     CK(cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     CK(cudaFuncSetAttribute(ctc_engine_kernel<kK, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    CK(cudaFuncSetAttribute(ctc_grad_kernel<kK, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    CK(cudaFuncSetAttribute(ctc_grad_kernel<kK, 32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     if (s_eng < eng_pad) s_eng = eng_pad;
     printf("nqmax %d nsplit %d\n", p.nqmax, p.nsplit);
     printf("B=%d T=%d C=%d Lmax=%d nwl=%d R=%d smem prep %zu engine %zu grad %zu\n", B, T, C, Lmax, p.nwl, R, s_prep, s_eng, s_grad);
@@ -69,7 +69,7 @@ int main(int argc, char **argv) {
         ctc_engine_kernel<kK, 32><<<2 * B, (p.nwl + 1) * 32, s_eng>>>(p);
         cudaEventRecord(e[2]);
         if (getenv("SCORE_ONLY")) { CtcParams q = p; q.score_only = 1; cudaEventRecord(e[1]); ctc_engine_kernel<kK, 32><<<B, (p.nwl + 1) * 32, s_eng>>>(q); cudaEventRecord(e[2]); }
-        ctc_grad_kernel<kK, 32><<<dim3(p.nsplit, B), p.nqmax * 32, s_grad>>>(p);
+        ctc_grad_kernel<kK, 32, false><<<dim3(p.nsplit, B), p.nqmax * 32, s_grad>>>(p);
         cudaEventRecord(e[3]);
         CK(cudaDeviceSynchronize());
         for (int k = 0; k < 3; ++k) { float ms; cudaEventElapsedTime(&ms, e[k], e[k + 1]); best[k] = std::min(best[k], ms); }

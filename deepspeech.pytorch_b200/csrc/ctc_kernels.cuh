@@ -672,6 +672,82 @@ __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double p
     }
 }
 
+// Full group (8 rows), "meet in the middle": the alpha chain (rows 0..3, then 4..7) and the beta chain (rows 7..4,
+// then 3..0) are independent until they cross, so they are interleaved step by step in ONE instruction stream -- twice
+// the instruction-level parallelism, half as many dependent steps.  First half: both store their rows (alpha rows
+// 0-3, betabar rows 4-7, same thread-private shared-memory slots).  Second half: each meets the other's stored rows
+// and forms the posteriors.
+template <int K>
+__device__ __forceinline__ void posterior_row(const double (&al)[K], const double (&bb)[K], double g,
+                                              const int (&lpos)[K / 2], bool core, float *psort_r, float *bpart_r) {
+    double bsum = 0.0;
+#pragma unroll
+    for (int h = 0; h < K / 2; ++h) {
+        bsum = fma(al[2 * h], bb[2 * h], bsum);
+        const double pl = al[2 * h + 1] * bb[2 * h + 1] * g;
+        if (lpos[h] >= 0) psort_r[lpos[h]] = (float)pl;
+    }
+    *bpart_r = core ? (float)(bsum * g) : 0.f;
+}
+
+template <int K, int CP>
+__device__ __forceinline__ void grad_group_mitm(Cells<K> &ca, double pa, double fa, Cells<K> &cb, double pb0,
+                                                double pb1, double fb, double g, const unsigned *yt, int blank,
+                                                const int (&idx)[K / 2], const double (&skipA)[K / 2],
+                                                const double (&skipB)[K / 2], const int (&lpos)[K / 2], bool core,
+                                                int lane, double *rows, float *psort, int Lp, float *bpart_w) {
+    constexpr int H = kGroup / 2;
+    YRow<K> ya, yb;
+    load_y<K, CP>(ya, yt, 0, blank, idx);
+    load_y<K, CP>(yb, yt, kGroup - 1, blank, idx);
+#pragma unroll
+    for (int j = 0; j < kGroup; ++j) {
+        const int ra = j, rb = kGroup - 1 - j;  // alpha row, beta row of this iteration
+        YRow<K> yan, ybn;
+        load_y<K, CP>(yan, yt, min(ra + 1, kGroup - 1), blank, idx);
+        load_y<K, CP>(ybn, yt, max(rb - 1, 0), blank, idx);
+        double stored_b[K], stored_a[K];
+        if (j >= H) {  // second half: fetch the other chain's stored row early
+            const double *sb = rows + (size_t)ra * 32 * K, *sa = rows + (size_t)rb * 32 * K;
+#pragma unroll
+            for (int h = 0; h < K / 2; ++h) {
+                const double2 vb = *reinterpret_cast<const double2 *>(sb + ((size_t)h * 32 + lane) * 2);
+                const double2 va = *reinterpret_cast<const double2 *>(sa + ((size_t)h * 32 + lane) * 2);
+                stored_b[2 * h] = vb.x; stored_b[2 * h + 1] = vb.y;
+                stored_a[2 * h] = va.x; stored_a[2 * h + 1] = va.y;
+            }
+        }
+        // ---- alpha step (row ra)
+        const double p1 = pa * fa;
+        const double top = alpha_top<K>(ca.a, ya, skipA);
+        pa = __shfl_up_sync(kFull, top, 1);
+        if (lane == 0) pa = 0.0;
+        // ---- beta step (row rb)
+        const double n1 = pb0 * fb, n2 = pb1 * fb;
+        double b0, b1, s0, s1v;
+        beta_bottom<K>(cb.a, yb, skipB, b0, b1, s0, s1v);
+        pb0 = __shfl_down_sync(kFull, s0, 1);
+        pb1 = __shfl_down_sync(kFull, s1v, 1);
+        if (lane == 31) { pb0 = 0.0; pb1 = 0.0; }
+        alpha_rest<K>(ca.a, top, p1, ya, skipA);
+        double bb[K];
+        beta_rest<K>(cb.a, bb, b0, b1, s0, s1v, n1, n2, yb, skipB);
+        if (j < H) {
+            double *da = rows + (size_t)ra * 32 * K, *db = rows + (size_t)rb * 32 * K;
+#pragma unroll
+            for (int h = 0; h < K / 2; ++h) {
+                *reinterpret_cast<double2 *>(da + ((size_t)h * 32 + lane) * 2) = make_double2(ca.a[2 * h], ca.a[2 * h + 1]);
+                *reinterpret_cast<double2 *>(db + ((size_t)h * 32 + lane) * 2) = make_double2(bb[2 * h], bb[2 * h + 1]);
+            }
+        } else {
+            posterior_row<K>(ca.a, stored_b, g, lpos, core, psort + ra * Lp, bpart_w + ra * 32 + lane);
+            posterior_row<K>(stored_a, bb, g, lpos, core, psort + rb * Lp, bpart_w + rb * 32 + lane);
+        }
+        ya = yan;
+        yb = ybn;
+    }
+}
+
 template <int K, int CP, bool BIG>
 __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcParams p) {
     static_assert(K == 8, "the label table and the 224-state chunking are laid out for K = 8");
@@ -783,55 +859,52 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
             }
             fetch(nblk_next);
         }
-        // ---- alpha rows t0 .. t0+nrow-1 from the checkpoint "after row t0-1"
-        double pr0, pr1 = 0.0, f;
+        // ---- alpha state "after row t0-1" and beta state "after row t0+nrow" with their inflows
+        double pa, fa, pb0, pb1, fb;
         {
             const int En = __shfl_up_sync(kFull, c.E, 1);
-            pr0 = __shfl_up_sync(kFull, c.a[K - 1], 1);
-            f = (En == kDeadE) ? 0.0 : pow2i(En - c.E);
-            if (lane == 0) pr0 = 0.0;
+            pa = __shfl_up_sync(kFull, c.a[K - 1], 1);
+            fa = (En == kDeadE) ? 0.0 : pow2i(En - c.E);
+            if (lane == 0) pa = 0.0;
             if (blk == 0) {  // everything in scale 2^0; virtual alpha_{-1}(-1) = 1 flows into state 0
-                f = 1.0;
-                pr0 = (e == 0) ? 1.0 : 0.0;
+                fa = 1.0;
+                pa = (e == 0) ? 1.0 : 0.0;
             }
         }
-        const int Ea = c.E;
-        PROF(long long h1 = prof_clk();)
-        mbar_wait(&ybar[cur], (it >> 1) & 1);
-        PROF(long long h2 = prof_clk();)
-        if (nrow == R) grad_alpha_rows<K, CP, true>(c, pr0, f, yt, nrow, p.bpos, idx, skipA, lane, arow);
-        else grad_alpha_rows<K, CP, false>(c, pr0, f, yt, nrow, p.bpos, idx, skipA, lane, arow);
-        // ---- beta sweep backwards over the group, posteriors
-        PROF(long long h3 = prof_clk();)
+        Cells<K> cbeta;
         if (t0 + nrow == Tb) {  // virtual beta_T: 1 at state S-1, everything in scale 2^0
-            c.E = 0;
+            cbeta.E = 0;
 #pragma unroll
-            for (int k = 0; k < K; ++k) c.a[k] = (valid_e && e * K + k == s_last) ? 1.0 : 0.0;
-            f = 1.0;
+            for (int k = 0; k < K; ++k) cbeta.a[k] = (valid_e && e * K + k == s_last) ? 1.0 : 0.0;
+            fb = 1.0;
         } else {
 #pragma unroll
-            for (int k = 0; k < K; ++k) c.a[k] = bsave[k];
-            c.E = Eb0;
-            const int En = __shfl_down_sync(kFull, c.E, 1);
-            f = (En == kDeadE) ? 0.0 : pow2i(En - c.E);
+            for (int k = 0; k < K; ++k) cbeta.a[k] = bsave[k];
+            cbeta.E = Eb0;
+            const int En = __shfl_down_sync(kFull, cbeta.E, 1);
+            fb = (En == kDeadE) ? 0.0 : pow2i(En - cbeta.E);
         }
-        pr0 = __shfl_down_sync(kFull, c.a[0], 1);
-        pr1 = __shfl_down_sync(kFull, c.a[1], 1);
-        if (lane == 31) { pr0 = 0.0; pr1 = 0.0; }
-        {
-            // posterior(t,s) = alpha_t(s) * betabar_t(s) / P ; both exponents are constant over the group
-            const double g = pow2i(min(max(Ea, -(1 << 28)) + max(c.E, -(1 << 28)) - eP, 1000)) * invP;
-            float *bpart_w = bpart + (size_t)q * R * 32;
-            if (nrow == R)
-                grad_beta_rows<K, CP, true>(c, pr0, pr1, f, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
-                                            psort, Lp, bpart_w);
-            else
-                grad_beta_rows<K, CP, false>(c, pr0, pr1, f, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
-                                             psort, Lp, bpart_w);
+        pb0 = __shfl_down_sync(kFull, cbeta.a[0], 1);
+        pb1 = __shfl_down_sync(kFull, cbeta.a[1], 1);
+        if (lane == 31) { pb0 = 0.0; pb1 = 0.0; }
+        // posterior(t,s) = alpha_t(s) * betabar_t(s) / P ; both exponents are constant over the group
+        const double g = pow2i(min(max(c.E, -(1 << 28)) + max(cbeta.E, -(1 << 28)) - eP, 1000)) * invP;
+        float *bpart_w = bpart + (size_t)q * R * 32;
+        PROF(long long h1 = prof_clk();)
+        mbar_wait(&ybar[cur], (it >> 1) & 1);
+        PROF(long long h2 = prof_clk(); long long h3 = h2;)
+        if (nrow == R) {
+            grad_group_mitm<K, CP>(c, pa, fa, cbeta, pb0, pb1, fb, g, yt, p.bpos, idx, skipA, skipB, lpos, core, lane,
+                                   arow, psort, Lp, bpart_w);
+        } else {
+            grad_alpha_rows<K, CP, false>(c, pa, fa, yt, nrow, p.bpos, idx, skipA, lane, arow);
+            PROF(h3 = prof_clk();)
+            grad_beta_rows<K, CP, false>(cbeta, pb0, pb1, fb, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
+                                         psort, Lp, bpart_w);
         }
         PROF(long long h4 = prof_clk();)
         named_bar_sync(1, nbar);
-        PROF(long long h4b = prof_clk(); gb1 += h4b - h4;)
+        PROF(float probe = *reinterpret_cast<volatile float *>(bpart + lane); long long h4b = prof_clk() + (probe > 1e30f ? 1 : 0); gb1 += h4b - h4;)
         // ---- per-class occupancy, gradient rows written once
         if (BIG) {
             // large alphabets: occupancies stay indexed by POSITION (0: blank, 1+i: label i); ctc_final_big_kernel
@@ -873,6 +946,9 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
                         int qi = coff[cc];
                         const int q1 = coff[cc + 1];
                         float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
+#ifdef RED_NOSEG
+                        qi = q1;
+#endif
                         for (; qi + 3 < q1; qi += 4) {
                             o0 += ps[qi];
                             o1 += ps[qi + 1];
@@ -882,6 +958,9 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
                         for (; qi < q1; ++qi) o0 += ps[qi];
                         o = (o0 + o1) + (o2 + o3);
                     }
+#ifdef RED_NOSTORE
+                    if (o == 12345.f)
+#endif
                     p.grads[((size_t)(t0 + r) * p.B + b) * C + cc] =
                         scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) - o);
                 }

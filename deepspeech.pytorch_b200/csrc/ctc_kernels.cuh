@@ -252,7 +252,10 @@ __device__ __forceinline__ void decode_tlab(const uint4 tl, int (&idx)[K / 2], d
 }
 
 // ================================================================================================ engine
-constexpr int kLookAhead = 4;  // emission tiles in flight ahead of the first lattice warp
+#ifndef CTC_LOOKAHEAD
+#define CTC_LOOKAHEAD 4
+#endif
+constexpr int kLookAhead = CTC_LOOKAHEAD;  // emission tiles in flight ahead of the first lattice warp
 
 struct EngineSmem {
     size_t ytile, bars, slots, misc, total;
@@ -406,6 +409,8 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
     Slot *slots = reinterpret_cast<Slot *>(smem + lay.slots);
     double *pm = reinterpret_cast<double *>(smem + lay.misc);  // [2]
     int *pe = reinterpret_cast<int *>(smem + lay.misc + 16);   // [2]
+    double *ck = (fwd ? p.ckA : p.ckB) + (size_t)b * p.nblk * NT * K;
+    int *ckE = (fwd ? p.ckAE : p.ckBE) + (size_t)b * p.nblk * NT;
 
     const int Tb = min(max(p.act_lens[b], 0), p.T);
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
@@ -438,26 +443,33 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
         __syncwarp();
         const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
         const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
+        int ist = 0;  // ring slot of the next tile to issue (issue() is called with j = 0, 1, 2, ...)
         auto issue = [&](int j) {
+            const int st = ist;
+            ist = (ist + 1 == NS) ? 0 : ist + 1;
             if (j < ngroups && lane == 0) {
                 const int G = fwd ? j : (ngroups - 1 - j);
                 const int t0 = G * kGroup;
                 const int nr = min(kGroup, Tb - t0);
-                const int st = j % NS;
                 mbar_arrive_expect_tx(&y_full[st], rowbytes * nr);
                 tma_bulk_g2s(ytile + (size_t)(st * kGroup) * 2 * Cp, ybase + (size_t)t0 * 2 * Cp, rowbytes * nr,
                              &y_full[st]);
             }
         };
+        int wst = 0, wph = 0;  // ring slot / mbarrier phase of the next tile to wait for
+        auto wait_tile = [&]() {
+            mbar_wait(&y_full[wst], wph);
+            if (++wst == NS) { wst = 0; wph ^= 1; }
+        };
         PROF(long long tp0 = prof_clk(); long long t_work = 0; long long t_bar = 0;)
         for (int j = 0; j <= kLookAhead; ++j) issue(j);
-        mbar_wait(&y_full[0], 0);
+        wait_tile();
         named_bar_sync(1, nbar);
         for (int i = 0; i < nsuper; ++i) {
             PROF(long long ta = prof_clk();)
             fence_proxy_async();
             issue(i + kLookAhead + 1);
-            if (i + 1 < ngroups) mbar_wait(&y_full[(i + 1) % NS], ((i + 1) / NS) & 1);
+            if (i + 1 < ngroups) wait_tile();
             PROF(long long tb = prof_clk();)
             named_bar_sync(1, nbar);
             PROF(long long tc = prof_clk(); t_work += tb - ta; t_bar += tc - tb;)
@@ -480,8 +492,6 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
     for (int k = 0; k < K; ++k) c.a[k] = 0.0;
     c.E = 0;
     double f = 1.0, pr0 = 0.0, pr1 = 0.0;
-    double *ck = (fwd ? p.ckA : p.ckB) + (size_t)b * p.nblk * NT * K;
-    int *ckE = (fwd ? p.ckAE : p.ckBE) + (size_t)b * p.nblk * NT;
     const int q = fwd ? warp : (nwa - 1 - warp);  // position in the systolic pipeline
     const bool has_lower = warp > 0, has_upper = warp + 1 < nwa;
     Slot *slot_mine = slots + warp * kRing;
@@ -504,55 +514,67 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
     named_bar_sync(1, nbar);
     PROF(long long tp0 = prof_clk(); long long t_work = 0; long long t_bar = 0; long long ngr = 0; long long t_loop = 0; ProfAcc pa; pa.steps = 0; pa.ren = 0; pa.settle = 0; pa.send = 0;)
 
-    for (int i = 0; i < nsuper; ++i) {
-        const int j = i - q;
-        PROF(long long ta = prof_clk();)
-        if (j >= 0 && j < ngroups) {
-            PROF(++ngr;)
-            const int G = fwd ? j : (ngroups - 1 - j);
-            const int t0 = G * kGroup;
-            const int nr = min(kGroup, Tb - t0);
-            const unsigned *yt = ytile + (size_t)((j % NS) * kGroup) * 2 * Cp;
-            PROF(long long tl0 = prof_clk();)
-            if (fwd) {
-                if (nr == kGroup)
-                    alpha_group<K, CP, true>(c, pr0, f, yt, nr, t0, p.bpos, idx, skipA, lane, has_lower, has_upper,
+    // Systolic schedule: this warp runs group j in super-step q + j and idles (barrier only) before and after.  All
+    // per-group indices advance incrementally -- no multiplies, divisions or 64-bit address rebuilds per group.
+    for (int i = 0; i < q; ++i) named_bar_sync(1, nbar);
+    int st = 0;                                       // ring slot of this warp's next emission tile
+    const unsigned *yt = ytile;
+    int t0 = fwd ? 0 : (ngroups - 1) * kGroup;        // first row of the current group
+    const int dt = fwd ? kGroup : -kGroup;
+    const int ntail = Tb - (ngroups - 1) * kGroup;    // rows of the ragged last group (1..8)
+    // checkpoints (settled exponents): alpha after row t0+7 -> block G+1 ; beta_{t0} -> block G-1, i.e. every group
+    // but this direction's last one.  Global layout per (block, lattice warp): [K/2 cell pairs][32 lanes] double2, so
+    // every store (and every load of the gradient kernel) is one fully coalesced 512-byte access.
+    const int cb0 = fwd ? 1 : ngroups - 2;
+    double2 *ckp = reinterpret_cast<double2 *>(ck + ((ptrdiff_t)cb0 * NT + warp * 32) * K) + lane;
+    int *ckEp = ckE + (ptrdiff_t)cb0 * NT + thread;
+    const ptrdiff_t ckstep = (fwd ? 1 : -1) * (ptrdiff_t)NT * (K / 2), ckEstep = (fwd ? 1 : -1) * (ptrdiff_t)NT;
+    const bool want_ck = !p.score_only;
+    for (int j = 0; j < ngroups; ++j) {
+        PROF(long long ta = prof_clk(); ++ngr;)
+        const bool tail = fwd ? (j == ngroups - 1) : (j == 0);
+        PROF(long long tl0 = prof_clk();)
+        if (fwd) {
+            if (!tail || ntail == kGroup)
+                alpha_group<K, CP, true>(c, pr0, f, yt, kGroup, t0, p.bpos, idx, skipA, lane, has_lower, has_upper,
                                          slot_mine, slot_in PROF_PASS);
-                else
-                    alpha_group<K, CP, false>(c, pr0, f, yt, nr, t0, p.bpos, idx, skipA, lane, has_lower, has_upper,
+            else
+                alpha_group<K, CP, false>(c, pr0, f, yt, ntail, t0, p.bpos, idx, skipA, lane, has_lower, has_upper,
                                           slot_mine, slot_in PROF_PASS);
-            } else {
-                if (nr == kGroup)
-                    beta_group<K, CP, true>(c, pr0, pr1, f, yt, nr, t0, p.bpos, idx, skipB, lane, has_lower,
+        } else {
+            if (!tail || ntail == kGroup)
+                beta_group<K, CP, true>(c, pr0, pr1, f, yt, kGroup, t0, p.bpos, idx, skipB, lane, has_lower,
                                         has_upper, slot_mine, slot_in);
-                else
-                    beta_group<K, CP, false>(c, pr0, pr1, f, yt, nr, t0, p.bpos, idx, skipB, lane, has_lower,
+            else
+                beta_group<K, CP, false>(c, pr0, pr1, f, yt, ntail, t0, p.bpos, idx, skipB, lane, has_lower,
                                          has_upper, slot_mine, slot_in);
-            }
-            PROF(t_loop += prof_clk() - tl0;)
-            // checkpoint (renormalised, settled): alpha after row t0+7 -> block G+1 ; beta_{t0} -> block G-1
-            const int cb = fwd ? G + 1 : G - 1;
-            if (!p.score_only && cb >= 0 && cb * kGroup < Tb) {
-                double *dst = ck + ((size_t)cb * NT + thread) * K;
+        }
+        PROF(t_loop += prof_clk() - tl0;)
+        if (j < ngroups - 1) {
+            if (want_ck) {
 #pragma unroll
-                for (int k = 0; k < K; k += 2)
-                    *reinterpret_cast<double2 *>(dst + k) = make_double2(c.a[k], c.a[k + 1]);
-                ckE[(size_t)cb * NT + thread] = c.E;
+                for (int k = 0; k < K; k += 2) ckp[(k / 2) * 32] = make_double2(c.a[k], c.a[k + 1]);
+                *ckEp = c.E;
             }
-            if (fwd && j == ngroups - 1) {
-                // ---- P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2): the owning threads publish (mantissa, exponent)
-                const int s1 = S - 1, s2 = S - 2;
+            ckp += ckstep;
+            ckEp += ckEstep;
+        } else if (fwd) {
+            // ---- P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2): the owning threads publish (mantissa, exponent)
+            const int s1 = S - 1, s2 = S - 2;
 #pragma unroll
-                for (int k = 0; k < K; ++k) {
-                    if (thread * K + k == s1) { pm[0] = c.a[k]; pe[0] = c.E; }
-                    if (thread * K + k == s2) { pm[1] = c.a[k]; pe[1] = c.E; }
-                }
+            for (int k = 0; k < K; ++k) {
+                if (thread * K + k == s1) { pm[0] = c.a[k]; pe[0] = c.E; }
+                if (thread * K + k == s2) { pm[1] = c.a[k]; pe[1] = c.E; }
             }
         }
+        t0 += dt;
+        yt += kGroup * 2 * Cp;
+        if (++st == NS) { st = 0; yt = ytile; }
         PROF(long long tb = prof_clk();)
         named_bar_sync(1, nbar);
         PROF(long long tc = prof_clk(); t_work += tb - ta; t_bar += tc - tb;)
     }
+    for (int i = q + ngroups; i < nsuper; ++i) named_bar_sync(1, nbar);
     PROF(if (lane == 0 && blockIdx.x < 2) { long long *d = p.dbg + (blockIdx.x * 16 + warp) * 8; d[0] = prof_clk() - tp0; d[1] = t_work; d[2] = t_bar; d[3] = ngr; d[4] = t_loop; d[5] = pa.steps; d[6] = pa.ren; d[7] = pa.settle; })
 
     if (fwd && thread == 0) {
@@ -823,8 +845,8 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
 #pragma unroll
         for (int k = 0; k < K; k += 2) {
             double2 va = make_double2(0.0, 0.0), vb = make_double2(0.0, 0.0);
-            if (hasA) va = *reinterpret_cast<const double2 *>(p.ckA + (cb + e) * K + k);
-            if (hasB) vb = *reinterpret_cast<const double2 *>(p.ckB + (cb + e) * K + k);
+            if (hasA) va = *reinterpret_cast<const double2 *>(p.ckA + (cb + (e & ~31)) * K + ((k / 2) * 32 + (e & 31)) * 2);
+            if (hasB) vb = *reinterpret_cast<const double2 *>(p.ckB + (cb + (e & ~31)) * K + ((k / 2) * 32 + (e & 31)) * 2);
             nA[k] = va.x; nA[k + 1] = va.y;
             nB[k] = vb.x; nB[k + 1] = vb.y;
         }

@@ -35,7 +35,8 @@ struct Plan {
     int nqmax;   // grad kernel warps per CTA
     int nsplit;  // grad kernel CTAs per utterance
     int big;     // large-alphabet path (C > kMaxSmallC)
-    size_t o_rowstat, o_occpos, o_order;
+    size_t o_rowstat, o_occpos, o_order, o_units, o_cu;
+    int numax;   // reduction units per utterance (small alphabets)
     size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_tlab, o_coff, o_labels, o_llen, o_alen;
     size_t total;
 };
@@ -58,12 +59,12 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     const int R = kGroup;
     pl->nqmax = (S + kK * kCoreThreads - 1) / (kK * kCoreThreads);
     if (pl->nqmax > kMaxGradWarps) return false;
-    if (grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK).total > kSmemLimit) return false;
+    if (grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK, pl->big != 0).total > kSmemLimit) return false;
     pl->R = R;
     pl->nblk = T > 0 ? (T + R - 1) / R : 1;
     pl->smem_prep = pl->big ? prep_big_smem(C, Lmax) : prep_smem(C, Lmax);
     pl->smem_engine = engine_smem(pl->Cp, nwl).total;
-    pl->smem_grad = grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK).total;
+    pl->smem_grad = grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK, pl->big != 0).total;
     {
         // deal the time groups of an utterance to enough CTAs to fill the machine about twice over
         const int resident = (int)(kSmemLimit / pl->smem_grad) > 0 ? (int)(kSmemLimit / pl->smem_grad) : 1;
@@ -90,6 +91,9 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->o_occpos = o;  if (pl->big) o = align256(o + sizeof(float) * (size_t)T * B * pl->Cp);
     pl->o_order = o;   if (pl->big) o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
     pl->o_coff = o;   o = align256(o + sizeof(int) * (size_t)B * (C + 1));
+    pl->numax = pl->big ? 0 : grad_max_units(C, Lmax, pl->nqmax);
+    pl->o_units = o;  o = align256(o + sizeof(unsigned) * (size_t)B * pl->numax);
+    pl->o_cu = o;     if (!pl->big) o = align256(o + sizeof(int) * (size_t)B * (C + 1));
     pl->o_labels = o; o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
     pl->o_llen = o;   o = align256(o + sizeof(int) * B);
     pl->o_alen = o;   o = align256(o + sizeof(int) * B);
@@ -317,6 +321,9 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
     p.nsplit = pl.nsplit;
     p.nqmax = pl.nqmax;
     p.coff = reinterpret_cast<int *>(ws + pl.o_coff);
+    p.units = reinterpret_cast<unsigned *>(ws + pl.o_units);
+    p.cu = reinterpret_cast<int *>(ws + pl.o_cu);
+    p.numax = pl.numax;
 
     int launches = 0;
     cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches);

@@ -50,6 +50,9 @@ struct CtcParams {
     int *feas;          // [B] 1 = feasible
     int *laboff;        // [B] offset of utterance b in `labels`
     int *coff;          // [B][C+1]  class segment offsets in that order
+    unsigned *units;    // [B][numax] reduction units of the gradient kernel: start | len << 16 (see grad_units)
+    int *cu;            // [B][C+1]   first unit of class c
+    int numax;          // units per utterance (upper bound)
     uint4 *tlab;        // [B][nwl*32] per lattice thread (K = 8): packed label classes, skip/valid bits, lpos
     int bpos;           // index of the blank inside an emission row (class rows: blank; position rows: 0)
     int big;            // 1: large-alphabet path (emission rows indexed by label POSITION, see ctc_prep_big_kernel)
@@ -77,6 +80,20 @@ struct __align__(8) Slot {
 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+
+// Posterior rows of the gradient kernel (one per time step of a group): [0, Lmax) label posteriors at their
+// class-sorted positions, then nq * 32 per-thread partial sums of the blank posteriors.  The pitch is 1 (mod 32) so
+// that the 8 rows of a group start in 8 different banks.
+constexpr int kUnit = 8;         // positions per reduction unit
+constexpr int kCoreThreads = 28; // engine threads per gradient-kernel warp (224 states) + 2 halo threads each side
+__host__ __device__ inline int grad_nq(int L) { return (2 * L + 1 + 8 * kCoreThreads - 1) / (8 * kCoreThreads); }
+__host__ __device__ inline int grad_row_pitch(int Lmax, int nqmax) {
+    const int n = (Lmax > 0 ? Lmax : 1) + nqmax * 32;
+    return ((n + 30) / 32) * 32 + 1;
+}
+__host__ __device__ inline int grad_max_units(int C, int Lmax, int nqmax) {
+    return ((Lmax > 0 ? Lmax : 1) + kUnit - 1) / kUnit + C + nqmax * (32 / kUnit);
+}
 
 // ================================================================================================ prep
 constexpr int kPrepRows = 128;
@@ -141,6 +158,24 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
     const int *lab = p.labels + off;
     if (warp == 0) sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
     __syncthreads();
+    if (!p.big && tid == 0) {
+        // Reduction units of the gradient kernel: every class segment of the sorted posterior row is cut into pieces
+        // of <= kUnit positions (the blank's segment is the block of per-thread partial sums behind the labels), so
+        // the per-class sums are formed by equal-sized, independent tasks instead of one serial walk per class.
+        const int *cf = p.coff + (size_t)b * (C + 1);
+        unsigned *un = p.units + (size_t)b * p.numax;
+        int *cu = p.cu + (size_t)b * (C + 1);
+        const int Lb = p.Lmax > 0 ? p.Lmax : 1;
+        const int nq = grad_nq(L);
+        int nu = 0;
+        for (int c = 0; c < C; ++c) {
+            cu[c] = nu;
+            int s0 = cf[c], s1 = cf[c + 1];
+            if (c == p.blank) { s0 = Lb; s1 = Lb + nq * 32; }
+            for (; s0 < s1; s0 += kUnit) un[nu++] = (unsigned)s0 | ((unsigned)min(kUnit, s1 - s0) << 16);
+        }
+        cu[C] = nu;
+    }
     if (p.big)
         for (int i = tid; i < L; i += blockDim.x) p.order[(size_t)b * p.Lmax + lps[i]] = i;
     const int NT = p.nwl * 32;
@@ -608,21 +643,24 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
 // exponent-settled, so inside a group every thread works with ONE alpha exponent and ONE beta exponent.
 // The next group's checkpoints (registers) and emission tile (TMA, double buffer) are prefetched during the
 // current one.
-constexpr int kCoreThreads = 28;
 constexpr int kMaxGradWarps = 10;  // ceil((2*1023+1) / 224)
 
 struct GradSmem {
-    size_t ytile, bar, coff, psort, arow, bpart, total;
+    size_t ytile, bar, units, cu, psort, partial, arow, total;
+    int pitch, numax;
 };
-__host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, int K) {
+__host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, int K, bool big) {
     GradSmem s;
+    s.pitch = grad_row_pitch(Lmax, nq);
+    s.numax = big ? 0 : grad_max_units(C, Lmax, nq);
     size_t o = 0;
     s.ytile = o; o = align16(o + sizeof(unsigned) * 2 * kGroup * 2 * Cp);
     s.bar = o;   o = align16(o + 2 * sizeof(uint64_t));
-    s.coff = o;  o = align16(o + sizeof(int) * (C + 1));
-    s.psort = o; o = align16(o + sizeof(float) * kGroup * (Lmax > 0 ? Lmax : 1));
+    s.units = o; o = align16(o + sizeof(unsigned) * s.numax);
+    s.cu = o;    o = align16(o + sizeof(int) * (big ? 0 : C + 1));
+    s.psort = o; o = align16(o + sizeof(float) * kGroup * s.pitch);
+    s.partial = o; o = align16(o + sizeof(float) * kGroup * s.numax);
     s.arow = o;  o = align16(o + sizeof(double) * (size_t)nq * kGroup * 32 * K);
-    s.bpart = o; o = align16(o + sizeof(float) * (size_t)nq * kGroup * 32);
     s.total = o;
     return s;
 }
@@ -688,7 +726,7 @@ __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double p
                 const double pl = av[h].y * bb[2 * h + 1] * g;
                 if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
             }
-            bpart_w[r * 32 + lane] = core ? (float)(bsum * g) : 0.f;
+            bpart_w[r * Lp + lane] = core ? (float)(bsum * g) : 0.f;
             y = yn;
         }
     }
@@ -762,8 +800,8 @@ __device__ __forceinline__ void grad_group_mitm(Cells<K> &ca, double pa, double 
                 *reinterpret_cast<double2 *>(db + ((size_t)h * 32 + lane) * 2) = make_double2(bb[2 * h], bb[2 * h + 1]);
             }
         } else {
-            posterior_row<K>(ca.a, stored_b, g, lpos, core, psort + ra * Lp, bpart_w + ra * 32 + lane);
-            posterior_row<K>(stored_a, bb, g, lpos, core, psort + rb * Lp, bpart_w + rb * 32 + lane);
+            posterior_row<K>(ca.a, stored_b, g, lpos, core, psort + ra * Lp, bpart_w + ra * Lp + lane);
+            posterior_row<K>(stored_a, bb, g, lpos, core, psort + rb * Lp, bpart_w + rb * Lp + lane);
         }
         ya = yan;
         yb = ybn;
@@ -792,14 +830,17 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
     const int S = 2 * L + 1;
     const int nq = (S + K * kCoreThreads - 1) / (K * kCoreThreads);  // <= p.nqmax == blockDim.x / 32
-    const GradSmem lay = grad_smem(C, Cp, p.Lmax, p.nqmax, K);
+    const GradSmem lay = grad_smem(C, Cp, p.Lmax, p.nqmax, K, BIG);
     unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
     uint64_t *ybar = reinterpret_cast<uint64_t *>(smem + lay.bar);
-    int *coff = reinterpret_cast<int *>(smem + lay.coff);
+    unsigned *units = reinterpret_cast<unsigned *>(smem + lay.units);
+    int *cu = reinterpret_cast<int *>(smem + lay.cu);
     float *psort = reinterpret_cast<float *>(smem + lay.psort);
+    float *partial = reinterpret_cast<float *>(smem + lay.partial);
     double *arow = reinterpret_cast<double *>(smem + lay.arow) + (size_t)q * R * 32 * K;
-    float *bpart = reinterpret_cast<float *>(smem + lay.bpart);
-    const int Lp = p.Lmax > 0 ? p.Lmax : 1;
+    const int Lp = lay.pitch;                    // pitch of a posterior row
+    const int Lb = p.Lmax > 0 ? p.Lmax : 1;      // where the blank partial sums start inside a row
+    float *bpart = psort + Lb;                   // [row * Lp + warp * 32 + lane]
     const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
     const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
 
@@ -811,11 +852,15 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
         mbar_arrive_expect_tx(&ybar[0], rowbytes * nr0);
         tma_bulk_g2s(ytile, ybase + (size_t)(z * R) * 2 * Cp, rowbytes * nr0, &ybar[0]);
     }
-    {
-        const int *cg = p.coff + (size_t)b * (C + 1);
-        for (int c = tid; c <= C; c += blockDim.x) coff[c] = cg[c];
+    int NU = 0;
+    if (!BIG) {
+        const int *cg = p.cu + (size_t)b * (C + 1);
+        NU = cg[C];
+        const unsigned *ug = p.units + (size_t)b * p.numax;
+        for (int c = tid; c <= C; c += blockDim.x) cu[c] = cg[c];
+        for (int u = tid; u < NU; u += blockDim.x) units[u] = ug[u];
     }
-    __syncthreads();  // mbarrier init + coff visible
+    __syncthreads();  // mbarrier init + unit tables visible
     if (q >= nq) return;  // warps beyond this utterance's states
     const int nbar = nq * 32;
 
@@ -911,7 +956,7 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
         if (lane == 31) { pb0 = 0.0; pb1 = 0.0; }
         // posterior(t,s) = alpha_t(s) * betabar_t(s) / P ; both exponents are constant over the group
         const double g = pow2i(min(max(c.E, -(1 << 28)) + max(cbeta.E, -(1 << 28)) - eP, 1000)) * invP;
-        float *bpart_w = bpart + (size_t)q * R * 32;
+        float *bpart_w = bpart + q * 32;
         PROF(long long h1 = prof_clk();)
         mbar_wait(&ybar[cur], (it >> 1) & 1);
         PROF(long long h2 = prof_clk(); long long h3 = h2;)
@@ -934,58 +979,43 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
             for (int r = q; r < nrow; r += nq) {
                 float *dst = p.occpos + ((size_t)b * p.T + t0 + r) * Cp;
                 float ob = 0.f;
-                for (int j = 0; j < nq; ++j) ob += bpart[(j * R + r) * 32 + lane];
+                for (int j = 0; j < nq; ++j) ob += bpart[r * Lp + j * 32 + lane];
 #pragma unroll
                 for (int d = 16; d; d >>= 1) ob += __shfl_xor_sync(kFull, ob, d);
                 if (lane == 0) dst[0] = ob;
                 for (int i = lane; i < L; i += 32) dst[1 + i] = psort[r * Lp + i];
             }
         } else {
-            // lane = (class slot lane>>3, row lane&7): the 8 lanes of a class walk the same segment of the
-            // class-sorted posteriors (equal trip counts), 4 independent loads in flight; warp q takes classes
-            // q*4+slot, +4*nq, ...
+            // lane = (task slot lane>>3, row lane&7).  Phase A: one task per (unit, row) sums <= 8 adjacent posteriors
+            // (rows sit 1 bank apart, consecutive units 8 banks apart: conflict-free); phase B: one task per
+            // (class, row) adds the class's unit sums in a fixed order and writes the gradient.
             const float scale = p.grad_scale;
-            const int r = lane & 7;
-            for (int cc = q * 4 + (lane >> 3); cc < C; cc += 4 * nq) {
-                float o = 0.f;
-                if (r < nrow) {
-                    if (cc == p.blank) {
-                        const float *bp = bpart + r * 32;
-                        float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
-                        for (int j = 0; j < nq; ++j) {
-                            const float *bj = bp + (size_t)j * R * 32;
+            const int r = lane & 7, slot = q * 4 + (lane >> 3);
+            for (int u = slot; u < NU; u += 4 * nq) {
+                const unsigned un = units[u];
+                const float *ps = psort + r * Lp + (un & 0xffffu);
+                const int len = (int)(un >> 16);
+                float v[kUnit];
 #pragma unroll
-                            for (int l = 0; l < 32; l += 4) {
-                                o0 += bj[l];
-                                o1 += bj[l + 1];
-                                o2 += bj[l + 2];
-                                o3 += bj[l + 3];
-                            }
-                        }
-                        o = (o0 + o1) + (o2 + o3);
-                    } else {
-                        const float *ps = psort + r * Lp;
-                        int qi = coff[cc];
-                        const int q1 = coff[cc + 1];
-                        float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
-#ifdef RED_NOSEG
-                        qi = q1;
-#endif
-                        for (; qi + 3 < q1; qi += 4) {
-                            o0 += ps[qi];
-                            o1 += ps[qi + 1];
-                            o2 += ps[qi + 2];
-                            o3 += ps[qi + 3];
-                        }
-                        for (; qi < q1; ++qi) o0 += ps[qi];
-                        o = (o0 + o1) + (o2 + o3);
-                    }
-#ifdef RED_NOSTORE
-                    if (o == 12345.f)
-#endif
-                    p.grads[((size_t)(t0 + r) * p.B + b) * C + cc] =
-                        scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) - o);
+                for (int i = 0; i < kUnit; ++i) v[i] = (i < len) ? ps[i] : 0.f;
+                partial[u * kGroup + r] = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+            }
+            named_bar_sync(2, nbar);
+            for (int cc = slot; cc < C; cc += 4 * nq) {
+                const float *pp = partial + r;
+                int u0 = cu[cc];
+                const int u1 = cu[cc + 1];
+                float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
+                for (; u0 + 3 < u1; u0 += 4) {
+                    o0 += pp[u0 * kGroup];
+                    o1 += pp[(u0 + 1) * kGroup];
+                    o2 += pp[(u0 + 2) * kGroup];
+                    o3 += pp[(u0 + 3) * kGroup];
                 }
+                for (; u0 < u1; ++u0) o0 += pp[u0 * kGroup];
+                if (r < nrow)
+                    p.grads[((size_t)(t0 + r) * p.B + b) * C + cc] =
+                        scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) - ((o0 + o1) + (o2 + o3)));
             }
         }
         PROF(long long h5 = prof_clk();)

@@ -46,11 +46,13 @@ int main(int argc, char **argv) {
     CK(cudaMalloc(&p.ckA, ck)); CK(cudaMalloc(&p.ckB, ck)); CK(cudaMalloc(&p.ckAE, ckE)); CK(cudaMalloc(&p.ckBE, ckE));
     CK(cudaMalloc(&p.Pm, 8 * B)); CK(cudaMalloc(&p.Pe, 4 * B)); CK(cudaMalloc(&p.feas, 4 * B)); CK(cudaMalloc(&p.laboff, 4 * B));
     CK(cudaMalloc(&p.tlab, 16 * (size_t)B * NT)); CK(cudaMalloc(&p.coff, 4 * (size_t)B * (C + 1)));
+    p.numax = grad_max_units(C, Lmax, (2 * Lmax + 1 + 223) / 224);
+    CK(cudaMalloc(&p.units, 4 * (size_t)B * p.numax)); CK(cudaMalloc(&p.cu, 4 * (size_t)B * (C + 1)));
 #ifdef CTC_PROFILE
     CK(cudaMalloc(&p.dbg, 8 * 2 * B * 16 * 8 + 8192)); CK(cudaMemset(p.dbg, 0, 8 * 2 * B * 16 * 8 + 8192));
 #endif
     p.nqmax = (2 * Lmax + 1 + 223) / 224;
-    size_t s_prep = prep_smem(C, Lmax), s_eng = engine_smem(p.Cp, p.nwl).total, s_grad = grad_smem(C, p.Cp, Lmax, p.nqmax, kK).total;
+    size_t s_prep = prep_smem(C, Lmax), s_eng = engine_smem(p.Cp, p.nwl).total, s_grad = grad_smem(C, p.Cp, Lmax, p.nqmax, kK, false).total;
     { int resident = (int)(227 * 1024 / s_grad); if (resident < 1) resident = 1; p.nsplit = (2 * 148 * resident + B - 1) / B; if (p.nsplit > p.nblk) p.nsplit = p.nblk; if (argc > 5) p.nsplit = atoi(argv[5]); }
     CK(cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     CK(cudaFuncSetAttribute(ctc_engine_kernel<kK, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));

@@ -158,23 +158,38 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
     const int *lab = p.labels + off;
     if (warp == 0) sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
     __syncthreads();
-    if (!p.big && tid == 0) {
+    if (!p.big && warp == 0) {
         // Reduction units of the gradient kernel: every class segment of the sorted posterior row is cut into pieces
         // of <= kUnit positions (the blank's segment is the block of per-thread partial sums behind the labels), so
         // the per-class sums are formed by equal-sized, independent tasks instead of one serial walk per class.
+        // One lane per class, warp prefix sum over the unit counts.
         const int *cf = p.coff + (size_t)b * (C + 1);
         unsigned *un = p.units + (size_t)b * p.numax;
         int *cu = p.cu + (size_t)b * (C + 1);
         const int Lb = p.Lmax > 0 ? p.Lmax : 1;
         const int nq = grad_nq(L);
-        int nu = 0;
-        for (int c = 0; c < C; ++c) {
-            cu[c] = nu;
-            int s0 = cf[c], s1 = cf[c + 1];
-            if (c == p.blank) { s0 = Lb; s1 = Lb + nq * 32; }
+        int base = 0;
+        for (int c0 = 0; c0 < C; c0 += 32) {
+            const int c = c0 + lane;
+            int s0 = 0, s1 = 0;
+            if (c < C) {
+                s0 = cf[c];
+                s1 = cf[c + 1];
+                if (c == p.blank) { s0 = Lb; s1 = Lb + nq * 32; }
+            }
+            const int n = (s1 - s0 + kUnit - 1) / kUnit;
+            int incl = n;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(kFull, incl, d);
+                if (lane >= d) incl += o;
+            }
+            int nu = base + incl - n;
+            if (c < C) cu[c] = nu;
             for (; s0 < s1; s0 += kUnit) un[nu++] = (unsigned)s0 | ((unsigned)min(kUnit, s1 - s0) << 16);
+            base += __shfl_sync(kFull, incl, 31);
         }
-        cu[C] = nu;
+        if (lane == 0) cu[C] = base;
     }
     if (p.big)
         for (int i = tid; i < L; i += blockDim.x) p.order[(size_t)b * p.Lmax + lps[i]] = i;
@@ -660,16 +675,45 @@ __host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, i
     s.cu = o;    o = align16(o + sizeof(int) * (big ? 0 : C + 1));
     s.psort = o; o = align16(o + sizeof(float) * kGroup * s.pitch);
     s.partial = o; o = align16(o + sizeof(float) * kGroup * s.numax);
-    s.arow = o;  o = align16(o + sizeof(double) * (size_t)nq * kGroup * 32 * K);
+    s.arow = o;  o = align16(o + sizeof(int) * (size_t)nq * kGroup * 32 * K);
     s.total = o;
     return s;
 }
 
-// alpha rows of one group recomputed into shared memory (thread-private slots, conflict-free 16-byte accesses)
+// Rows parked in shared memory are only ever multiplied into posteriors (the recursions continue from registers in
+// full fp64), so they are stored as the HIGH WORD of the double, rounded to nearest: the complete exponent range and
+// 21 significant bits (relative error <= 2^-22 on a posterior <= 1, i.e. < 2.4e-7 on a gradient entry) at half the
+// shared memory and half the load/store wavefronts -- which is what lets a third CTA fit on the SM.
+// Thread-private slots, [K/4][32 lanes] int4: conflict-free 16-byte accesses.
+template <int K>
+__device__ __forceinline__ void park_row(int *row, int lane, const double (&v)[K]) {
+#pragma unroll
+    for (int h = 0; h < K / 4; ++h) {
+        int4 w;
+        w.x = __double2hiint(v[4 * h + 0]) + (int)((unsigned)__double2loint(v[4 * h + 0]) >> 31);
+        w.y = __double2hiint(v[4 * h + 1]) + (int)((unsigned)__double2loint(v[4 * h + 1]) >> 31);
+        w.z = __double2hiint(v[4 * h + 2]) + (int)((unsigned)__double2loint(v[4 * h + 2]) >> 31);
+        w.w = __double2hiint(v[4 * h + 3]) + (int)((unsigned)__double2loint(v[4 * h + 3]) >> 31);
+        *reinterpret_cast<int4 *>(row + (h * 32 + lane) * 4) = w;
+    }
+}
+template <int K>
+__device__ __forceinline__ void fetch_row(const int *row, int lane, double (&v)[K]) {
+#pragma unroll
+    for (int h = 0; h < K / 4; ++h) {
+        const int4 w = *reinterpret_cast<const int4 *>(row + (h * 32 + lane) * 4);
+        v[4 * h + 0] = __hiloint2double(w.x, 0);
+        v[4 * h + 1] = __hiloint2double(w.y, 0);
+        v[4 * h + 2] = __hiloint2double(w.z, 0);
+        v[4 * h + 3] = __hiloint2double(w.w, 0);
+    }
+}
+
+// alpha rows of one group recomputed into shared memory
 template <int K, int CP, bool FULL>
 __device__ __forceinline__ void grad_alpha_rows(Cells<K> &c, double pr0, double f, const unsigned *yt, int nrow,
                                                 int blank, const int (&idx)[K / 2], const double (&skipA)[K / 2],
-                                                int lane, double *arow) {
+                                                int lane, int *arow) {
     YRow<K> y;
     load_y<K, CP>(y, yt, 0, blank, idx);
 #pragma unroll
@@ -682,10 +726,7 @@ __device__ __forceinline__ void grad_alpha_rows(Cells<K> &c, double pr0, double 
             pr0 = __shfl_up_sync(kFull, top, 1);
             if (lane == 0) pr0 = 0.0;
             alpha_rest<K>(c.a, top, p1, y, skipA);
-            double *ar = arow + (size_t)r * 32 * K;
-#pragma unroll
-            for (int h = 0; h < K / 2; ++h)
-                *reinterpret_cast<double2 *>(ar + ((size_t)h * 32 + lane) * 2) = make_double2(c.a[2 * h], c.a[2 * h + 1]);
+            park_row<K>(arow + r * 32 * K, lane, c.a);
             y = yn;
         }
     }
@@ -697,7 +738,7 @@ template <int K, int CP, bool FULL>
 __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double pr1, double f, double g,
                                                const unsigned *yt, int nrow, int blank, const int (&idx)[K / 2],
                                                const double (&skipB)[K / 2], const int (&lpos)[K / 2], bool core,
-                                               int lane, const double *arow, float *psort, int Lp, float *bpart_w) {
+                                               int lane, const int *arow, float *psort, int Lp, float *bpart_w) {
     YRow<K> y;
     load_y<K, CP>(y, yt, nrow - 1, blank, idx);
 #pragma unroll
@@ -706,11 +747,8 @@ __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double p
         if (FULL || r >= 0) {
             YRow<K> yn;
             load_y<K, CP>(yn, yt, max(r - 1, 0), blank, idx);
-            const double *ar = arow + (size_t)r * 32 * K;
-            double2 av[K / 2];
-#pragma unroll
-            for (int h = 0; h < K / 2; ++h)
-                av[h] = *reinterpret_cast<const double2 *>(ar + ((size_t)h * 32 + lane) * 2);
+            double av[K];
+            fetch_row<K>(arow + r * 32 * K, lane, av);
             const double n1 = pr0 * f, n2 = pr1 * f;
             double b0, b1, s0, s1v;
             beta_bottom<K>(c.a, y, skipB, b0, b1, s0, s1v);
@@ -722,8 +760,8 @@ __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double p
             double bsum = 0.0;
 #pragma unroll
             for (int h = 0; h < K / 2; ++h) {
-                bsum = fma(av[h].x, bb[2 * h], bsum);
-                const double pl = av[h].y * bb[2 * h + 1] * g;
+                bsum = fma(av[2 * h], bb[2 * h], bsum);
+                const double pl = av[2 * h + 1] * bb[2 * h + 1] * g;
                 if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
             }
             bpart_w[r * Lp + lane] = core ? (float)(bsum * g) : 0.f;
@@ -755,7 +793,7 @@ __device__ __forceinline__ void grad_group_mitm(Cells<K> &ca, double pa, double 
                                                 double pb1, double fb, double g, const unsigned *yt, int blank,
                                                 const int (&idx)[K / 2], const double (&skipA)[K / 2],
                                                 const double (&skipB)[K / 2], const int (&lpos)[K / 2], bool core,
-                                                int lane, double *rows, float *psort, int Lp, float *bpart_w) {
+                                                int lane, int *rows, float *psort, int Lp, float *bpart_w) {
     constexpr int H = kGroup / 2;
     YRow<K> ya, yb;
     load_y<K, CP>(ya, yt, 0, blank, idx);
@@ -768,14 +806,8 @@ __device__ __forceinline__ void grad_group_mitm(Cells<K> &ca, double pa, double 
         load_y<K, CP>(ybn, yt, max(rb - 1, 0), blank, idx);
         double stored_b[K], stored_a[K];
         if (j >= H) {  // second half: fetch the other chain's stored row early
-            const double *sb = rows + (size_t)ra * 32 * K, *sa = rows + (size_t)rb * 32 * K;
-#pragma unroll
-            for (int h = 0; h < K / 2; ++h) {
-                const double2 vb = *reinterpret_cast<const double2 *>(sb + ((size_t)h * 32 + lane) * 2);
-                const double2 va = *reinterpret_cast<const double2 *>(sa + ((size_t)h * 32 + lane) * 2);
-                stored_b[2 * h] = vb.x; stored_b[2 * h + 1] = vb.y;
-                stored_a[2 * h] = va.x; stored_a[2 * h + 1] = va.y;
-            }
+            fetch_row<K>(rows + ra * 32 * K, lane, stored_b);
+            fetch_row<K>(rows + rb * 32 * K, lane, stored_a);
         }
         // ---- alpha step (row ra)
         const double p1 = pa * fa;
@@ -793,12 +825,8 @@ __device__ __forceinline__ void grad_group_mitm(Cells<K> &ca, double pa, double 
         double bb[K];
         beta_rest<K>(cb.a, bb, b0, b1, s0, s1v, n1, n2, yb, skipB);
         if (j < H) {
-            double *da = rows + (size_t)ra * 32 * K, *db = rows + (size_t)rb * 32 * K;
-#pragma unroll
-            for (int h = 0; h < K / 2; ++h) {
-                *reinterpret_cast<double2 *>(da + ((size_t)h * 32 + lane) * 2) = make_double2(ca.a[2 * h], ca.a[2 * h + 1]);
-                *reinterpret_cast<double2 *>(db + ((size_t)h * 32 + lane) * 2) = make_double2(bb[2 * h], bb[2 * h + 1]);
-            }
+            park_row<K>(rows + ra * 32 * K, lane, ca.a);
+            park_row<K>(rows + rb * 32 * K, lane, bb);
         } else {
             posterior_row<K>(ca.a, stored_b, g, lpos, core, psort + ra * Lp, bpart_w + ra * Lp + lane);
             posterior_row<K>(stored_a, bb, g, lpos, core, psort + rb * Lp, bpart_w + rb * Lp + lane);
@@ -837,7 +865,7 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
     int *cu = reinterpret_cast<int *>(smem + lay.cu);
     float *psort = reinterpret_cast<float *>(smem + lay.psort);
     float *partial = reinterpret_cast<float *>(smem + lay.partial);
-    double *arow = reinterpret_cast<double *>(smem + lay.arow) + (size_t)q * R * 32 * K;
+    int *arow = reinterpret_cast<int *>(smem + lay.arow) + (size_t)q * R * 32 * K;
     const int Lp = lay.pitch;                    // pitch of a posterior row
     const int Lb = p.Lmax > 0 ? p.Lmax : 1;      // where the blank partial sums start inside a row
     float *bpart = psort + Lb;                   // [row * Lp + warp * 32 + lane]

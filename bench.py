@@ -92,7 +92,8 @@ def cpu_port(d, steps=3, warmup=1, threads=0):
     """Time the oracle's fp32 OpenMP port on the host cores over the given batch; returns (frames/s, cores)."""
     from oracle import ctc_oracle
     a, lab, al, ll = d["acts"].numpy(), d["labels"].numpy(), d["act_lens"].numpy(), d["label_lens"].numpy()
-    cores = threads or ctc_oracle.max_threads()
+    # all the host cores this process may run on (torchrun exports OMP_NUM_THREADS=1: do not let that shrink the arm)
+    cores = threads or max(len(os.sched_getaffinity(0)), ctc_oracle.max_threads())
     for _ in range(warmup):
         ctc_oracle.compute(a, lab, al, ll, precision="f32", num_threads=cores)
     best = float("inf")
@@ -104,6 +105,16 @@ def cpu_port(d, steps=3, warmup=1, threads=0):
         best = min(best, ts[-1])
     frames = d["T"] * d["B"]
     return frames / best, cores, sum(ts) / len(ts)
+
+
+def load_traffic(kernel, workload):
+    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture of this workload (or None)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return t["bytes"][kernel] if t.get("workload") == workload else None
+    except (OSError, KeyError, ValueError):
+        return None
 
 
 def run_reference(args, w):
@@ -251,8 +262,8 @@ def run_b200(args, w):
         achieved = dom[1] / (dom[2] * 1e-3) / 1e9
         step_gbs = 8 * C * frames / (ms_per_step * 1e-3) / 1e9
         cpu = None
-        if world == 1 or True:
-            d0 = d if rank == 0 else None
+        if world == 1:  # reported at N=1 only
+            d0 = d
             fps_cpu, cores, mean_s = cpu_port(d0, steps=3, warmup=1)
             cpu = {"value": fps_cpu, "unit": UNIT, "cores": cores, "kind": "port",
                    "sample": f"oracle fp32 OpenMP port, full batch B={B} T={T} C={C}, best of 3 ({mean_s:.2f} s each)"}
@@ -263,7 +274,7 @@ def run_b200(args, w):
                            "valid_frames": int(d["act_lens"].sum()), "l2": "flushed (256 MB memset) between timed steps",
                            "lengths": "device-resident (no host sync in the step)"},
                 "roofline": {"bound": "hbm", "kernel": dom[0], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "peak_kind": peak_kind, "traffic": None,
+                             "frac": achieved / peak, "peak_kind": peak_kind, "traffic": load_traffic(dom[0], w.name),
                              "alg_bytes_per_launch": dom[1], "kernel_ms": dom[2],
                              "prep_kernel_ms": prep_ms, "engine_kernel_ms": eng_ms, "grad_kernel_ms": grad_ms,
                              "step_alg_gbs": step_gbs, "step_frac": step_gbs / peak,

@@ -71,7 +71,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         // the headline shape: 10 CTAs/utterance 154 us, 19: 141, 32: 139, 63: 141)
         const int resident = (int)(kSmemLimit / pl->smem_grad) > 0 ? (int)(kSmemLimit / pl->smem_grad) : 1;
         int ns = (7 * 148 * resident + B - 1) / B;
-        if (ns > pl->nblk) ns = pl->nblk;
+        if (ns > pl->nblk / 4) ns = pl->nblk / 4;  // >= 4 groups per CTA: amortise its set-up
         if (ns < 1) ns = 1;
         pl->nsplit = ns;
     }
@@ -334,10 +334,20 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
 }
 
 // ------------------------------------------------------------------------------------------------ host-buffer path
+// The batch is cut into up to kHostChunks slices of utterances, each with its own stream, compact device buffers and
+// workspace: the host->device copy of slice k+1, the kernels of slice k and the device->host copy of slice k-1
+// overlap (the kernels are bound by the T-step recursion, not by the SM count, so slices also run side by side).
+constexpr int kHostChunks = 4;
+constexpr int kHostMinChunk = 8;  // utterances per slice below which slicing stops paying
+
 struct ctcB200Context {
     float *d_acts = nullptr, *d_grads = nullptr, *d_costs = nullptr;
     void *d_ws = nullptr;
-    size_t n_acts = 0, n_costs = 0, n_ws = 0;
+    size_t n_acts = 0, n_grads = 0, n_costs = 0, n_ws = 0;
+    cudaStream_t side[kHostChunks] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t done[kHostChunks] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t start = nullptr;
+    bool streams_ok = false;
 };
 
 static bool grow(void **ptr, size_t *have, size_t need) {
@@ -347,6 +357,17 @@ static bool grow(void **ptr, size_t *have, size_t need) {
     *have = 0;
     if (cudaMalloc(ptr, need) != cudaSuccess) return false;
     *have = need;
+    return true;
+}
+
+static bool make_streams(ctcB200Context *c) {
+    if (c->streams_ok) return true;
+    if (cudaEventCreateWithFlags(&c->start, cudaEventDisableTiming) != cudaSuccess) return false;
+    for (int k = 0; k < kHostChunks; ++k) {
+        if (cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking) != cudaSuccess) return false;
+        if (cudaEventCreateWithFlags(&c->done[k], cudaEventDisableTiming) != cudaSuccess) return false;
+    }
+    c->streams_ok = true;
     return true;
 }
 
@@ -362,6 +383,11 @@ extern "C" ctcB200Status ctc_b200_destroy(ctcB200Context *c) {
     cudaFree(c->d_grads);
     cudaFree(c->d_costs);
     cudaFree(c->d_ws);
+    for (int k = 0; k < kHostChunks; ++k) {
+        if (c->side[k]) cudaStreamDestroy(c->side[k]);
+        if (c->done[k]) cudaEventDestroy(c->done[k]);
+    }
+    if (c->start) cudaEventDestroy(c->start);
     delete c;
     return CTC_B200_STATUS_SUCCESS;
 }
@@ -371,40 +397,86 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
                                                int B, int C, float *costs_host, double *loss_sum,
                                                const ctcB200Options *opts_in) {
     if (!c || !acts_host || !costs_host || !label_lens || !act_lens) return CTC_B200_STATUS_INVALID_VALUE;
+    if (B < 1 || T < 0 || C < 2) return CTC_B200_STATUS_INVALID_VALUE;
     ctcB200Options o;
     if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
     if (o.lengths_on_device) return CTC_B200_STATUS_INVALID_VALUE;
-    int mx = 0;
-    for (int b = 0; b < B; ++b) mx = label_lens[b] > mx ? label_lens[b] : mx;
-    size_t wsb = 0;
-    ctcB200Status s = ctc_b200_workspace_size(T, B, C, mx, &o, &wsb);
-    if (s != CTC_B200_STATUS_SUCCESS) return s;
-    const size_t nel = (size_t)T * B * C;
-    size_t n_grads = c->n_acts;
-    void *pa = c->d_acts, *pg = c->d_grads, *pc = c->d_costs;
-    size_t ha = c->n_acts, hc = c->n_costs;
-    if (!grow(&pa, &ha, nel * sizeof(float))) return CTC_B200_STATUS_MEMOPS_FAILED;
-    c->d_acts = (float *)pa; c->n_acts = ha;
-    if (grads_host) {
-        size_t hg = c->d_grads ? n_grads : 0;
-        if (!grow(&pg, &hg, nel * sizeof(float))) return CTC_B200_STATUS_MEMOPS_FAILED;
-        c->d_grads = (float *)pg;
+    for (int b = 0; b < B; ++b)
+        if (label_lens[b] < 0) return CTC_B200_STATUS_INVALID_VALUE;
+
+    // ---- slices of utterances [b0, b0 + nb)
+    int nch = B / kHostMinChunk;
+    nch = nch < 1 ? 1 : (nch > kHostChunks ? kHostChunks : nch);
+    int b0s[kHostChunks + 1];
+    size_t ws_off[kHostChunks + 1], lab_off[kHostChunks + 1];
+    b0s[0] = 0; ws_off[0] = 0; lab_off[0] = 0;
+    for (int k = 0; k < nch; ++k) {
+        const int nb = B / nch + (k < B % nch ? 1 : 0);
+        b0s[k + 1] = b0s[k] + nb;
+        int mx = 0;
+        size_t nl = 0;
+        for (int b = b0s[k]; b < b0s[k + 1]; ++b) {
+            mx = label_lens[b] > mx ? label_lens[b] : mx;
+            nl += (size_t)label_lens[b];
+        }
+        lab_off[k + 1] = lab_off[k] + nl;
+        size_t wsb = 0;
+        ctcB200Status s = ctc_b200_workspace_size(T, nb, C, mx, &o, &wsb);
+        if (s != CTC_B200_STATUS_SUCCESS) return s;
+        ws_off[k + 1] = ws_off[k] + align256(wsb);
     }
-    if (!grow(&pc, &hc, sizeof(float) * B)) return CTC_B200_STATUS_MEMOPS_FAILED;
-    c->d_costs = (float *)pc; c->n_costs = hc;
-    if (!grow(&c->d_ws, &c->n_ws, wsb)) return CTC_B200_STATUS_MEMOPS_FAILED;
-    cudaStream_t st = (cudaStream_t)o.stream;
-    if (cudaMemcpyAsync(c->d_acts, acts_host, nel * sizeof(float), cudaMemcpyHostToDevice, st) != cudaSuccess)
-        return CTC_B200_STATUS_MEMOPS_FAILED;
-    s = ctc_b200_compute(c->d_acts, grads_host ? c->d_grads : nullptr, labels, label_lens, act_lens, T, B, C,
-                         c->d_costs, c->d_ws, c->n_ws, &o);
-    if (s != CTC_B200_STATUS_SUCCESS) return s;
-    if (grads_host &&
-        cudaMemcpyAsync(grads_host, c->d_grads, nel * sizeof(float), cudaMemcpyDeviceToHost, st) != cudaSuccess)
-        return CTC_B200_STATUS_MEMOPS_FAILED;
-    if (cudaMemcpyAsync(costs_host, c->d_costs, sizeof(float) * B, cudaMemcpyDeviceToHost, st) != cudaSuccess)
-        return CTC_B200_STATUS_MEMOPS_FAILED;
-    if (cudaStreamSynchronize(st) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+    const size_t nel = (size_t)T * B * C;
+    {
+        void *pa = c->d_acts, *pg = c->d_grads, *pc = c->d_costs;
+        if (!grow(&pa, &c->n_acts, nel * sizeof(float))) { c->d_acts = nullptr; return CTC_B200_STATUS_MEMOPS_FAILED; }
+        c->d_acts = (float *)pa;
+        if (grads_host) {
+            if (!grow(&pg, &c->n_grads, nel * sizeof(float))) { c->d_grads = nullptr; return CTC_B200_STATUS_MEMOPS_FAILED; }
+            c->d_grads = (float *)pg;
+        }
+        if (!grow(&pc, &c->n_costs, sizeof(float) * B)) { c->d_costs = nullptr; return CTC_B200_STATUS_MEMOPS_FAILED; }
+        c->d_costs = (float *)pc;
+        if (!grow(&c->d_ws, &c->n_ws, ws_off[nch])) return CTC_B200_STATUS_MEMOPS_FAILED;
+    }
+    cudaStream_t user = (cudaStream_t)o.stream;
+    if (nch > 1) {
+        if (!make_streams(c)) return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (cudaEventRecord(c->start, user) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+    }
+    int launches = 0;
+    const size_t host_pitch = (size_t)B * C * sizeof(float);
+    for (int k = 0; k < nch; ++k) {
+        const int b0 = b0s[k], nb = b0s[k + 1] - b0;
+        cudaStream_t st = nch > 1 ? c->side[k] : user;
+        if (nch > 1 && cudaStreamWaitEvent(st, c->start, 0) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+        // compact device copies [T][nb][C] of this slice (rows of the host tensor are B*C floats apart)
+        float *da = c->d_acts + (size_t)T * b0 * C;
+        float *dg = grads_host ? c->d_grads + (size_t)T * b0 * C : nullptr;
+        const size_t width = (size_t)nb * C * sizeof(float);
+        if (T > 0 && cudaMemcpy2DAsync(da, width, acts_host + (size_t)b0 * C, host_pitch, width, (size_t)T,
+                                       cudaMemcpyHostToDevice, st) != cudaSuccess)
+            return CTC_B200_STATUS_MEMOPS_FAILED;
+        ctcB200Options ok = o;
+        ok.stream = (void *)st;
+        ctcB200Status s = ctc_b200_compute(da, dg, labels ? labels + lab_off[k] : nullptr, label_lens + b0,
+                                           act_lens + b0, T, nb, C, c->d_costs + b0,
+                                           static_cast<unsigned char *>(c->d_ws) + ws_off[k],
+                                           ws_off[k + 1] - ws_off[k], &ok);
+        if (s != CTC_B200_STATUS_SUCCESS) return s;
+        launches += g_last_launches;
+        if (dg && T > 0 && cudaMemcpy2DAsync(grads_host + (size_t)b0 * C, host_pitch, dg, width, width, (size_t)T,
+                                             cudaMemcpyDeviceToHost, st) != cudaSuccess)
+            return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (cudaMemcpyAsync(costs_host + b0, c->d_costs + b0, sizeof(float) * nb, cudaMemcpyDeviceToHost, st) !=
+            cudaSuccess)
+            return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (nch > 1) {
+            if (cudaEventRecord(c->done[k], st) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+            if (cudaStreamWaitEvent(user, c->done[k], 0) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+        }
+    }
+    g_last_launches = launches;
+    if (cudaStreamSynchronize(user) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
     if (loss_sum) {
         double acc = 0.0;
         for (int b = 0; b < B; ++b) acc += (double)costs_host[b];

@@ -286,18 +286,20 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     }
 }
 
-// Decode one entry of the prep kernels' label table.
+// Decode one entry of the prep kernels' label table (4 labels = 8 lattice states per entry).  K = 8: the whole
+// entry; K = 4: labels 2*half .. 2*half+1 of it.
 template <int K>
 __device__ __forceinline__ void decode_tlab(const uint4 tl, int (&idx)[K / 2], double (&skipA)[K / 2],
-                                            double (&skipB)[K / 2], int (&lpos)[K / 2], bool want_lpos) {
-    static_assert(K == 8, "label table is laid out for K = 8");
+                                            double (&skipB)[K / 2], int (&lpos)[K / 2], bool want_lpos, int half = 0) {
+    static_assert(K == 8 || K == 4, "label table entries hold 4 labels");
 #pragma unroll
-    for (int h = 0; h < K / 2; ++h) {
-        idx[h] = (tl.x >> (8 * h)) & 0xff;
-        skipA[h] = ((tl.y >> h) & 1) ? 1.0 : 0.0;
-        skipB[h] = ((tl.y >> (4 + h)) & 1) ? 1.0 : 0.0;
+    for (int hh = 0; hh < K / 2; ++hh) {
+        const int h = (K == 8) ? hh : 2 * half + hh;
+        idx[hh] = (tl.x >> (8 * h)) & 0xff;
+        skipA[hh] = ((tl.y >> h) & 1) ? 1.0 : 0.0;
+        skipB[hh] = ((tl.y >> (4 + h)) & 1) ? 1.0 : 0.0;
         const unsigned lw = (h < 2) ? tl.z : tl.w;
-        lpos[h] = (want_lpos && ((tl.y >> (8 + h)) & 1)) ? (int)((lw >> (16 * (h & 1))) & 0xffff) : -1;
+        lpos[hh] = (want_lpos && ((tl.y >> (8 + h)) & 1)) ? (int)((lw >> (16 * (h & 1))) & 0xffff) : -1;
     }
 }
 
@@ -532,7 +534,8 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
     const int thread = warp * 32 + lane;  // lattice thread index; owns states [thread*K, thread*K+K)
     int idx[K / 2], lab_i[K / 2];
     double skipA[K / 2], skipB[K / 2];
-    decode_tlab<K>(p.tlab[(size_t)b * NT + thread], idx, skipA, skipB, lab_i, false);
+    decode_tlab<K>(p.tlab[(size_t)b * NT + (K == 8 ? thread : (thread >> 1))], idx, skipA, skipB, lab_i, false,
+                   thread & 1);
     (void)lab_i;
     (void)C;
 

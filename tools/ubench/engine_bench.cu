@@ -56,7 +56,9 @@ int main(int argc, char **argv) {
     { int resident = (int)(227 * 1024 / s_grad); if (resident < 1) resident = 1; p.nsplit = (2 * 148 * resident + B - 1) / B; if (p.nsplit > p.nblk) p.nsplit = p.nblk; if (argc > 5) p.nsplit = atoi(argv[5]); }
     CK(cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     CK(cudaFuncSetAttribute(ctc_engine_kernel<kK, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+#if KK == 8
     CK(cudaFuncSetAttribute(ctc_grad_kernel<kK, 32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+#endif
     if (s_eng < eng_pad) s_eng = eng_pad;
     printf("nqmax %d nsplit %d\n", p.nqmax, p.nsplit);
     printf("B=%d T=%d C=%d Lmax=%d nwl=%d R=%d smem prep %zu engine %zu grad %zu\n", B, T, C, Lmax, p.nwl, R, s_prep, s_eng, s_grad);
@@ -71,7 +73,9 @@ int main(int argc, char **argv) {
         ctc_engine_kernel<kK, 32><<<2 * B, (p.nwl + 1) * 32, s_eng>>>(p);
         cudaEventRecord(e[2]);
         if (getenv("SCORE_ONLY")) { CtcParams q = p; q.score_only = 1; cudaEventRecord(e[1]); ctc_engine_kernel<kK, 32><<<B, (p.nwl + 1) * 32, s_eng>>>(q); cudaEventRecord(e[2]); }
+#if KK == 8
         ctc_grad_kernel<kK, 32, false><<<dim3(p.nsplit, B), p.nqmax * 32, s_grad>>>(p);
+#endif
         cudaEventRecord(e[3]);
         CK(cudaDeviceSynchronize());
         for (int k = 0; k < 3; ++k) { float ms; cudaEventElapsedTime(&ms, e[k], e[k + 1]); best[k] = std::min(best[k], ms); }

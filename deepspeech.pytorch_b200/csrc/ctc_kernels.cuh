@@ -664,7 +664,7 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
 constexpr int kMaxGradWarps = 10;  // ceil((2*1023+1) / 224)
 
 struct GradSmem {
-    size_t ytile, bar, units, cu, psort, partial, arow, total;
+    size_t ytile, bar, units, cu, psort, arow, total;
     int pitch, numax;
 };
 __host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, int K, bool big) {
@@ -677,7 +677,6 @@ __host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, i
     s.units = o; o = align16(o + sizeof(unsigned) * s.numax);
     s.cu = o;    o = align16(o + sizeof(int) * (big ? 0 : C + 1));
     s.psort = o; o = align16(o + sizeof(float) * kGroup * s.pitch);
-    s.partial = o; o = align16(o + sizeof(float) * kGroup * s.numax);
     s.arow = o;  o = align16(o + sizeof(int) * (size_t)nq * kGroup * 32 * K);
     s.total = o;
     return s;
@@ -773,74 +772,15 @@ __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double p
     }
 }
 
-// Full group (8 rows), "meet in the middle": the alpha chain (rows 0..3, then 4..7) and the beta chain (rows 7..4,
-// then 3..0) are independent until they cross, so they are interleaved step by step in ONE instruction stream -- twice
-// the instruction-level parallelism, half as many dependent steps.  First half: both store their rows (alpha rows
-// 0-3, betabar rows 4-7, same thread-private shared-memory slots).  Second half: each meets the other's stored rows
-// and forms the posteriors.
-template <int K>
-__device__ __forceinline__ void posterior_row(const double (&al)[K], const double (&bb)[K], double g,
-                                              const int (&lpos)[K / 2], bool core, float *psort_r, float *bpart_r) {
-    double bsum = 0.0;
-#pragma unroll
-    for (int h = 0; h < K / 2; ++h) {
-        bsum = fma(al[2 * h], bb[2 * h], bsum);
-        const double pl = al[2 * h + 1] * bb[2 * h + 1] * g;
-        if (lpos[h] >= 0) psort_r[lpos[h]] = (float)pl;
-    }
-    *bpart_r = core ? (float)(bsum * g) : 0.f;
-}
-
-template <int K, int CP>
-__device__ __forceinline__ void grad_group_mitm(Cells<K> &ca, double pa, double fa, Cells<K> &cb, double pb0,
-                                                double pb1, double fb, double g, const unsigned *yt, int blank,
-                                                const int (&idx)[K / 2], const double (&skipA)[K / 2],
-                                                const double (&skipB)[K / 2], const int (&lpos)[K / 2], bool core,
-                                                int lane, int *rows, float *psort, int Lp, float *bpart_w) {
-    constexpr int H = kGroup / 2;
-    YRow<K> ya, yb;
-    load_y<K, CP>(ya, yt, 0, blank, idx);
-    load_y<K, CP>(yb, yt, kGroup - 1, blank, idx);
-#pragma unroll
-    for (int j = 0; j < kGroup; ++j) {
-        const int ra = j, rb = kGroup - 1 - j;  // alpha row, beta row of this iteration
-        YRow<K> yan, ybn;
-        load_y<K, CP>(yan, yt, min(ra + 1, kGroup - 1), blank, idx);
-        load_y<K, CP>(ybn, yt, max(rb - 1, 0), blank, idx);
-        double stored_b[K], stored_a[K];
-        if (j >= H) {  // second half: fetch the other chain's stored row early
-            fetch_row<K>(rows + ra * 32 * K, lane, stored_b);
-            fetch_row<K>(rows + rb * 32 * K, lane, stored_a);
-        }
-        // ---- alpha step (row ra)
-        const double p1 = pa * fa;
-        const double top = alpha_top<K>(ca.a, ya, skipA);
-        pa = __shfl_up_sync(kFull, top, 1);
-        if (lane == 0) pa = 0.0;
-        // ---- beta step (row rb)
-        const double n1 = pb0 * fb, n2 = pb1 * fb;
-        double b0, b1, s0, s1v;
-        beta_bottom<K>(cb.a, yb, skipB, b0, b1, s0, s1v);
-        pb0 = __shfl_down_sync(kFull, s0, 1);
-        pb1 = __shfl_down_sync(kFull, s1v, 1);
-        if (lane == 31) { pb0 = 0.0; pb1 = 0.0; }
-        alpha_rest<K>(ca.a, top, p1, ya, skipA);
-        double bb[K];
-        beta_rest<K>(cb.a, bb, b0, b1, s0, s1v, n1, n2, yb, skipB);
-        if (j < H) {
-            park_row<K>(rows + ra * 32 * K, lane, ca.a);
-            park_row<K>(rows + rb * 32 * K, lane, bb);
-        } else {
-            posterior_row<K>(ca.a, stored_b, g, lpos, core, psort + ra * Lp, bpart_w + ra * Lp + lane);
-            posterior_row<K>(stored_a, bb, g, lpos, core, psort + rb * Lp, bpart_w + rb * Lp + lane);
-        }
-        ya = yan;
-        yb = ybn;
-    }
-}
-
+// 128 registers x 128 threads and ~56 KB of shared memory per CTA on the headline shape: 4 CTAs (16 warps) per SM.
+// The kernel is latency-bound per warp, so residency is what buys throughput (measured: 2 CTAs/SM 172 us, 3: 123 us,
+// 4: 103 us); an interleaved alpha/beta "meet in the middle" variant needed 168 registers and lost to this one.
+#ifndef CTC_GRAD_MAXREG
+#define CTC_GRAD_MAXREG 128
+#endif
+#define CTC_GRAD_ATTR __maxnreg__(CTC_GRAD_MAXREG)
 template <int K, int CP, bool BIG>
-__global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcParams p) {
+__global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
     static_assert(K == 8, "the label table and the 224-state chunking are laid out for K = 8");
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int R = kGroup, Cp = CP;
@@ -867,7 +807,6 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
     unsigned *units = reinterpret_cast<unsigned *>(smem + lay.units);
     int *cu = reinterpret_cast<int *>(smem + lay.cu);
     float *psort = reinterpret_cast<float *>(smem + lay.psort);
-    float *partial = reinterpret_cast<float *>(smem + lay.partial);
     int *arow = reinterpret_cast<int *>(smem + lay.arow) + (size_t)q * R * 32 * K;
     const int Lp = lay.pitch;                    // pitch of a posterior row
     const int Lb = p.Lmax > 0 ? p.Lmax : 1;      // where the blank partial sums start inside a row
@@ -992,8 +931,10 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
         mbar_wait(&ybar[cur], (it >> 1) & 1);
         PROF(long long h2 = prof_clk(); long long h3 = h2;)
         if (nrow == R) {
-            grad_group_mitm<K, CP>(c, pa, fa, cbeta, pb0, pb1, fb, g, yt, p.bpos, idx, skipA, skipB, lpos, core, lane,
-                                   arow, psort, Lp, bpart_w);
+            grad_alpha_rows<K, CP, true>(c, pa, fa, yt, nrow, p.bpos, idx, skipA, lane, arow);
+            PROF(h3 = prof_clk();)
+            grad_beta_rows<K, CP, true>(cbeta, pb0, pb1, fb, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
+                                        psort, Lp, bpart_w);
         } else {
             grad_alpha_rows<K, CP, false>(c, pa, fa, yt, nrow, p.bpos, idx, skipA, lane, arow);
             PROF(h3 = prof_clk();)
@@ -1018,32 +959,35 @@ __global__ void __launch_bounds__(kMaxGradWarps * 32) ctc_grad_kernel(const CtcP
             }
         } else {
             // lane = (task slot lane>>3, row lane&7).  Phase A: one task per (unit, row) sums <= 8 adjacent posteriors
-            // (rows sit 1 bank apart, consecutive units 8 banks apart: conflict-free); phase B: one task per
-            // (class, row) adds the class's unit sums in a fixed order and writes the gradient.
+            // (rows sit 1 bank apart, consecutive units 8 banks apart: conflict-free) and leaves the sum in the
+            // unit's first slot; phase B: one task per (class, row) adds the class's unit sums in a fixed order and
+            // writes the gradient.
             const float scale = p.grad_scale;
             const int r = lane & 7, slot = q * 4 + (lane >> 3);
+            float *prow = psort + r * Lp;
             for (int u = slot; u < NU; u += 4 * nq) {
                 const unsigned un = units[u];
-                const float *ps = psort + r * Lp + (un & 0xffffu);
+                float *ps = prow + (un & 0xffffu);
                 const int len = (int)(un >> 16);
                 float v[kUnit];
 #pragma unroll
                 for (int i = 0; i < kUnit; ++i) v[i] = (i < len) ? ps[i] : 0.f;
-                partial[u * kGroup + r] = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+                ps[0] = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
             }
             named_bar_sync(2, nbar);
             for (int cc = slot; cc < C; cc += 4 * nq) {
-                const float *pp = partial + r;
-                int u0 = cu[cc];
-                const int u1 = cu[cc + 1];
+                const int u0 = cu[cc], n = cu[cc + 1] - u0;
+                // the units of a class are consecutive pieces of its segment: unit k starts at s0 + 8k
+                const float *pu = prow + (n > 0 ? (units[u0] & 0xffffu) : 0u);
                 float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
-                for (; u0 + 3 < u1; u0 += 4) {
-                    o0 += pp[u0 * kGroup];
-                    o1 += pp[(u0 + 1) * kGroup];
-                    o2 += pp[(u0 + 2) * kGroup];
-                    o3 += pp[(u0 + 3) * kGroup];
+                int k = 0;
+                for (; k + 3 < n; k += 4) {
+                    o0 += pu[kUnit * k];
+                    o1 += pu[kUnit * (k + 1)];
+                    o2 += pu[kUnit * (k + 2)];
+                    o3 += pu[kUnit * (k + 3)];
                 }
-                for (; u0 < u1; ++u0) o0 += pp[u0 * kGroup];
+                for (; k < n; ++k) o0 += pu[kUnit * k];
                 if (r < nrow)
                     p.grads[((size_t)(t0 + r) * p.B + b) * C + cc] =
                         scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) - ((o0 + o1) + (o2 + o3)));

@@ -3,9 +3,11 @@
 // get_warpctc_version reached from /root/reference/train.py:12,904,600,352,457 through warpctc_pytorch).
 //
 // Host side only plans the launch (shape -> lattice warps, rows per checkpoint block, shared memory, workspace
-// carving) and enqueues; it never synchronises the device and keeps no state besides a per-device
-// "max dynamic smem attribute already set" cache.
+// carving, length-bucket slices) and enqueues; it never synchronises the device.  State kept per device: a
+// "max dynamic smem attribute already set" cache and a small pool of internal side streams + events on which the
+// per-slice kernels are forked from and joined back to the caller's stream.
 #include <cuda_runtime.h>
+#include <mutex>
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -23,6 +25,35 @@ constexpr int kK = 8;               // states per lattice thread
 constexpr size_t kSmemLimit = 227 * 1024;
 thread_local int g_last_launches = 0;
 
+// ---- length-bucket slices (see sort_by_length in ctc_kernels.cuh)
+constexpr int kMaxSlices = 8;
+constexpr int kMinSliceB = 8;  // utterances per slice below which slicing stops paying
+struct SidePool {
+    bool ok = false;
+    cudaStream_t side[kMaxSlices];
+    cudaEvent_t fork, join[kMaxSlices];
+};
+SidePool g_pool[64];
+std::mutex g_pool_mu;  // held while a sliced launch is being enqueued: the pool's events are shared by all callers
+
+SidePool *side_pool(int dev) {
+    if (dev < 0 || dev >= 64) return nullptr;
+    SidePool &sp = g_pool[dev];
+    if (sp.ok) return &sp;
+    if (cudaEventCreateWithFlags(&sp.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    for (int k = 0; k < kMaxSlices; ++k) {
+        if (cudaStreamCreateWithFlags(&sp.side[k], cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&sp.join[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    }
+    sp.ok = true;
+    return &sp;
+}
+
+int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
 struct Plan {
     int nwl;   // lattice warps per CTA
     int R;     // rows per checkpoint block (16 or 8)
@@ -35,7 +66,9 @@ struct Plan {
     int nqmax;   // grad kernel warps per CTA
     int nsplit;  // grad kernel CTAs per utterance
     int big;     // large-alphabet path (C > kMaxSmallC)
-    size_t o_rowstat, o_occpos, o_order, o_units, o_cu;
+    size_t o_rowstat, o_occpos, o_order, o_units, o_cu, o_bord;
+    int nslices;           // length-bucket slices the engine / grad launches are cut into (1 = unsliced)
+    size_t smem_engine_req;  // dynamic shared memory REQUESTED for an engine CTA (>= smem_engine, see make_plan)
     int numax;   // reduction units per utterance (small alphabets)
     size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_tlab, o_coff, o_labels, o_llen, o_alen;
     size_t total;
@@ -76,6 +109,21 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         pl->nsplit = ns;
     }
     if (pl->smem_engine > kSmemLimit || pl->smem_prep > kSmemLimit) return false;
+    {
+        // Length-bucket slices: up to kMaxSlices, each at least kMinSliceB utterances.  CTC_B200_SLICES overrides.
+        int ns = B / kMinSliceB;
+        ns = ns < 1 ? 1 : (ns > kMaxSlices ? kMaxSlices : ns);
+        ns = env_int("CTC_B200_SLICES", ns);
+        ns = ns < 1 ? 1 : (ns > kMaxSlices ? kMaxSlices : ns);
+        if (ns > B || B > kMaxSortB) ns = 1;
+        pl->nslices = ns;
+        if (ns > 1 && pl->smem_prep < sizeof(int) * (size_t)B) pl->smem_prep = sizeof(int) * (size_t)B;
+        // An engine CTA may REQUEST more shared memory than it uses so that fewer gradient CTAs of other slices fit
+        // beside it on its SM (they would steal issue slots and FP64 pipe from the latency-critical recursion).
+        size_t req = (size_t)env_int("CTC_B200_ENGINE_SMEM_KB", 0) * 1024;
+        if (req > kSmemLimit) req = kSmemLimit;
+        pl->smem_engine_req = req > pl->smem_engine ? req : pl->smem_engine;
+    }
     size_t o = 0;
     const size_t ck = sizeof(double) * (size_t)B * pl->nblk * NT * kK;
     const size_t ckE = sizeof(int) * (size_t)B * pl->nblk * NT;
@@ -96,11 +144,51 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->numax = pl->big ? 0 : grad_max_units(C, Lmax, pl->nqmax);
     pl->o_units = o;  o = align256(o + sizeof(unsigned) * (size_t)B * pl->numax);
     pl->o_cu = o;     if (!pl->big) o = align256(o + sizeof(int) * (size_t)B * (C + 1));
+    pl->o_bord = o;   o = align256(o + sizeof(int) * (size_t)B);
     pl->o_labels = o; o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
     pl->o_llen = o;   o = align256(o + sizeof(int) * B);
     pl->o_alen = o;   o = align256(o + sizeof(int) * B);
     pl->total = o;
     return true;
+}
+
+// Engine + gradient launches, cut into length-bucket slices on the pool's side streams (forked from and joined back
+// to the caller's stream with events, so the caller sees ordinary stream semantics and graph capture still works).
+// All engines are enqueued before any gradient kernel: the longest slice (rank 0..) starts first.
+template <typename EngineLaunch, typename GradLaunch>
+cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, bool do_engine, bool do_grad,
+                          EngineLaunch eng, GradLaunch grd) {
+    if (!do_engine && !do_grad) return cudaSuccess;
+    if (pl.nslices <= 1) {
+        if (do_engine) eng(p, p.B, st);
+        if (do_grad) grd(p, p.B, st);
+        return cudaGetLastError();
+    }
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    SidePool *sp = side_pool(dev);
+    if (!sp) return cudaErrorUnknown;
+    const int ns = pl.nslices;
+    if ((e = cudaEventRecord(sp->fork, st)) != cudaSuccess) return e;
+    for (int k = 0; k < ns; ++k)
+        if ((e = cudaStreamWaitEvent(sp->side[k], sp->fork, 0)) != cudaSuccess) return e;
+    for (int pass = 0; pass < 2; ++pass) {
+        if (pass == 0 ? !do_engine : !do_grad) continue;
+        for (int k = 0; k < ns; ++k) {
+            CtcParams pk = p;
+            pk.slice0 = (int)((long long)p.B * k / ns);
+            const int nb = (int)((long long)p.B * (k + 1) / ns) - pk.slice0;
+            if (pass == 0) eng(pk, nb, sp->side[k]); else grd(pk, nb, sp->side[k]);
+        }
+    }
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    for (int k = 0; k < ns; ++k) {
+        if ((e = cudaEventRecord(sp->join[k], sp->side[k])) != cudaSuccess) return e;
+        if ((e = cudaStreamWaitEvent(st, sp->join[k], 0)) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
 }
 
 template <int CP>
@@ -124,25 +212,23 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
     if (!(phase_mask & 4) && p.T > 0) {
         const long long rows = (long long)p.T * p.B;
         const int nrb = (int)((rows + kPrepRows - 1) / kPrepRows);
-        ctc_prep_kernel<<<nrb + p.B, kPrepRows, pl.smem_prep, st>>>(p);
+        ctc_prep_kernel<<<nrb + p.B + (pl.nslices > 1 ? 1 : 0), kPrepRows, pl.smem_prep, st>>>(p);
         ++*launches;
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
-    if (!(phase_mask & 1)) {
-        const int engine_ctas = p.score_only ? p.B : 2 * p.B;
-        ctc_engine_kernel<kK, CP><<<engine_ctas, (pl.nwl + 1) * 32, pl.smem_engine, st>>>(p);
-        ++*launches;
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-    }
-    if (!p.score_only && p.T > 0 && !(phase_mask & 2)) {
-        dim3 grid(pl.nsplit, p.B);
-        ctc_grad_kernel<kK, CP, false><<<grid, pl.nqmax * 32, pl.smem_grad, st>>>(p);
-        ++*launches;
-        e = cudaGetLastError();
-    }
-    return e;
+    const bool do_engine = !(phase_mask & 1);
+    const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
+    return launch_sliced(
+        p, pl, st, do_engine, do_grad,
+        [&](const CtcParams &pk, int nb, cudaStream_t s) {
+            ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+            ++*launches;
+        },
+        [&](const CtcParams &pk, int nb, cudaStream_t s) {
+            ctc_grad_kernel<kK, CP, false><<<dim3(pl.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pk);
+            ++*launches;
+        });
 }
 
 cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
@@ -165,24 +251,27 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
     cudaError_t e = cudaSuccess;
     const long long rows = (long long)p.T * p.B;
     if (!(phase_mask & 4) && p.T > 0) {
-        ctc_prep_utt_kernel<<<p.B, kPrepRows, pl.smem_prep, st>>>(p);
+        ctc_prep_utt_kernel<<<p.B + (pl.nslices > 1 ? 1 : 0), kPrepRows, pl.smem_prep, st>>>(p);
         ++*launches;
         ctc_prep_big_kernel<CP><<<(unsigned)rows, kBigThreads, 256, st>>>(p);
         ++*launches;
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
-    if (!(phase_mask & 1)) {
-        const int engine_ctas = p.score_only ? p.B : 2 * p.B;
-        ctc_engine_kernel<kK, CP><<<engine_ctas, (pl.nwl + 1) * 32, pl.smem_engine, st>>>(p);
-        ++*launches;
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-    }
-    if (!p.score_only && p.T > 0 && !(phase_mask & 2)) {
-        dim3 grid(pl.nsplit, p.B);
-        ctc_grad_kernel<kK, CP, true><<<grid, pl.nqmax * 32, pl.smem_grad, st>>>(p);
-        ++*launches;
+    const bool do_engine = !(phase_mask & 1);
+    const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
+    e = launch_sliced(
+        p, pl, st, do_engine, do_grad,
+        [&](const CtcParams &pk, int nb, cudaStream_t s) {
+            ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+            ++*launches;
+        },
+        [&](const CtcParams &pk, int nb, cudaStream_t s) {
+            ctc_grad_kernel<kK, CP, true><<<dim3(pl.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pk);
+            ++*launches;
+        });
+    if (e != cudaSuccess) return e;
+    if (do_grad) {
         ctc_final_big_kernel<CP><<<(unsigned)rows, kBigThreads, 0, st>>>(p);
         ++*launches;
         e = cudaGetLastError();
@@ -238,9 +327,9 @@ int ctc_b200_last_launch_count(void) { return g_last_launches; }
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------ compute
-extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const int *labels, const int *label_lens,
-                                          const int *act_lens, int T, int B, int C, float *costs, void *workspace,
-                                          size_t workspace_bytes, const ctcB200Options *opts_in) {
+static ctcB200Status compute_impl(const float *acts, float *grads, const int *labels, const int *label_lens,
+                                  const int *act_lens, int T, int B, int C, float *costs, void *workspace,
+                                  size_t workspace_bytes, const ctcB200Options *opts_in, bool allow_slices) {
     g_last_launches = 0;
     ctcB200Options o;
     if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
@@ -269,6 +358,7 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
     Plan pl;
     if (!make_plan(T, B, C, Lmax, &pl)) return CTC_B200_STATUS_INVALID_VALUE;
     if (workspace_bytes < pl.total) return CTC_B200_STATUS_INVALID_VALUE;
+    if (!allow_slices) pl.nslices = 1;  // the host-buffer path pipelines whole utterance slices itself
 
     unsigned char *ws = static_cast<unsigned char *>(workspace);
     CtcParams p;
@@ -326,11 +416,20 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
     p.units = reinterpret_cast<unsigned *>(ws + pl.o_units);
     p.cu = reinterpret_cast<int *>(ws + pl.o_cu);
     p.numax = pl.numax;
+    p.bord = pl.nslices > 1 ? reinterpret_cast<int *>(ws + pl.o_bord) : nullptr;
+    p.slice0 = 0;
 
     int launches = 0;
     cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches);
     g_last_launches = launches;
     return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
+}
+
+extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const int *labels, const int *label_lens,
+                                          const int *act_lens, int T, int B, int C, float *costs, void *workspace,
+                                          size_t workspace_bytes, const ctcB200Options *opts_in) {
+    return compute_impl(acts, grads, labels, label_lens, act_lens, T, B, C, costs, workspace, workspace_bytes, opts_in,
+                        true);
 }
 
 // ------------------------------------------------------------------------------------------------ host-buffer path
@@ -458,10 +557,9 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
             return CTC_B200_STATUS_MEMOPS_FAILED;
         ctcB200Options ok = o;
         ok.stream = (void *)st;
-        ctcB200Status s = ctc_b200_compute(da, dg, labels ? labels + lab_off[k] : nullptr, label_lens + b0,
-                                           act_lens + b0, T, nb, C, c->d_costs + b0,
-                                           static_cast<unsigned char *>(c->d_ws) + ws_off[k],
-                                           ws_off[k + 1] - ws_off[k], &ok);
+        ctcB200Status s = compute_impl(da, dg, labels ? labels + lab_off[k] : nullptr, label_lens + b0, act_lens + b0,
+                                       T, nb, C, c->d_costs + b0, static_cast<unsigned char *>(c->d_ws) + ws_off[k],
+                                       ws_off[k + 1] - ws_off[k], &ok, false);
         if (s != CTC_B200_STATUS_SUCCESS) return s;
         launches += g_last_launches;
         if (dg && T > 0 && cudaMemcpy2DAsync(grads_host + (size_t)b0 * C, host_pitch, dg, width, width, (size_t)T,

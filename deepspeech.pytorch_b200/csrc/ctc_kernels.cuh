@@ -59,6 +59,8 @@ struct CtcParams {
     float2 *rowstat;    // big: [T*B] (row max, 1/sum) of the softmax
     float *occpos;      // big: [B][T][Cp] occupancies by position (0: blank, 1+i: label i)
     int *order;         // big: [B][Lmax] label index at class-sorted position j
+    int *bord;          // [B] utterances ordered by decreasing act_len (length bucketing, see sort_by_length)
+    int slice0;         // engine / grad kernels: this launch covers bord[slice0 .. slice0 + gridDim) (bord == 0: b itself)
     int nsplit;         // grad kernel: time blocks are dealt round-robin to this many CTAs per utterance
     int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
 #ifdef CTC_PROFILE
@@ -101,7 +103,7 @@ constexpr int kPrepRows = 128;
 __host__ __device__ inline size_t prep_smem(int C, int Lmax) {
     const size_t rows = align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows;
     const size_t utt = sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1);  // class-sorted positions of one utterance
-    return (rows > utt ? rows : utt) + sizeof(int) * (C + 1) + 64;
+    return (rows > utt ? rows : utt) + sizeof(int) * (C + 1) + 64;  // >= 4 * kMaxSortB bytes is checked by the plan
 }
 
 // Class-sorted positions of the labels of one utterance (one warp): lpos[i] = rank of label i when labels are
@@ -215,6 +217,28 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
     }
 }
 
+// Length bucketing on the device (one CTA; lengths may live only on the device, so the host never sees them):
+// bord[rank] = utterance, ranked by decreasing number of frames (ties by index).  Rank by counting, O(B^2 / 128) per
+// thread with the lengths cached in shared memory -- a few microseconds for B <= 1024, hidden behind the softmax
+// blocks of the same launch.  The host then launches the recursion and gradient kernels per SLICE of ranks on side
+// streams: slices of short utterances finish their recursion early and their gradient work fills the SMs while
+// the long ones are still stepping through time.
+constexpr int kMaxSortB = 2048;
+__device__ __forceinline__ void sort_by_length(const CtcParams &p, int *keys) {
+    const int tid = threadIdx.x, B = p.B;
+    for (int i = tid; i < B; i += blockDim.x) keys[i] = min(max(p.act_lens[i], 0), p.T);
+    __syncthreads();
+    for (int i = tid; i < B; i += blockDim.x) {
+        const int ki = keys[i];
+        int rank = 0;
+        for (int j = 0; j < B; ++j) {
+            const int kj = keys[j];
+            rank += (kj > ki || (kj == ki && j < i)) ? 1 : 0;
+        }
+        p.bord[rank] = i;
+    }
+}
+
 __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -225,6 +249,10 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     const size_t utt_bytes = sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
     int *cnt = reinterpret_cast<int *>(smem + (rows_bytes > utt_bytes ? rows_bytes : utt_bytes));
 
+    if ((int)blockIdx.x >= nrb + p.B) {  // last CTA (present only when the launch is sliced): length bucketing
+        sort_by_length(p, reinterpret_cast<int *>(smem));
+        return;
+    }
     if ((int)blockIdx.x >= nrb) {
         prep_utterance(p, blockIdx.x - nrb, reinterpret_cast<int *>(smem), cnt);
         return;
@@ -448,7 +476,8 @@ template <int K, int CP>
 __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel(const CtcParams p) {
     static_assert(K % 2 == 0 && K >= 4, "K must be even and >= 4");
     extern __shared__ __align__(16) unsigned char smem[];
-    const int b = p.score_only ? blockIdx.x : (blockIdx.x >> 1);
+    const int bi = p.slice0 + (p.score_only ? blockIdx.x : (blockIdx.x >> 1));
+    const int b = p.bord ? p.bord[bi] : bi;
     const bool fwd = p.score_only ? true : !(blockIdx.x & 1);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nwl = p.nwl, C = p.C;
@@ -784,7 +813,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
     static_assert(K == 8, "the label table and the 224-state chunking are laid out for K = 8");
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int R = kGroup, Cp = CP;
-    const int z = blockIdx.x, b = blockIdx.y;
+    const int z = blockIdx.x, b = p.bord ? p.bord[p.slice0 + blockIdx.y] : p.slice0 + (int)blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
     const int C = p.C, NT = p.nwl * 32;
     const int Tb = min(max(p.act_lens[b], 0), p.T);
@@ -1034,6 +1063,10 @@ __host__ __device__ inline size_t prep_big_smem(int C, int Lmax) {
 __global__ void __launch_bounds__(kPrepRows) ctc_prep_utt_kernel(const CtcParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     int *lps = reinterpret_cast<int *>(smem);
+    if ((int)blockIdx.x >= p.B) {  // extra CTA of a sliced launch: length bucketing
+        sort_by_length(p, lps);
+        return;
+    }
     prep_utterance(p, blockIdx.x, lps, lps + (p.Lmax > 0 ? p.Lmax : 1));
 }
 

@@ -118,14 +118,13 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         if (ns > B || B > kMaxSortB) ns = 1;
         pl->nslices = ns;
         if (ns > 1 && pl->smem_prep < sizeof(int) * (size_t)B) pl->smem_prep = sizeof(int) * (size_t)B;
-        // An engine CTA may REQUEST more shared memory than it uses so that fewer gradient CTAs of other slices fit
-        // beside it on its SM (they would steal issue slots and FP64 pipe from the latency-critical recursion).
-        size_t req = (size_t)env_int("CTC_B200_ENGINE_SMEM_KB", 0) * 1024;
-        if (req > kSmemLimit) req = kSmemLimit;
+        // (Padding the engine's shared-memory request to keep gradient CTAs of other slices off its SM was measured:
+        // no effect at 0 / 120 / 180 KB, so engines simply request what they use.)
+        const size_t req = 0;
         pl->smem_engine_req = req > pl->smem_engine ? req : pl->smem_engine;
     }
     size_t o = 0;
-    const size_t ck = sizeof(double) * (size_t)B * pl->nblk * NT * kK;
+    const size_t ck = sizeof(int) * (size_t)B * pl->nblk * NT * kK;
     const size_t ckE = sizeof(int) * (size_t)B * pl->nblk * NT;
     pl->o_y = o;      o = align256(o + sizeof(unsigned) * (size_t)T * B * 2 * pl->Cp);
     pl->o_ckA = o;    o = align256(o + ck);
@@ -396,8 +395,8 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.Lmax = pl.Lmax;
     p.score_only = grads ? 0 : 1;
     p.y = reinterpret_cast<unsigned *>(ws + pl.o_y);
-    p.ckA = reinterpret_cast<double *>(ws + pl.o_ckA);
-    p.ckB = reinterpret_cast<double *>(ws + pl.o_ckB);
+    p.ckA = reinterpret_cast<int *>(ws + pl.o_ckA);
+    p.ckB = reinterpret_cast<int *>(ws + pl.o_ckB);
     p.ckAE = reinterpret_cast<int *>(ws + pl.o_ckAE);
     p.ckBE = reinterpret_cast<int *>(ws + pl.o_ckBE);
     p.Pm = reinterpret_cast<double *>(ws + pl.o_Pm);

@@ -37,6 +37,10 @@ __device__ __forceinline__ double pow2i(int d) {
 // biased exponent field of a non-negative double (0 => zero/denormal)
 __device__ __forceinline__ int expo_field(double x) { return __double2hiint(x) >> 20; }
 
+// High word of a non-negative double, rounded to nearest: the full exponent range with 21 significant bits.  Used for
+// values that only seed / enter products of the gradient pass (parked rows, checkpoints): relative error <= 2^-22.
+__device__ __forceinline__ int hi_round(double x) { return __double2hiint(x) + (int)((unsigned)__double2loint(x) >> 31); }
+
 // ---------------------------------------------------------------- barriers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 

@@ -43,7 +43,7 @@ struct CtcParams {
     // workspace
     unsigned *y;        // [B][T][2*Cp] softmax rows, planar fp64: Cp high words then Cp low words (exact widening
                         // of the fp32 softmax, clamped to >= 2^-126)
-    double *ckA, *ckB;  // [B][nblk][nwl*32*K] mantissas
+    int *ckA, *ckB;     // [B][nblk][nwl][K/4][32] int4: checkpoint mantissas as rounded high words (hi_round)
     int *ckAE, *ckBE;   // [B][nblk][nwl*32]   exponents
     double *Pm;         // [B] mantissa of p(l|x) in [1,2)
     int *Pe;            // [B] exponent of p(l|x)
@@ -490,7 +490,7 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
     Slot *slots = reinterpret_cast<Slot *>(smem + lay.slots);
     double *pm = reinterpret_cast<double *>(smem + lay.misc);  // [2]
     int *pe = reinterpret_cast<int *>(smem + lay.misc + 16);   // [2]
-    double *ck = (fwd ? p.ckA : p.ckB) + (size_t)b * p.nblk * NT * K;
+    int *ck = (fwd ? p.ckA : p.ckB) + (size_t)b * p.nblk * NT * K;
     int *ckE = (fwd ? p.ckAE : p.ckBE) + (size_t)b * p.nblk * NT;
 
     const int Tb = min(max(p.act_lens[b], 0), p.T);
@@ -605,12 +605,14 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
     const int dt = fwd ? kGroup : -kGroup;
     const int ntail = Tb - (ngroups - 1) * kGroup;    // rows of the ragged last group (1..8)
     // checkpoints (settled exponents): alpha after row t0+7 -> block G+1 ; beta_{t0} -> block G-1, i.e. every group
-    // but this direction's last one.  Global layout per (block, lattice warp): [K/2 cell pairs][32 lanes] double2, so
-    // every store (and every load of the gradient kernel) is one fully coalesced 512-byte access.
+    // but this direction's last one.  They only seed the gradient kernel's 8-step recomputation, so the mantissas are
+    // stored as rounded high words (hi_round: full exponent range, 21 bits): half the bytes of the largest stream of
+    // the whole pass.  Global layout per (block, lattice warp): [K/4][32 lanes] int4 -- every store (and every load of
+    // the gradient kernel) is one fully coalesced 512-byte access.
     const int cb0 = fwd ? 1 : ngroups - 2;
-    double2 *ckp = reinterpret_cast<double2 *>(ck + ((ptrdiff_t)cb0 * NT + warp * 32) * K) + lane;
+    int4 *ckp = reinterpret_cast<int4 *>(ck + ((ptrdiff_t)cb0 * NT + warp * 32) * K) + lane;
     int *ckEp = ckE + (ptrdiff_t)cb0 * NT + thread;
-    const ptrdiff_t ckstep = (fwd ? 1 : -1) * (ptrdiff_t)NT * (K / 2), ckEstep = (fwd ? 1 : -1) * (ptrdiff_t)NT;
+    const ptrdiff_t ckstep = (fwd ? 1 : -1) * (ptrdiff_t)NT * (K / 4), ckEstep = (fwd ? 1 : -1) * (ptrdiff_t)NT;
     const bool want_ck = !p.score_only;
     for (int j = 0; j < ngroups; ++j) {
         PROF(long long ta = prof_clk(); ++ngr;)
@@ -635,7 +637,9 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
         if (j < ngroups - 1) {
             if (want_ck) {
 #pragma unroll
-                for (int k = 0; k < K; k += 2) ckp[(k / 2) * 32] = make_double2(c.a[k], c.a[k + 1]);
+                for (int k = 0; k < K; k += 4)
+                    ckp[(k / 4) * 32] = make_int4(hi_round(c.a[k]), hi_round(c.a[k + 1]), hi_round(c.a[k + 2]),
+                                                  hi_round(c.a[k + 3]));
                 *ckEp = c.E;
             }
             ckp += ckstep;
@@ -721,10 +725,10 @@ __device__ __forceinline__ void park_row(int *row, int lane, const double (&v)[K
 #pragma unroll
     for (int h = 0; h < K / 4; ++h) {
         int4 w;
-        w.x = __double2hiint(v[4 * h + 0]) + (int)((unsigned)__double2loint(v[4 * h + 0]) >> 31);
-        w.y = __double2hiint(v[4 * h + 1]) + (int)((unsigned)__double2loint(v[4 * h + 1]) >> 31);
-        w.z = __double2hiint(v[4 * h + 2]) + (int)((unsigned)__double2loint(v[4 * h + 2]) >> 31);
-        w.w = __double2hiint(v[4 * h + 3]) + (int)((unsigned)__double2loint(v[4 * h + 3]) >> 31);
+        w.x = hi_round(v[4 * h + 0]);
+        w.y = hi_round(v[4 * h + 1]);
+        w.z = hi_round(v[4 * h + 2]);
+        w.w = hi_round(v[4 * h + 3]);
         *reinterpret_cast<int4 *>(row + (h * 32 + lane) * 4) = w;
     }
 }
@@ -881,18 +885,18 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
     const int s_last = S - 1;
 
     // checkpoint registers of the NEXT group to process (prefetched one group ahead)
-    double nA[K], nB[K];
+    int4 nA[K / 4], nB[K / 4];
     int nEa = 0, nEb = 0;
     auto fetch = [&](int blk) {
         const size_t cb = ((size_t)b * p.nblk + blk) * NT;
         const bool hasA = valid_e && blk > 0, hasB = valid_e && (blk + 1) * R < Tb;
+        const size_t base = (cb + (e & ~31)) * K;
 #pragma unroll
-        for (int k = 0; k < K; k += 2) {
-            double2 va = make_double2(0.0, 0.0), vb = make_double2(0.0, 0.0);
-            if (hasA) va = *reinterpret_cast<const double2 *>(p.ckA + (cb + (e & ~31)) * K + ((k / 2) * 32 + (e & 31)) * 2);
-            if (hasB) vb = *reinterpret_cast<const double2 *>(p.ckB + (cb + (e & ~31)) * K + ((k / 2) * 32 + (e & 31)) * 2);
-            nA[k] = va.x; nA[k + 1] = va.y;
-            nB[k] = vb.x; nB[k + 1] = vb.y;
+        for (int h = 0; h < K / 4; ++h) {
+            nA[h] = make_int4(0, 0, 0, 0);
+            nB[h] = make_int4(0, 0, 0, 0);
+            if (hasA) nA[h] = *reinterpret_cast<const int4 *>(p.ckA + base + (h * 32 + (e & 31)) * 4);
+            if (hasB) nB[h] = *reinterpret_cast<const int4 *>(p.ckB + base + (h * 32 + (e & 31)) * 4);
         }
         nEa = hasA ? p.ckAE[cb + e] : 0;
         nEb = hasB ? p.ckBE[cb + e] : 0;
@@ -911,7 +915,12 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
         Cells<K> c;
         double bsave[K];
 #pragma unroll
-        for (int k = 0; k < K; ++k) { c.a[k] = nA[k]; bsave[k] = nB[k]; }
+        for (int h = 0; h < K / 4; ++h) {
+            c.a[4 * h + 0] = __hiloint2double(nA[h].x, 0); bsave[4 * h + 0] = __hiloint2double(nB[h].x, 0);
+            c.a[4 * h + 1] = __hiloint2double(nA[h].y, 0); bsave[4 * h + 1] = __hiloint2double(nB[h].y, 0);
+            c.a[4 * h + 2] = __hiloint2double(nA[h].z, 0); bsave[4 * h + 2] = __hiloint2double(nB[h].z, 0);
+            c.a[4 * h + 3] = __hiloint2double(nA[h].w, 0); bsave[4 * h + 3] = __hiloint2double(nB[h].w, 0);
+        }
         c.E = nEa;
         const int Eb0 = nEb;
         const int nblk_next = blk + p.nsplit;

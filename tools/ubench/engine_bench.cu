@@ -42,7 +42,7 @@ int main(int argc, char **argv) {
     CK(cudaMemcpy(d_ll, ll.data(), B * 4, cudaMemcpyHostToDevice)); CK(cudaMemcpy(d_al, al.data(), B * 4, cudaMemcpyHostToDevice));
     p.acts = d_acts; p.grads = d_grads; p.costs = d_costs; p.labels = d_lab; p.label_lens = d_ll; p.act_lens = d_al;
     CK(cudaMalloc(&p.y, sizeof(unsigned) * (size_t)T * B * 2 * p.Cp));
-    size_t ck = sizeof(double) * (size_t)B * p.nblk * NT * kK, ckE = sizeof(int) * (size_t)B * p.nblk * NT;
+    size_t ck = sizeof(int) * (size_t)B * p.nblk * NT * kK, ckE = sizeof(int) * (size_t)B * p.nblk * NT;
     CK(cudaMalloc(&p.ckA, ck)); CK(cudaMalloc(&p.ckB, ck)); CK(cudaMalloc(&p.ckAE, ckE)); CK(cudaMalloc(&p.ckBE, ckE));
     CK(cudaMalloc(&p.Pm, 8 * B)); CK(cudaMalloc(&p.Pe, 4 * B)); CK(cudaMalloc(&p.feas, 4 * B)); CK(cudaMalloc(&p.laboff, 4 * B));
     CK(cudaMalloc(&p.tlab, 16 * (size_t)B * NT)); CK(cudaMalloc(&p.coff, 4 * (size_t)B * (C + 1)));

@@ -193,3 +193,67 @@ def test_errors(b200):
     with pytest.raises(RuntimeError):  # act_len > T
         b200.ctc_forward_backward(a.cuda(), torch.tensor([1], dtype=torch.int32),
                                   torch.tensor([11, 10], dtype=torch.int32), torch.tensor([1, 0], dtype=torch.int32))
+
+
+def test_length_bucket_slices_are_invisible(oracle, b200, monkeypatch):
+    # The engine/grad launches are cut into length-bucket slices on side streams; the result of an utterance must
+    # not depend on how the batch was sliced (bitwise), including batch sizes that do not divide evenly.
+    for B in (64, 37, 9):
+        d = _wl(b200, "cpu_b16_t500", seed=5, B=B)
+        monkeypatch.setenv("CTC_B200_SLICES", "1")
+        c1, g1 = _run(b200, d)
+        for ns in ("2", "5", "8"):
+            monkeypatch.setenv("CTC_B200_SLICES", ns)
+            c2, g2 = _run(b200, d)
+            assert np.array_equal(c1, c2) and np.array_equal(g1, g2), (B, ns)
+        monkeypatch.delenv("CTC_B200_SLICES")
+        if B == 37:
+            _check(oracle, b200, d)
+
+
+def test_sliced_launch_orders_with_caller_stream(b200):
+    # work enqueued on the caller's stream after the call must see the finished gradients (fork/join events)
+    d = _wl(b200, "cpu_b16_t500", seed=6, B=32)
+    acts = d["acts"].cuda()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        costs, grads = b200.ctc_forward_backward(acts, d["labels"], d["act_lens"], d["label_lens"])
+        total = grads.abs().sum() + costs.sum()  # consumer on the same (non-default) stream
+    s.synchronize()
+    c2, g2 = b200.ctc_forward_backward(acts, d["labels"], d["act_lens"], d["label_lens"])
+    torch.cuda.synchronize()
+    assert torch.equal(grads, g2) and torch.equal(costs, c2)
+    assert abs(float(total) - float(g2.abs().sum() + c2.sum())) <= 1e-3 * abs(float(total))
+
+
+@pytest.mark.parametrize("B", [3, 16, 33, 64])
+def test_host_buffer_entry(oracle, b200, B):
+    # ctc_b200_compute_host (the C-ABI entry bench.py's e2e leg times): pinned host buffers in and out, the batch
+    # pipelined in utterance slices; must equal the device-resident entry bit for bit
+    import ctypes
+
+    lib = b200.pkg._lib.load()
+    d = _wl(b200, "cpu_b16_t500", seed=8, B=B)
+    T, C = d["T"], d["C"]
+    h_acts = d["acts"].contiguous().pin_memory()
+    h_grads = torch.full_like(d["acts"], float("nan")).pin_memory()
+    h_costs = torch.empty(B, dtype=torch.float32).pin_memory()
+    ctx = ctypes.c_void_p()
+    b200.pkg._lib.check(lib.ctc_b200_create(ctypes.byref(ctx)))
+    opts = b200.pkg._lib.CtcOptions()
+    lib.ctc_b200_default_options(ctypes.byref(opts))
+    loss_sum = ctypes.c_double(0.0)
+    hl, hal, hll = d["labels"].contiguous(), d["act_lens"].contiguous(), d["label_lens"].contiguous()
+    for _ in range(2):  # second call reuses the context's buffers and streams
+        st = lib.ctc_b200_compute_host(ctx, h_acts.data_ptr(), h_grads.data_ptr(), hl.data_ptr(), hll.data_ptr(),
+                                       hal.data_ptr(), T, B, C, h_costs.data_ptr(), ctypes.byref(loss_sum),
+                                       ctypes.byref(opts))
+        b200.pkg._lib.check(st, "ctc_b200_compute_host")
+    lib.ctc_b200_destroy(ctx)
+    costs, grads = _run(b200, d)
+    assert np.array_equal(h_costs.numpy().astype(np.float64), costs)
+    assert np.array_equal(h_grads.numpy().astype(np.float64), grads)
+    assert abs(loss_sum.value - costs.sum()) <= 1e-6 * abs(costs.sum())
+    if B == 33:
+        oc, og = oracle.compute(d["acts"].numpy(), hl.numpy(), hal.numpy(), hll.numpy())
+        assert np.abs(h_grads.numpy().astype(np.float64) - og).max() <= GRAD_ATOL

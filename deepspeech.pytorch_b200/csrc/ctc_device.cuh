@@ -4,14 +4,16 @@
 //   alpha / beta live in the LINEAR domain.  Each lattice thread owns K adjacent states of the blank-extended
 //   label sequence l'  as fp64 mantissas plus ONE int exponent E: value = m * 2^E.
 //   * every kGroup (= 8) time steps a thread rescales its own mantissas by an exact power of two so that the
-//     largest lies in [1,2) (thread-local, no communication); a thread whose mantissas are all zero is DEAD
-//     (E = kDeadE).  Emissions are clamped to >= 2^-126, so nothing can underflow within one group.
-//   * inflow from the neighbouring thread arrives as a (mantissa, exponent) pair taken at the same instant and is
-//     multiplied by 2^(E_nbr - E_me) on the RECEIVE side; if the neighbour sits more than 2^kLift above me (or I
-//     am dead) I first re-base onto its exponent (my content is negligible next to what is about to flow in).
-//   Measured on B200 (tools/ubench/lat.cu): DFMA latency 8 clk, 16 lanes/clk/SMSP; SHFL 27 clk; bar.sync (4 warps)
-//   39 clk.  A K=8 lattice step is ~20 fp64 instructions = ~40 clk of FP64 pipe per warp, so neighbour values are
-//   exchanged one step AHEAD of their use and block-wide synchronisation happens once per group, not per step.
+//     largest lies in [1,2) (renorm, thread-local); a thread whose mantissas are all zero is DEAD (E = kDeadE).
+//     Emissions are clamped to >= 2^-126, so nothing can underflow within one group.
+//   * right after the renorm the warp SETTLES its exponents (settle): dead threads adopt the exponent of the nearest
+//     live thread on their inflow side, threads sitting more than 2^kLift below their inflow neighbour re-base onto
+//     it.  Exponents are then fixed for the whole next group, so a step moves mantissas only and scales the value
+//     flowing in from the neighbouring thread by the per-group constant f = 2^(E_nbr - E_me).
+//   Measured on B200 (tools/ubench/lat*.cu): DFMA latency 8 clk, 16 lanes/clk/SMSP; SHFL 27 clk; bar.sync (4 warps)
+//   39-52 clk; an E-shuffle plus rescale in every step costs +32 clk/step, which is why exponents are per group.
+//   A K=8 lattice step is ~21 fp64 + ~30 other instructions, ~90-100 clk for the one warp an SMSP hosts, so
+//   neighbour values are exchanged one step AHEAD of their use and the CTA synchronises once per group.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -230,25 +232,6 @@ __device__ __forceinline__ void beta_rest(double (&a)[K], double (&bb)[K], doubl
     bb[1] = b1;
     a[0] = n0;
     a[1] = n1v;
-}
-
-// Per-thread constants of the blank-extended sequence: emission index and skip masks of the K/2 label states.
-// lab: int [L] labels of this utterance (shared or global).  Invalid (padding) label states point at `blank`.
-template <int K>
-__device__ __forceinline__ void thread_labels(const int *lab, int L, int thread, int C, int blank,
-                                              int (&idx)[K / 2], double (&skipA)[K / 2], double (&skipB)[K / 2],
-                                              int (&lab_i)[K / 2]) {
-#pragma unroll
-    for (int h = 0; h < K / 2; ++h) {
-        const int i = (thread * K) / 2 + h;  // label position of state thread*K + 2h+1
-        const bool valid = i < L;
-        int c = valid ? lab[i] : blank;
-        c = min(max(c, 0), C - 1);
-        idx[h] = c;
-        lab_i[h] = valid ? i : -1;
-        skipA[h] = (valid && (i == 0 || min(max(lab[i - 1], 0), C - 1) != c)) ? 1.0 : 0.0;
-        skipB[h] = (valid && i + 1 < L && min(max(lab[i + 1], 0), C - 1) != c) ? 1.0 : 0.0;
-    }
 }
 
 }  // namespace ctcb200

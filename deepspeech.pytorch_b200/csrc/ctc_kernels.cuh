@@ -1,21 +1,26 @@
-// csrc/ctc_kernels.cuh -- the three kernels of the B200 CTC loss (sm_100a), small-alphabet (class-row) path.
+// csrc/ctc_kernels.cuh -- the kernels of the B200 CTC loss (sm_100a).
 //
-//   ctc_prep_kernel   : grid ceil(T*B/128) + B.  Row blocks: fused softmax over C per (t,b) -- coalesced float4 loads
-//                       of 128 consecutive rows into shared memory, one thread per row for max / sum, coalesced
-//                       stores of the fp32 emission rows y[b,t,0:Cp] (utterance-major, 16-byte-multiple pitch: the 8
-//                       rows of a group are ONE TMA bulk copy).  Utterance blocks: label offsets and the class-sorted label order.
-//   ctc_engine_kernel : grid 2B (score-only: B).  CTA 2b runs the alpha recursion of utterance b forwards in time,
-//                       CTA 2b+1 the beta recursion backwards, concurrently on different SMs.  Lattice warps hold
-//                       K states per thread in registers and form a SYSTOLIC pipeline over groups of 8 time steps:
-//                       in super-step i, warp q works on group i-q, so boundary values cross warps through a
-//                       shared-memory ring one group late and the CTA synchronises once per group (not per step).
-//                       A producer warp TMA-prefetches the emission rows of the coming groups into a ring.
-//                       Every R steps the state is checkpointed.  The alpha CTA ends with P = p(l|x) -> costs[b].
-//   ctc_grad_kernel   : grid (ceil(T/R), B).  One CTA per (utterance, block of R time steps): recomputes the alpha
-//                       rows of the block from its checkpoint into shared memory, sweeps beta backwards from the
-//                       beta checkpoint, forms posteriors alpha*betabar/P, reduces them per class in shared memory
-//                       and writes grad = scale * (softmax - occupancy) once, one coalesced row segment per (t,b).
-//                       Rows t >= act_lens[b] are written as zeros by the same kernel.
+//   ctc_prep_kernel   : grid ceil(T*B/128) + B (+1).  Row blocks: fused softmax over C per (t,b) -- coalesced float4
+//                       loads of 128 consecutive rows into shared memory, one thread per row for max / sum, coalesced
+//                       stores of the emission rows y[b,t,:] as PLANAR fp64 words (Cp high words, Cp low words;
+//                       utterance-major, so the 8 rows of a group are ONE TMA bulk copy); padding frames get their
+//                       zero gradient rows here.  Utterance blocks: label offsets, class-sorted label order, the
+//                       per-thread label table and the gradient kernel's reduction units.  Extra block of a sliced
+//                       launch: utterances ranked by length (sort_by_length).
+//   ctc_engine_kernel : grid 2 * nb (score-only: nb) per slice.  CTA 2i runs the alpha recursion of utterance i
+//                       forwards in time, CTA 2i+1 the beta recursion backwards, concurrently on different SMs.
+//                       Lattice warps hold K = 8 states per thread in registers and form a SYSTOLIC pipeline over
+//                       groups of 8 time steps: in super-step i warp q works on group i-q, boundary values cross warps
+//                       through a shared-memory ring one group late and the CTA synchronises once per group.  A
+//                       producer warp TMA-prefetches the emission tiles of the coming groups into a ring.  After every
+//                       group the renormalised, settled state is checkpointed.  The alpha CTA ends with P = p(l|x).
+//   ctc_grad_kernel   : grid (nsplit, nb) per slice, 4 CTAs/SM.  CTA (z, i) takes time groups z, z+nsplit, ... of
+//                       utterance i: warp q recomputes alpha over its 224 states (+16-state halos) from the
+//                       checkpoint into shared memory, sweeps beta backwards from the beta checkpoint forming
+//                       posteriors alpha*betabar/P, then the CTA reduces them per class in equal-sized units and
+//                       writes grad = scale * (softmax - occupancy) once.
+//   large alphabets (C > 128): ctc_prep_utt_kernel + ctc_prep_big_kernel (streaming softmax, emission rows gathered by
+//                       label POSITION) -> the same engine / grad kernels at pitch 256 -> ctc_final_big_kernel.
 //
 // Replaces the arithmetic behind `criterion(logits, targets, output_sizes.cpu(), target_sizes)`
 // (/root/reference/train.py:600; eval :352,:457), i.e. warp-ctc's softmax + compute_alpha + compute_betas_and_grad
@@ -690,10 +695,9 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
 // One CTA per (utterance, every nsplit-th group of 8 time steps).  Warp q owns the 224 lattice states
 // [224q, 224q+224) (28 core threads) and recomputes a HALO of 16 states (2 threads) on either side, which is exactly
 // how far information travels in 8 steps (2 states per step): the warps of a CTA never exchange boundary values and
-// synchronise only twice per group, around the per-class reduction.  The checkpoints are renormalised and
-// exponent-settled, so inside a group every thread works with ONE alpha exponent and ONE beta exponent.
-// The next group's checkpoints (registers) and emission tile (TMA, double buffer) are prefetched during the
-// current one.
+// synchronise only around the per-class reduction.  The checkpoints are renormalised and exponent-settled, so inside
+// a group every thread works with ONE alpha exponent and ONE beta exponent.  The next group's checkpoints
+// (registers) and emission tile (TMA, double buffer) are prefetched during the current one.
 constexpr int kMaxGradWarps = 10;  // ceil((2*1023+1) / 224)
 
 struct GradSmem {

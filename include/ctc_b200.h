@@ -22,8 +22,14 @@
  *   costs  : DEVICE fp32 [B], -log p(l_b | x_b); the caller sums (train.py:601 then divides by B)
  *   lengths/labels may live on the host (what the reference passes) or on the device (lets the caller drop the
  *            `.cpu()` sync at train.py:600) -- see ctcB200Options.lengths_on_device
- *   All work is enqueued on options->stream; no call synchronises the device or keeps global state.
- *   Errors are returned as ctcB200Status, never thrown or aborted.
+ *   All work is ordered on options->stream: the caller sees ordinary stream semantics (later work on that stream
+ *   sees the results; stream capture into a CUDA graph works).  Internally the recursion and gradient kernels are
+ *   launched per LENGTH-BUCKET SLICE of the batch (utterances ranked by frames on the device) on a small per-device
+ *   pool of side streams that are forked from and joined back to options->stream with events, so that the gradient
+ *   work of short utterances overlaps the recursion of long ones.  The pool (streams + events) is the only state
+ *   the library keeps; it is created on first use and shared by all callers (enqueue is serialised by a mutex).
+ *   Environment: CTC_B200_SLICES=n overrides the slice count (1 = everything on options->stream itself).
+ *   ctc_b200_compute never synchronises the device.  Errors are returned as ctcB200Status, never thrown or aborted.
  */
 #ifndef CTC_B200_H_
 #define CTC_B200_H_
@@ -91,8 +97,10 @@ ctcB200Status ctc_b200_compute(const float *acts, float *grads, const int *label
 /*
  * Host-buffer convenience path (what a non-torch caller of the reference's CPU location would use, and what
  * bench.py's end-to-end leg times): acts/grads/costs are HOST pointers (pinned memory recommended); the call
- * stages them through device buffers owned by `ctx`, runs ctc_b200_compute and copies results back, all on
- * opts->stream, then synchronises that stream.  *loss_sum receives sum_b costs[b].
+ * stages them through device buffers owned by `ctx`, runs the kernels and copies results back, ordered on
+ * opts->stream, then synchronises that stream.  The batch is pipelined in up to 4 slices of utterances on streams
+ * owned by `ctx`: the host->device copy of slice k+1, the kernels of slice k and the device->host copy of slice k-1
+ * overlap.  *loss_sum receives sum_b costs[b].
  */
 typedef struct ctcB200Context ctcB200Context;
 ctcB200Status ctc_b200_create(ctcB200Context **ctx);

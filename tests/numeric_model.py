@@ -1,7 +1,7 @@
 """tests/numeric_model.py -- numpy model of the NUMERIC SCHEME the CUDA lattice kernels use (test support).
 
-Not an oracle and not the product: it mirrors, array-for-thread, the arithmetic of csrc/ctc_lattice.cuh so the
-representation can be checked on the CPU against oracle/ before any GPU time is spent:
+Not an oracle and not the product: it mirrors, array-for-thread, the arithmetic of csrc/ctc_device.cuh and
+csrc/ctc_kernels.cuh so the representation can be checked on the CPU against oracle/ before any GPU time is spent:
 
   * emissions y = softmax(acts) in fp32, clamped to >= 2^-126, widened (exactly) to fp64
   * alpha / beta in the LINEAR domain, fp64 mantissa, one int exponent per group of K adjacent states
@@ -9,6 +9,10 @@ representation can be checked on the CPU against oracle/ before any GPU time is 
   * renormalisation every N steps: group max -> [1,2)  (exact power-of-two scaling)
   * neighbour-group inflow scaled by 2^(E_nbr - E_me), clamped to the fp64 exponent range
   * posterior(t,s) = m_alpha * m_betabar * 2^(E_alpha + E_beta - E_P) / m_P
+  * engine / gradient split with checkpoints every N steps; checkpoints and parked alpha rows kept as rounded high
+    words (21 significant bits), which is where the gradient's extra ~5e-7 comes from
+(The exponent lift is modelled as a scan with LIFT = 500; the kernel iterates a neighbour rule with kLift = 250 --
+both only act on threads whose content is negligible next to their inflow.)
 """
 from __future__ import annotations
 
@@ -126,25 +130,39 @@ def betabar(lat: Lattice, v, E):
     return v + n1 + lat.skip_b * n2
 
 
-def run(acts_tc, label, K: int = 8, N: int = 8, blank: int = 0):
-    """Full fwd+bwd for one utterance with the scaled-linear scheme.  Returns (cost, grad[T,C])."""
+def round_hi(v):
+    """What csrc/ctc_device.cuh hi_round keeps of a non-negative double: the high word, rounded to nearest --
+    the full exponent range and 21 significant bits."""
+    m, e = np.frexp(v)
+    return np.ldexp(np.round(m * 2.0 ** 21) / 2.0 ** 21, e)
+
+
+def run(acts_tc, label, K: int = 8, N: int = 8, blank: int = 0, hi_words: bool = True):
+    """Full fwd+bwd for one utterance with the scaled-linear scheme.  Returns (cost, grad[T,C]).
+
+    Mirrors the kernels' split: the ENGINE runs the alpha and beta chains in full fp64 and leaves a checkpoint
+    (mantissas, exponents) at every group boundary; the GRADIENT pass restarts both chains from the checkpoints of
+    each group and multiplies parked alpha rows into live betabar rows.  With hi_words the checkpoints and the parked
+    rows keep only the rounded high word of each double, as on the device."""
     T, C = acts_tc.shape
     y = softmax_f32(acts_tc)
     lat = Lattice(label, K, blank)
     G = lat.G
-    # ---- alpha, all rows kept (model only; the kernel checkpoints + recomputes)
-    A = np.zeros((T, G, K))
-    EA = np.zeros((T, G), dtype=np.int64)
+    S = lat.S
+    keep = round_hi if hi_words else (lambda x: x)
+    ngroups = (T + N - 1) // N
+    # ---- engine, alpha: checkpoint g = state BEFORE row g*N (after renormalisation)
+    ckA = [None] * ngroups
     v = np.zeros((G, K))
     E = np.zeros(G, dtype=np.int64)
     for t in range(T):
+        if t % N == 0:
+            ckA[t // N] = (v.copy(), E.copy())
         v = alpha_step(lat, v, E, y[t], t == 0)
-        if (t + 1) % N == 0:
+        if (t + 1) % N == 0 or t == T - 1:
             v, E = _renorm(v, E, True)
-        A[t], EA[t] = v, E
     # ---- P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2)
-    flat = (v * np.ldexp(1.0, 0)).reshape(-1)
-    S = lat.S
+    flat = v.reshape(-1)
     gl, gs = (S - 1) // K, (S - 2) // K
     eP = max(E[gl], E[gs]) if S > 1 else E[gl]
     mP = flat[S - 1] * _pow2(np.array(E[gl] - eP))
@@ -152,22 +170,38 @@ def run(acts_tc, label, K: int = 8, N: int = 8, blank: int = 0):
         mP = mP + flat[S - 2] * _pow2(np.array(E[gs] - eP))
     if mP == 0:
         return float("inf"), np.zeros((T, C))
-    fr, ex = np.frexp(mP)  # normalise P's mantissa (kernel: frexp on one thread)
+    fr, ex = np.frexp(mP)  # normalise P's mantissa (kernel: exponent field on one thread)
     mP, eP = fr * 2.0, eP + int(ex) - 1
     cost = -(np.log(mP) + eP * np.log(2.0))
-    # ---- beta backwards, posterior, gradient
-    grad = np.zeros((T, C))
+    # ---- engine, beta: checkpoint g = standard beta AFTER row (g+1)*N, i.e. the state the group g sweep starts from
+    ckB = [None] * ngroups
     vb = np.zeros((G, K))
     vb.reshape(-1)[S - 1] = 1.0  # virtual beta_T
     Eb = np.zeros(G, dtype=np.int64)
     for t in range(T - 1, -1, -1):
-        bb = betabar(lat, vb, Eb)
-        g = _pow2(EA[t] + Eb - eP) / mP
-        post = (A[t] * bb * g[:, None]).reshape(-1)
-        occ = np.zeros(C)
-        np.add.at(occ, lat.ext[: lat.S], post[: lat.S])
-        grad[t] = y[t] - occ
-        vb = bb * lat.yrow(y[t])
+        if t == T - 1 or (t + 1) % N == 0:
+            ckB[t // N] = (vb.copy(), Eb.copy())
+        vb = betabar(lat, vb, Eb) * lat.yrow(y[t])
         if t % N == 0:
             vb, Eb = _renorm(vb, Eb, False)
+    # ---- gradient pass, one group at a time from the (rounded) checkpoints
+    grad = np.zeros((T, C))
+    for g in range(ngroups):
+        t0, t1 = g * N, min(T, (g + 1) * N)
+        va, Ea = ckA[g]
+        va = keep(va) if g > 0 else va            # block 0 starts from the exact virtual state
+        rows = []
+        for t in range(t0, t1):
+            va = alpha_step(lat, va, Ea, y[t], t == 0)
+            rows.append(keep(va))                 # parked row
+        vb, Eb = ckB[g]
+        vb = keep(vb) if t1 < T else vb           # the last block starts from the exact virtual beta_T
+        for t in range(t1 - 1, t0 - 1, -1):
+            bb = betabar(lat, vb, Eb)
+            gsc = _pow2(Ea + Eb - eP) / mP
+            post = (rows[t - t0] * bb * gsc[:, None]).reshape(-1)
+            occ = np.zeros(C)
+            np.add.at(occ, lat.ext[:S], post[:S])
+            grad[t] = y[t] - occ
+            vb = bb * lat.yrow(y[t])
     return float(cost), grad

@@ -80,13 +80,16 @@ def test_numeric_model_of_kernel_scheme(oracle):
     # the block-exponent linear-domain fp64 scheme the CUDA kernels use (tests/numeric_model.py), long and peaky
     import numeric_model as nm
     rng = np.random.default_rng(3)
-    for T, L, C, sigma in ((200, 40, 29, 1.0), (300, 90, 30, 5.0), (64, 32, 5, 8.0)):
+    for T, L, C, sigma in ((200, 40, 29, 1.0), (300, 90, 30, 5.0), (64, 32, 5, 8.0), (203, 40, 29, 1.0)):
         a = (rng.standard_normal((T, 1, C)) * sigma).astype(np.float32)
         lab = rng.integers(1, C, L).astype(np.int32)
         costs, grads = oracle.compute(a, lab, np.array([T], np.int32), np.array([L], np.int32))
-        cost, grad = nm.run(a[:, 0], lab.tolist(), K=8, N=8)
-        if np.isfinite(cost):
-            assert abs(cost - costs[0]) <= 1e-6 * abs(costs[0])
-            assert np.abs(grad - grads[:, 0]).max() <= 2e-6
-        else:
-            assert costs[0] == 0.0
+        for hi_words, bound in ((False, 5e-7), (True, 2e-6)):
+            # hi_words: checkpoints and parked rows keep 21 significant bits, as on the device -- the bound documents
+            # what that costs next to the 1e-5 tolerance of the GPU parity tests
+            cost, grad = nm.run(a[:, 0], lab.tolist(), K=8, N=8, hi_words=hi_words)
+            if np.isfinite(cost):
+                assert abs(cost - costs[0]) <= 1e-6 * abs(costs[0])
+                assert np.abs(grad - grads[:, 0]).max() <= bound
+            else:
+                assert costs[0] == 0.0

@@ -107,50 +107,59 @@ constexpr int kPrepRows = 128;
 
 __host__ __device__ inline size_t prep_smem(int C, int Lmax) {
     const size_t rows = align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows;
-    const size_t utt = sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1);  // class-sorted positions of one utterance
-    return (rows > utt ? rows : utt) + sizeof(int) * (C + 1) + 64;  // >= 4 * kMaxSortB bytes is checked by the plan
+    const size_t utt = 2 * sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1);  // sorted positions + staged labels
+    return (rows > utt ? rows : utt) + sizeof(int) * (C + 2) + 64;  // >= 4 * B bytes (sort block): see make_plan
 }
 
-// Class-sorted positions of the labels of one utterance (one warp): lpos[i] = rank of label i when labels are
-// stably sorted by class; coff[c] = first position of class c.  Lets the grad kernel reduce posteriors per class
-// over contiguous shared-memory segments, deterministically.
-__device__ __forceinline__ void sort_labels_warp(const int *lab, int L, int C, int *cnt, int *lpos_g, int *coff_g,
+// Class-sorted positions of the labels of one utterance (one warp, labels already staged in shared memory):
+// lpos[i] = rank of label i when labels are stably sorted by class; coff[c] = first position of class c.  Lets the
+// grad kernel reduce posteriors per class over contiguous shared-memory segments, deterministically.
+__device__ __forceinline__ void sort_labels_warp(const int *lab, int L, int C, int *cnt, int *lpos_s, int *coff_g,
                                                  int lane) {
-    for (int c = lane; c < C; c += 32) cnt[c] = 0;
+    for (int c = lane; c <= C; c += 32) cnt[c] = 0;
     __syncwarp();
-    for (int i = lane; i < L; i += 32) atomicAdd(&cnt[min(max(lab[i], 0), C - 1)], 1);
+    for (int i = lane; i < L; i += 32) atomicAdd(&cnt[lab[i]], 1);
     __syncwarp();
-    if (lane == 0) {
-        int run = 0;
-        for (int c = 0; c < C; ++c) {
-            const int n = cnt[c];
-            cnt[c] = run;
-            coff_g[c] = run;
-            run += n;
+    // exclusive prefix over the class counts: 32 classes per pass, shuffle scan
+    int run = 0;
+    for (int c0 = 0; c0 <= C; c0 += 32) {
+        const int c = c0 + lane;
+        const int n = (c < C) ? cnt[c] : 0;
+        int incl = n;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += o;
         }
-        coff_g[C] = run;
+        if (c <= C) {
+            cnt[c] = run + incl - n;
+            coff_g[c] = run + incl - n;
+        }
+        run += __shfl_sync(kFull, incl, 31);
     }
     __syncwarp();
     for (int base = 0; base < L; base += 32) {
         const int i = base + lane;
         const bool act = i < L;
-        const int c = act ? min(max(lab[i], 0), C - 1) : (-1 - lane);
+        const int c = act ? lab[i] : (-1 - lane);
         const unsigned m = __match_any_sync(kFull, c);
         const int rank = __popc(m & ((1u << lane) - 1u));
         const int start = act ? cnt[c] : 0;
         __syncwarp();
-        if (act) lpos_g[i] = start + rank;
+        if (act) lpos_s[i] = start + rank;
         if (act && rank == 0) cnt[c] = start + __popc(m);
         __syncwarp();
     }
 }
 
-// Utterance block of the prep kernels (128 threads): label offset, class-sorted order and the per-lattice-thread
-// label table (K = 8: thread e owns labels 4e .. 4e+3).  lps: shared int [Lmax]; cnt: shared int [C + 1].
-__device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *lps, int *cnt) {
+// Utterance block of the prep kernels (128 threads): label offset, class-sorted order, the per-lattice-thread label
+// table (K = 8: thread e owns labels 4e .. 4e+3) and the gradient kernel's reduction units.  The labels are staged in
+// shared memory first, so the block is three rounds of global latency (lengths, labels, results) rather than one
+// per label.  lps, labs: shared int [Lmax] each; cnt: shared int [C + 2].
+__device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *lps, int *labs, int *cnt) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int C = p.C;
-    int *s_off = cnt + C;
+    int *s_off = cnt + C + 1;
     if (tid == 0) *s_off = 0;
     __syncthreads();
     int part = 0;
@@ -158,19 +167,20 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
 #pragma unroll
     for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(kFull, part, d);
     if (lane == 0 && part) atomicAdd(s_off, part);
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
     __syncthreads();
     const int off = *s_off;
     if (tid == 0) p.laboff[b] = off;
-    const int L = min(max(p.label_lens[b], 0), p.Lmax);
-    const int *lab = p.labels + off;
+    for (int i = tid; i < L; i += blockDim.x) labs[i] = min(max(p.labels[off + i], 0), C - 1);
+    __syncthreads();
+    const int *lab = labs;
     if (warp == 0) sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
     __syncthreads();
-    if (!p.big && warp == 0) {
+    if (!p.big && warp == 1) {
         // Reduction units of the gradient kernel: every class segment of the sorted posterior row is cut into pieces
         // of <= kUnit positions (the blank's segment is the block of per-thread partial sums behind the labels), so
         // the per-class sums are formed by equal-sized, independent tasks instead of one serial walk per class.
-        // One lane per class, warp prefix sum over the unit counts.
-        const int *cf = p.coff + (size_t)b * (C + 1);
+        // One lane per class, warp prefix sum over the unit counts.  cnt[c] now holds the END of class c's segment.
         unsigned *un = p.units + (size_t)b * p.numax;
         int *cu = p.cu + (size_t)b * (C + 1);
         const int Lb = p.Lmax > 0 ? p.Lmax : 1;
@@ -180,8 +190,8 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
             const int c = c0 + lane;
             int s0 = 0, s1 = 0;
             if (c < C) {
-                s0 = cf[c];
-                s1 = cf[c + 1];
+                s1 = cnt[c];                       // end of the segment (start + count after the ranking pass)
+                s0 = (c > 0) ? cnt[c - 1] : 0;     // == start of class c: segments are contiguous
                 if (c == p.blank) { s0 = Lb; s1 = Lb + nq * 32; }
             }
             const int n = (s1 - s0 + kUnit - 1) / kUnit;
@@ -207,14 +217,13 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
         for (int h = 0; h < 4; ++h) {
             const int i = 4 * e + h;
             const bool valid = i < L;
-            int c = valid ? lab[i] : p.blank;
-            c = min(max(c, 0), C - 1);
+            const int c = valid ? lab[i] : min(max(p.blank, 0), C - 1);
             // emission-row index: the class itself, or (large alphabets) the label's own position 1 + i
             cls |= (unsigned)(p.big ? (valid ? 1 + i : 0) : c) << (8 * h);
             if (valid) {
                 bits |= 1u << (8 + h);
-                if (i == 0 || min(max(lab[i - 1], 0), C - 1) != c) bits |= 1u << h;            // skip into s
-                if (i + 1 < L && min(max(lab[i + 1], 0), C - 1) != c) bits |= 1u << (4 + h);  // skip out of s
+                if (i == 0 || lab[i - 1] != c) bits |= 1u << h;            // skip into s
+                if (i + 1 < L && lab[i + 1] != c) bits |= 1u << (4 + h);  // skip out of s
                 lp[h] = (unsigned)(p.big ? i : lps[i]);
             }
         }
@@ -251,22 +260,23 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     const long long nrows_total = (long long)p.T * p.B;
     const int nrb = (int)((nrows_total + kPrepRows - 1) / kPrepRows);
     const size_t rows_bytes = align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows;
-    const size_t utt_bytes = sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
+    const size_t utt_bytes = 2 * sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
     int *cnt = reinterpret_cast<int *>(smem + (rows_bytes > utt_bytes ? rows_bytes : utt_bytes));
 
-    if ((int)blockIdx.x >= nrb + p.B) {  // last CTA (present only when the launch is sliced): length bucketing
-        sort_by_length(p, reinterpret_cast<int *>(smem));
-        return;
-    }
-    if ((int)blockIdx.x >= nrb) {
-        prep_utterance(p, blockIdx.x - nrb, reinterpret_cast<int *>(smem), cnt);
+    // The utterance / sort blocks are long dependent chains of small loads: they take the LOWEST block indices so that
+    // they are scheduled first and run under the softmax blocks instead of forming the tail of the launch.
+    const int nextra = (int)gridDim.x - nrb;  // B utterance blocks (+1 sort block when the launch is sliced)
+    if ((int)blockIdx.x < nextra) {
+        if ((int)blockIdx.x == p.B)
+            sort_by_length(p, reinterpret_cast<int *>(smem));
+        else
+            prep_utterance(p, blockIdx.x, reinterpret_cast<int *>(smem),
+                           reinterpret_cast<int *>(smem) + (p.Lmax > 0 ? p.Lmax : 1), cnt);
         return;
     }
     // ---------------------------------------------------- row block: softmax of 128 consecutive (t,b) rows
     float *xs = reinterpret_cast<float *>(smem);
-    float *s_m = reinterpret_cast<float *>(smem + align16(sizeof(float) * kPrepRows * C));
-    float *s_inv = s_m + kPrepRows;
-    const long long row0 = (long long)blockIdx.x * kPrepRows;
+    const long long row0 = (long long)((int)blockIdx.x - nextra) * kPrepRows;
     const int nrows = (int)min((long long)kPrepRows, nrows_total - row0);
     const float *src = p.acts + row0 * C;
     const int n = nrows * C;
@@ -280,41 +290,43 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
         for (int i = tid; i < n; i += kPrepRows) xs[i] = __ldg(src + i);
     }
     __syncthreads();
-    {
-        float inv = -1.f, m = 0.f;
-        if (tid < nrows) {
-            const long long row = row0 + tid;
-            const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
-            if (t < min(max(p.act_lens[b], 0), p.T)) {
-                const float *x = xs + tid * C;
-                m = x[0];
-                for (int c = 1; c < C; ++c) m = fmaxf(m, x[c]);
-                float sum = 0.f;
-                for (int c = 0; c < C; ++c) sum += expf(x[c] - m);
-                inv = 1.0f / sum;
-            }
-        }
-        s_m[tid] = m;
-        s_inv[tid] = inv;
-    }
-    __syncthreads();
-    for (int r = warp; r < nrows; r += kPrepRows / 32) {
-        const float inv = s_inv[r];
-        const long long row = row0 + r;
-        if (inv < 0.f) {
-            // padding frame (t >= act_lens[b]): never read by the lattice kernels; its gradient row is zero
-            if (p.grads)
-                for (int c = lane; c < C; c += 32) p.grads[row * C + c] = 0.f;
-            continue;
-        }
-        const float m = s_m[r];
+    // Cp / 4 lanes per row (8 for C <= 32), 4 adjacent classes per lane: max and sum by shuffles inside the lane group,
+    // every exp evaluated once, the emission row written as two 16-byte stores per lane.
+    const int lpr = Cp >> 2, rpw = 32 / lpr;  // lanes per row, rows per warp pass
+    const int j = lane & (lpr - 1);
+    for (int r0 = warp * rpw; r0 < nrows; r0 += (kPrepRows / 32) * rpw) {
+        const int r = r0 + lane / lpr;
+        const bool valid = r < nrows;
+        const long long row = row0 + (valid ? r : 0);
         const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
-        unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * Cp;  // utterance-major: a tile of rows is one bulk copy
-        for (int c = lane; c < Cp; c += 32) {
+        const bool active = valid && t < min(max(p.act_lens[b], 0), p.T);
+        float x[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[i] = (valid && 4 * j + i < C) ? xs[r * C + 4 * j + i] : -INFINITY;
+        float m = fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3]));
+        for (int d = 1; d < lpr; d <<= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
+        if (!valid) m = 0.f;
+        float e[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) e[i] = (4 * j + i < C) ? expf(x[i] - m) : 0.f;
+        float sum = (e[0] + e[1]) + (e[2] + e[3]);
+        for (int d = 1; d < lpr; d <<= 1) sum += __shfl_xor_sync(kFull, sum, d);
+        const float inv = 1.0f / sum;
+        if (active) {
             // y clamped to >= 2^-126: a feasible alignment never gets probability exactly 0 from fp32 underflow
-            const float v = fmaxf(c < C ? expf(xs[r * C + c] - m) * inv : 0.f, 1.17549435e-38f);
-            ydst[c] = y_hi_word(v);
-            ydst[Cp + c] = y_lo_word(v);
+            unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * Cp;  // utterance-major: a tile of rows is one bulk copy
+            uint4 hi, lo;
+            float v = fmaxf(e[0] * inv, 1.17549435e-38f); hi.x = y_hi_word(v); lo.x = y_lo_word(v);
+            v = fmaxf(e[1] * inv, 1.17549435e-38f); hi.y = y_hi_word(v); lo.y = y_lo_word(v);
+            v = fmaxf(e[2] * inv, 1.17549435e-38f); hi.z = y_hi_word(v); lo.z = y_lo_word(v);
+            v = fmaxf(e[3] * inv, 1.17549435e-38f); hi.w = y_hi_word(v); lo.w = y_lo_word(v);
+            *reinterpret_cast<uint4 *>(ydst + 4 * j) = hi;
+            *reinterpret_cast<uint4 *>(ydst + Cp + 4 * j) = lo;
+        } else if (valid && p.grads) {
+            // padding frame (t >= act_lens[b]): never read by the lattice kernels; its gradient row is zero
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (4 * j + i < C) p.grads[row * C + 4 * j + i] = 0.f;
         }
     }
 }
@@ -1068,7 +1080,7 @@ __device__ __forceinline__ float block_reduce(float v, float *red, bool is_max) 
 }
 
 __host__ __device__ inline size_t prep_big_smem(int C, int Lmax) {
-    const size_t utt = sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1) + sizeof(int) * (C + 1) + 64;
+    const size_t utt = 2 * sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1) + sizeof(int) * (C + 2) + 64;
     return utt > 256 ? utt : 256;
 }
 
@@ -1080,7 +1092,8 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_utt_kernel(const CtcParams
         sort_by_length(p, lps);
         return;
     }
-    prep_utterance(p, blockIdx.x, lps, lps + (p.Lmax > 0 ? p.Lmax : 1));
+    const int Lp = p.Lmax > 0 ? p.Lmax : 1;
+    prep_utterance(p, blockIdx.x, lps, lps + Lp, lps + 2 * Lp);
 }
 
 template <int CP>

@@ -441,7 +441,8 @@ constexpr int kHostMinChunk = 8;  // utterances per slice below which slicing st
 struct ctcB200Context {
     float *d_acts = nullptr, *d_grads = nullptr, *d_costs = nullptr;
     void *d_ws = nullptr;
-    size_t n_acts = 0, n_grads = 0, n_costs = 0, n_ws = 0;
+    int *d_meta = nullptr, *h_meta = nullptr;  // [labels | label_lens | act_lens]: device copy, pinned staging
+    size_t n_acts = 0, n_grads = 0, n_costs = 0, n_ws = 0, n_meta = 0, n_hmeta = 0;
     cudaStream_t side[kHostChunks] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t done[kHostChunks] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t start = nullptr;
@@ -481,6 +482,8 @@ extern "C" ctcB200Status ctc_b200_destroy(ctcB200Context *c) {
     cudaFree(c->d_grads);
     cudaFree(c->d_costs);
     cudaFree(c->d_ws);
+    cudaFree(c->d_meta);
+    if (c->h_meta) cudaFreeHost(c->h_meta);
     for (int k = 0; k < kHostChunks; ++k) {
         if (c->side[k]) cudaStreamDestroy(c->side[k]);
         if (c->done[k]) cudaEventDestroy(c->done[k]);
@@ -499,14 +502,24 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
     ctcB200Options o;
     if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
     if (o.lengths_on_device) return CTC_B200_STATUS_INVALID_VALUE;
-    for (int b = 0; b < B; ++b)
-        if (label_lens[b] < 0) return CTC_B200_STATUS_INVALID_VALUE;
+    if (o.blank < 0 || o.blank >= C) return CTC_B200_STATUS_INVALID_VALUE;
+    // validate once for the whole batch (what ctc_b200_compute does for host lengths), then hand the kernels DEVICE
+    // copies of labels and lengths: one pinned staging copy instead of three pageable ones per slice
+    size_t total_labels = 0;
+    for (int b = 0; b < B; ++b) {
+        if (label_lens[b] < 0 || act_lens[b] < 0 || act_lens[b] > T) return CTC_B200_STATUS_INVALID_VALUE;
+        total_labels += (size_t)label_lens[b];
+    }
+    if (total_labels > 0 && !labels) return CTC_B200_STATUS_INVALID_VALUE;
+    for (size_t i = 0; i < total_labels; ++i)
+        if (labels[i] < 0 || labels[i] >= C || labels[i] == o.blank) return CTC_B200_STATUS_INVALID_VALUE;
 
     // ---- slices of utterances [b0, b0 + nb)
     int nch = B / kHostMinChunk;
     nch = nch < 1 ? 1 : (nch > kHostChunks ? kHostChunks : nch);
     int b0s[kHostChunks + 1];
     size_t ws_off[kHostChunks + 1], lab_off[kHostChunks + 1];
+    int mxs[kHostChunks];
     b0s[0] = 0; ws_off[0] = 0; lab_off[0] = 0;
     for (int k = 0; k < nch; ++k) {
         const int nb = B / nch + (k < B % nch ? 1 : 0);
@@ -518,8 +531,9 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
             nl += (size_t)label_lens[b];
         }
         lab_off[k + 1] = lab_off[k] + nl;
+        mxs[k] = mx;
         size_t wsb = 0;
-        ctcB200Status s = ctc_b200_workspace_size(T, nb, C, mx, &o, &wsb);
+        ctcB200Status s = ctc_b200_workspace_size(T, nb, C, mx > 0 ? mx : 1, &o, &wsb);
         if (s != CTC_B200_STATUS_SUCCESS) return s;
         ws_off[k + 1] = ws_off[k] + align256(wsb);
     }
@@ -535,8 +549,28 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         if (!grow(&pc, &c->n_costs, sizeof(float) * B)) { c->d_costs = nullptr; return CTC_B200_STATUS_MEMOPS_FAILED; }
         c->d_costs = (float *)pc;
         if (!grow(&c->d_ws, &c->n_ws, ws_off[nch])) return CTC_B200_STATUS_MEMOPS_FAILED;
+        void *pm = c->d_meta;
+        const size_t meta_bytes = sizeof(int) * (total_labels + 2 * (size_t)B);
+        if (!grow(&pm, &c->n_meta, meta_bytes)) { c->d_meta = nullptr; return CTC_B200_STATUS_MEMOPS_FAILED; }
+        c->d_meta = (int *)pm;
+        if (meta_bytes > c->n_hmeta) {
+            if (c->h_meta) cudaFreeHost(c->h_meta);
+            c->h_meta = nullptr;
+            c->n_hmeta = 0;
+            if (cudaHostAlloc((void **)&c->h_meta, meta_bytes, cudaHostAllocDefault) != cudaSuccess)
+                return CTC_B200_STATUS_MEMOPS_FAILED;
+            c->n_hmeta = meta_bytes;
+        }
     }
     cudaStream_t user = (cudaStream_t)o.stream;
+    // the previous call synchronised `user` before returning, so the staging buffer is free to overwrite
+    if (total_labels) memcpy(c->h_meta, labels, sizeof(int) * total_labels);
+    memcpy(c->h_meta + total_labels, label_lens, sizeof(int) * (size_t)B);
+    memcpy(c->h_meta + total_labels + B, act_lens, sizeof(int) * (size_t)B);
+    if (cudaMemcpyAsync(c->d_meta, c->h_meta, sizeof(int) * (total_labels + 2 * (size_t)B), cudaMemcpyHostToDevice,
+                        user) != cudaSuccess)
+        return CTC_B200_STATUS_MEMOPS_FAILED;
+    const int *d_labels = c->d_meta, *d_llen = c->d_meta + total_labels, *d_alen = c->d_meta + total_labels + B;
     if (nch > 1) {
         if (!make_streams(c)) return CTC_B200_STATUS_MEMOPS_FAILED;
         if (cudaEventRecord(c->start, user) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
@@ -556,8 +590,10 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
             return CTC_B200_STATUS_MEMOPS_FAILED;
         ctcB200Options ok = o;
         ok.stream = (void *)st;
-        ctcB200Status s = compute_impl(da, dg, labels ? labels + lab_off[k] : nullptr, label_lens + b0, act_lens + b0,
-                                       T, nb, C, c->d_costs + b0, static_cast<unsigned char *>(c->d_ws) + ws_off[k],
+        ok.lengths_on_device = 1;
+        ok.max_label_len = mxs[k] > 0 ? mxs[k] : 1;
+        ctcB200Status s = compute_impl(da, dg, d_labels + lab_off[k], d_llen + b0, d_alen + b0, T, nb, C,
+                                       c->d_costs + b0, static_cast<unsigned char *>(c->d_ws) + ws_off[k],
                                        ws_off[k + 1] - ws_off[k], &ok, false);
         if (s != CTC_B200_STATUS_SUCCESS) return s;
         launches += g_last_launches;

@@ -257,3 +257,18 @@ def test_host_buffer_entry(oracle, b200, B):
     if B == 33:
         oc, og = oracle.compute(d["acts"].numpy(), hl.numpy(), hal.numpy(), hll.numpy())
         assert np.abs(h_grads.numpy().astype(np.float64) - og).max() <= GRAD_ATOL
+
+
+def test_deterministic_headline_and_long(b200, monkeypatch):
+    # a race in shared memory (parked rows, posterior rows, in-place unit sums, slot rings) would show up as run-to-run
+    # or slicing-dependent bit differences on the shapes with the most warps and the most concurrency
+    for name in ("headline_b64_t1500", "long_b32_t4000"):
+        d = _wl(b200, name, seed=17)
+        c0, g0 = _run(b200, d)
+        for _ in range(2):
+            c1, g1 = _run(b200, d)
+            assert np.array_equal(c0, c1) and np.array_equal(g0, g1), name
+        monkeypatch.setenv("CTC_B200_SLICES", "1")
+        c2, g2 = _run(b200, d)
+        monkeypatch.delenv("CTC_B200_SLICES")
+        assert np.array_equal(c0, c2) and np.array_equal(g0, g2), name

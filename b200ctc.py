@@ -26,6 +26,8 @@ def _load():
 pkg = _load()
 CTCLoss = pkg.CTCLoss
 ctc_forward_backward = pkg.ctc_forward_backward
+GreedyDecoder = pkg.GreedyDecoder
+greedy_decode = pkg.greedy_decode
 last_launch_count = pkg.last_launch_count
 build = pkg.build
 Labels = pkg.Labels

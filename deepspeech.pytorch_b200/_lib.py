@@ -21,7 +21,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 EXPORTS = ("ctc_b200_get_version", "ctc_b200_status_string", "ctc_b200_default_options", "ctc_b200_workspace_size",
            "ctc_b200_compute", "ctc_b200_create", "ctc_b200_destroy", "ctc_b200_compute_host",
-           "ctc_b200_last_launch_count")
+           "ctc_b200_compute_decode", "ctc_b200_greedy_decode", "ctc_b200_last_launch_count")
 
 
 class CtcOptions(ctypes.Structure):
@@ -84,6 +84,11 @@ def load():
     lib.ctc_b200_destroy.restype = I
     lib.ctc_b200_compute_host.argtypes = [V, V, V, V, V, V, I, I, I, V, P(ctypes.c_double), P(CtcOptions)]
     lib.ctc_b200_compute_host.restype = I
+    lib.ctc_b200_compute_decode.argtypes = [V, V, V, V, V, I, I, I, V, V, ctypes.c_size_t, V, V, V, V, P(CtcOptions)]
+    lib.ctc_b200_compute_decode.restype = I
+    lib.ctc_b200_greedy_decode.argtypes = [V, ctypes.c_longlong, ctypes.c_longlong, V, I, I, I, V, V, V, V,
+                                           P(CtcOptions)]
+    lib.ctc_b200_greedy_decode.restype = I
     lib.ctc_b200_last_launch_count.restype = I
     _lib = lib
     return lib

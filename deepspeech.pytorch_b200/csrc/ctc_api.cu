@@ -213,6 +213,10 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         const int nrb = (int)((rows + kPrepRows - 1) / kPrepRows);
         ctc_prep_kernel<<<nrb + p.B + (pl.nslices > 1 ? 1 : 0), kPrepRows, pl.smem_prep, st>>>(p);
         ++*launches;
+        if (p.path && p.dec_ids) {
+            ctc_collapse_kernel<<<p.B, 32, 0, st>>>(p.path, p.act_lens, p.T, p.B, p.blank, p.dec_ids, p.dec_off, p.dec_len);
+            ++*launches;
+        }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
@@ -254,6 +258,10 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         ++*launches;
         ctc_prep_big_kernel<CP><<<(unsigned)rows, kBigThreads, 256, st>>>(p);
         ++*launches;
+        if (p.path && p.dec_ids) {
+            ctc_collapse_kernel<<<p.B, 32, 0, st>>>(p.path, p.act_lens, p.T, p.B, p.blank, p.dec_ids, p.dec_off, p.dec_len);
+            ++*launches;
+        }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
@@ -326,9 +334,14 @@ int ctc_b200_last_launch_count(void) { return g_last_launches; }
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------ compute
+struct DecodeOut {
+    int *path, *ids, *offsets, *out_lens;
+};
+
 static ctcB200Status compute_impl(const float *acts, float *grads, const int *labels, const int *label_lens,
                                   const int *act_lens, int T, int B, int C, float *costs, void *workspace,
-                                  size_t workspace_bytes, const ctcB200Options *opts_in, bool allow_slices) {
+                                  size_t workspace_bytes, const ctcB200Options *opts_in, bool allow_slices,
+                                  const DecodeOut *dec = nullptr) {
     g_last_launches = 0;
     ctcB200Options o;
     if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
@@ -415,6 +428,13 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.units = reinterpret_cast<unsigned *>(ws + pl.o_units);
     p.cu = reinterpret_cast<int *>(ws + pl.o_cu);
     p.numax = pl.numax;
+    if (dec) {
+        if (!dec->path || !dec->ids || !dec->out_lens) return CTC_B200_STATUS_INVALID_VALUE;
+        p.path = dec->path;
+        p.dec_ids = dec->ids;
+        p.dec_off = dec->offsets;
+        p.dec_len = dec->out_lens;
+    }
     p.bord = pl.nslices > 1 ? reinterpret_cast<int *>(ws + pl.o_bord) : nullptr;
     p.slice0 = 0;
 
@@ -429,6 +449,35 @@ extern "C" ctcB200Status ctc_b200_compute(const float *acts, float *grads, const
                                           size_t workspace_bytes, const ctcB200Options *opts_in) {
     return compute_impl(acts, grads, labels, label_lens, act_lens, T, B, C, costs, workspace, workspace_bytes, opts_in,
                         true);
+}
+
+extern "C" ctcB200Status ctc_b200_compute_decode(const float *acts, float *grads, const int *labels,
+                                                 const int *label_lens, const int *act_lens, int T, int B, int C,
+                                                 float *costs, void *workspace, size_t workspace_bytes, int *path,
+                                                 int *ids, int *offsets, int *out_lens, const ctcB200Options *opts_in) {
+    const DecodeOut dec = {path, ids, offsets, out_lens};
+    return compute_impl(acts, grads, labels, label_lens, act_lens, T, B, C, costs, workspace, workspace_bytes, opts_in,
+                        true, &dec);
+}
+
+extern "C" ctcB200Status ctc_b200_greedy_decode(const float *acts, long long stride_t, long long stride_b,
+                                                const int *act_lens_dev, int T, int B, int C, int *path, int *ids,
+                                                int *offsets, int *out_lens, const ctcB200Options *opts_in) {
+    g_last_launches = 0;
+    ctcB200Options o;
+    if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
+    if (!acts || !path || !ids || !out_lens) return CTC_B200_STATUS_INVALID_VALUE;
+    if (B < 1 || T < 0 || C < 2 || o.blank < 0 || o.blank >= C) return CTC_B200_STATUS_INVALID_VALUE;
+    cudaStream_t st = (cudaStream_t)o.stream;
+    const long long rows = (long long)T * B;
+    if (rows > 0) {
+        ctc_argmax_kernel<<<(unsigned)((rows + 15) / 16), 128, 0, st>>>(acts, stride_t, stride_b, act_lens_dev, T, B, C,
+                                                                        path);
+        ++g_last_launches;
+    }
+    ctc_collapse_kernel<<<B, 32, 0, st>>>(path, act_lens_dev, T, B, o.blank, ids, offsets, out_lens);
+    ++g_last_launches;
+    return cudaGetLastError() == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }
 
 // ------------------------------------------------------------------------------------------------ host-buffer path

@@ -50,8 +50,12 @@ def _as_i32(x, name: str) -> torch.Tensor:
 def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank: int = 0,
                          zero_infinity: bool = True, grad_scale: float = 1.0, want_grads: bool = True,
                          max_label_len: Optional[int] = None, phase_mask: int = 0,
-                         out_grads: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+                         out_grads: Optional[torch.Tensor] = None, decode: bool = False):
     """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
+
+    decode=True calls ctc_b200_compute_decode instead and returns (costs, grads, best) where best is the dict
+    {"path": int32 [B,T], "ids": int32 [B,T], "offsets": int32 [B,T], "lens": int32 [B]} (all CUDA): the greedy
+    decoding of the same logits (decoder.py:165-197 of the reference), a by-product of the softmax pass.
 
     No host synchronisation happens here when labels/lengths are CUDA tensors (then `max_label_len` is required);
     with CPU labels/lengths (the reference's calling convention) they are staged to the device inside the call.
@@ -96,11 +100,96 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
         ws_len = ws.numel() - (ws_ptr - ws.data_ptr())
         costs = torch.empty(B, dtype=torch.float32, device=dev)
         grads = (out_grads if out_grads is not None else torch.empty_like(acts_c)) if want_grads else None
+        if decode:
+            best = {"path": torch.zeros(B, T, dtype=torch.int32, device=dev),
+                    "ids": torch.zeros(B, T, dtype=torch.int32, device=dev),
+                    "offsets": torch.zeros(B, T, dtype=torch.int32, device=dev),
+                    "lens": torch.zeros(B, dtype=torch.int32, device=dev)}
+            st = lib.ctc_b200_compute_decode(acts_c.data_ptr(), grads.data_ptr() if want_grads else None,
+                                             labels.data_ptr() if labels.numel() else None, label_lens.data_ptr(),
+                                             act_lens.data_ptr(), T, B, C, costs.data_ptr(), ws_ptr, ws_len,
+                                             best["path"].data_ptr(), best["ids"].data_ptr(),
+                                             best["offsets"].data_ptr(), best["lens"].data_ptr(), ctypes.byref(opts))
+            _lib.check(st, "ctc_b200_compute_decode")
+            return costs, grads, best
         st = lib.ctc_b200_compute(acts_c.data_ptr(), grads.data_ptr() if want_grads else None,
                                   labels.data_ptr() if labels.numel() else None, label_lens.data_ptr(),
                                   act_lens.data_ptr(), T, B, C, costs.data_ptr(), ws_ptr, ws_len, ctypes.byref(opts))
         _lib.check(st, "ctc_b200_compute")
     return costs, grads
+
+
+def greedy_decode(acts: torch.Tensor, act_lens=None, blank: int = 0, batch_first: bool = False):
+    """Stand-alone ctc_b200_greedy_decode on the current CUDA stream.
+
+    acts: CUDA fp32 logits or probabilities, [T,B,C] (the loss layout) or, with batch_first=True, [B,T,C] (what the
+    reference hands its decoder, train.py:367,472,575); any tensor whose class axis is contiguous is read in place.
+    Returns {"path", "ids", "offsets": int32 [B,T], "lens": int32 [B]} on the device (no synchronisation).
+    """
+    if not (isinstance(acts, torch.Tensor) and acts.is_cuda and acts.dtype == torch.float32 and acts.dim() == 3):
+        raise ValueError("acts must be a CUDA float32 3-d tensor (no CPU fallback exists)")
+    lib = _lib.load()
+    a = acts.detach()
+    if a.stride(2) != 1:
+        a = a.contiguous()
+    if batch_first:
+        B, T, C = a.shape
+        sb, st_ = a.stride(0), a.stride(1)
+    else:
+        T, B, C = a.shape
+        st_, sb = a.stride(0), a.stride(1)
+    dev = a.device
+    lens = None
+    if act_lens is not None:
+        lens = _as_i32(act_lens, "act_lens").to(dev)
+        if lens.numel() != B:
+            raise ValueError("act_lens must have one entry per batch element")
+    opts = _lib.CtcOptions()
+    lib.ctc_b200_default_options(ctypes.byref(opts))
+    with torch.cuda.device(dev):
+        opts.stream = torch.cuda.current_stream(dev).cuda_stream
+        opts.blank = int(blank)
+        best = {"path": torch.zeros(B, T, dtype=torch.int32, device=dev),
+                "ids": torch.zeros(B, T, dtype=torch.int32, device=dev),
+                "offsets": torch.zeros(B, T, dtype=torch.int32, device=dev),
+                "lens": torch.zeros(B, dtype=torch.int32, device=dev)}
+        st = lib.ctc_b200_greedy_decode(a.data_ptr(), int(st_), int(sb), lens.data_ptr() if lens is not None else None,
+                                        T, B, C, best["path"].data_ptr(), best["ids"].data_ptr(),
+                                        best["offsets"].data_ptr(), best["lens"].data_ptr(), ctypes.byref(opts))
+        _lib.check(st, "ctc_b200_greedy_decode")
+    return best
+
+
+class GreedyDecoder:
+    """Drop-in for the reference's `decoder.GreedyDecoder` (decoder.py:145-197) on the B200 path.
+
+        decoder = GreedyDecoder(labels, blank_index=labels.index('_'))        # test.py:80, train.py:880
+        strings, offsets = decoder.decode(probs, sizes)                       # train.py:367,472,575
+
+    `decode` takes the same batch-first [B,T,C] tensor (probabilities or logits: the argmax is the same) and returns
+    the same nested lists -- `strings[b] == [text]`, `offsets[b] == [IntTensor]` -- but the per-frame argmax, the
+    repeat/blank collapse and the offsets are computed on the device; only the collapsed ids cross to the host.
+    """
+
+    def __init__(self, labels, blank_index: int = 0):
+        self.labels = labels
+        self.int_to_char = dict(enumerate(labels))
+        self.blank_index = blank_index
+        self.space_index = labels.index(" ") if " " in labels else len(labels)
+
+    def decode_ids(self, probs: torch.Tensor, sizes=None, batch_first: bool = True):
+        return greedy_decode(probs, sizes, blank=self.blank_index, batch_first=batch_first)
+
+    def strings_from(self, best):
+        ids, offs, lens = best["ids"].cpu(), best["offsets"].cpu(), best["lens"].cpu().tolist()
+        strings, offsets = [], []
+        for b, n in enumerate(lens):
+            strings.append(["".join(self.int_to_char[int(i)] for i in ids[b, :n].tolist())])
+            offsets.append([offs[b, :n].to(torch.int)])
+        return strings, offsets
+
+    def decode(self, probs: torch.Tensor, sizes=None):
+        return self.strings_from(self.decode_ids(probs, sizes, batch_first=True))
 
 
 def last_launch_count() -> int:

@@ -109,6 +109,31 @@ ctcB200Status ctc_b200_compute_host(ctcB200Context *ctx, const float *acts_host,
                                     const int *labels, const int *label_lens, const int *act_lens, int T, int B,
                                     int C, float *costs_host, double *loss_sum, const ctcB200Options *opts);
 
+/*
+ * Greedy (best-path) decoding of the same logits -- the first "next" row of the scope table.
+ * Replaces GreedyDecoder.decode (/root/reference/decoder.py:182-197: argmax over the classes of every frame) and
+ * process_string (decoder.py:165-180: drop blanks and frames equal to the previous frame; the offset of a kept
+ * character is its frame index), which the reference runs in Python on every training batch (train.py:575) and
+ * eval batch (train.py:367,472).  Integer results, bit-exact against oracle/greedy_oracle.py; ties in a frame go to
+ * the lowest class index (torch.max).
+ *   path     : DEVICE int32 [B][T], receives the argmax class of every valid frame (the reference's `max_probs`)
+ *   ids      : DEVICE int32 [B][T], receives the collapsed sequence of utterance b in ids[b*T .. b*T + out_lens[b])
+ *   offsets  : DEVICE int32 [B][T] or NULL, frame index of every kept character
+ *   out_lens : DEVICE int32 [B]
+ * ctc_b200_compute_decode = ctc_b200_compute + the decode outputs, produced from the softmax pass that reads the
+ * logits anyway (no second read).  ctc_b200_greedy_decode is the stand-alone form for eval: element (t,b,c) of
+ * `acts` is read at acts[t*stride_t + b*stride_b + c], so both the loss layout [T,B,C] (stride_t = B*C, stride_b = C)
+ * and the reference decoder's batch-first [B,T,C] (stride_t = C, stride_b = T*C) work in place; act_lens is a
+ * DEVICE int32 [B] or NULL (= T for every utterance).  Both enqueue on opts->stream and return.
+ */
+ctcB200Status ctc_b200_compute_decode(const float *acts, float *grads, const int *labels, const int *label_lens,
+                                      const int *act_lens, int T, int B, int C, float *costs, void *workspace,
+                                      size_t workspace_bytes, int *path, int *ids, int *offsets, int *out_lens,
+                                      const ctcB200Options *opts);
+ctcB200Status ctc_b200_greedy_decode(const float *acts, long long stride_t, long long stride_b,
+                                     const int *act_lens_dev, int T, int B, int C, int *path, int *ids, int *offsets,
+                                     int *out_lens, const ctcB200Options *opts);
+
 /* number of kernel launches the last ctc_b200_compute on this thread enqueued (bench.py's gpu_launches claim) */
 int ctc_b200_last_launch_count(void);
 

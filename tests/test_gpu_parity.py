@@ -272,3 +272,55 @@ def test_deterministic_headline_and_long(b200, monkeypatch):
         c2, g2 = _run(b200, d)
         monkeypatch.delenv("CTC_B200_SLICES")
         assert np.array_equal(c0, c2) and np.array_equal(g0, g2), name
+
+
+def _greedy_check(best, path, ids, offs, act_lens):
+    lens = best["lens"].cpu().numpy()
+    assert lens.tolist() == [len(i) for i in ids]
+    gp, gi, go_ = best["path"].cpu().numpy(), best["ids"].cpu().numpy(), best["offsets"].cpu().numpy()
+    for b in range(len(ids)):
+        n = gp.shape[1] if act_lens is None else int(act_lens[b])
+        assert np.array_equal(gp[b, :n], path[b, :n]), b
+        assert gi[b, :lens[b]].tolist() == ids[b] and go_[b, :lens[b]].tolist() == offs[b], b
+
+
+def test_greedy_decode_matches_reference_goldens(b200):
+    # stand-alone entry on the reference decoder's own batch-first input; bit-exact integers
+    import glob
+    import os
+    for f in sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "greedy_*.npz"))):
+        z = np.load(f)
+        labels = str(z["labels"])
+        dec = b200.GreedyDecoder(labels, blank_index=int(z["blank"]))
+        probs = torch.from_numpy(z["probs_btc"]).cuda()
+        strings, offsets = dec.decode(probs, torch.from_numpy(z["sizes"]))
+        assert [s[0] for s in strings] == [str(s) for s in z["strings"]], f
+        assert np.array_equal(np.concatenate([o[0].numpy() for o in offsets]), z["offsets"]), f
+        # same through the loss layout [T,B,C] (a transposed, non-contiguous view is read in place)
+        best = b200.greedy_decode(probs.transpose(0, 1), torch.from_numpy(z["sizes"]), blank=int(z["blank"]))
+        assert best["lens"].cpu().numpy().tolist() == z["lens"].tolist()
+
+
+@pytest.mark.parametrize("name", ["cpu_b16_t500", "headline_b64_t1500"])
+def test_fused_decode_is_a_by_product(oracle, b200, name):
+    # ctc_b200_compute_decode: identical costs / gradients, plus the greedy decoding of the same logits
+    from oracle import greedy_oracle as go
+    d = _wl(b200, name, seed=23)
+    acts = d["acts"].cuda()
+    c0, g0 = b200.ctc_forward_backward(acts, d["labels"], d["act_lens"], d["label_lens"])
+    c1, g1, best = b200.ctc_forward_backward(acts, d["labels"], d["act_lens"], d["label_lens"], decode=True)
+    torch.cuda.synchronize()
+    assert torch.equal(c0, c1) and torch.equal(g0, g1)
+    path, ids, offs = go.decode(d["acts"].numpy(), d["act_lens"].numpy(), 0)
+    _greedy_check(best, path, ids, offs, d["act_lens"].numpy())
+    alone = b200.greedy_decode(acts, d["act_lens"], blank=0)
+    _greedy_check(alone, path, ids, offs, d["act_lens"].numpy())
+
+
+def test_fused_decode_large_alphabet(b200):
+    from oracle import greedy_oracle as go
+    w = b200.workloads.Workload("bigdec", 6, 90, 700, 20, 0.05, 0.2)
+    d = b200.workloads.make(w, seed=29)
+    _, _, best = b200.ctc_forward_backward(d["acts"].cuda(), d["labels"], d["act_lens"], d["label_lens"], decode=True)
+    path, ids, offs = go.decode(d["acts"].numpy(), d["act_lens"].numpy(), 0)
+    _greedy_check(best, path, ids, offs, d["act_lens"].numpy())

@@ -6,7 +6,8 @@ import os
 import numpy as np
 import pytest
 
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLDEN = sorted(f for f in glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz"))
+                if not os.path.basename(f).startswith("greedy_"))
 
 
 def test_golden_present():
@@ -93,3 +94,23 @@ def test_numeric_model_of_kernel_scheme(oracle):
                 assert np.abs(grad - grads[:, 0]).max() <= bound
             else:
                 assert costs[0] == 0.0
+
+
+def _greedy_golden():
+    import glob
+    import os
+    files = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "greedy_*.npz")))
+    assert len(files) == 3
+    return [np.load(f) for f in files]
+
+
+def test_greedy_oracle_against_reference_decoder_goldens():
+    # tests/golden/greedy_*.npz were produced by the reference's own decoder.py (make_golden_greedy.py)
+    from oracle import greedy_oracle as go
+    for z in _greedy_golden():
+        probs = z["probs_btc"]
+        path, ids, offs = go.decode(np.ascontiguousarray(probs.transpose(1, 0, 2)), z["sizes"], int(z["blank"]))
+        assert np.array_equal(path, z["path"])
+        assert go.to_strings(ids, str(z["labels"])) == [str(s) for s in z["strings"]]
+        assert [len(i) for i in ids] == z["lens"].tolist()
+        assert np.array_equal(np.concatenate([np.asarray(o, np.int32) for o in offs]), z["offsets"])

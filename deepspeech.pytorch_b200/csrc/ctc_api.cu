@@ -154,13 +154,22 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
 // Engine + gradient launches, cut into length-bucket slices on the pool's side streams (forked from and joined back
 // to the caller's stream with events, so the caller sees ordinary stream semantics and graph capture still works).
 // All engines are enqueued before any gradient kernel: the longest slice (rank 0..) starts first.
+// The collapse of the best path (decode by-product of the prep kernel) is independent of the lattice kernels: it is
+// enqueued behind the engine of the LAST slice (the shortest utterances, far from the critical path).
+inline void launch_collapse(const CtcParams &p, cudaStream_t s, int *launches) {
+    if (!p.path || !p.dec_ids) return;
+    ctc_collapse_kernel<<<p.B, kCollapseThreads, 0, s>>>(p.path, p.act_lens, p.T, p.B, p.blank, p.dec_ids, p.dec_off,
+                                                         p.dec_len);
+    ++*launches;
+}
+
 template <typename EngineLaunch, typename GradLaunch>
 cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, bool do_engine, bool do_grad,
-                          EngineLaunch eng, GradLaunch grd) {
-    if (!do_engine && !do_grad) return cudaSuccess;
-    if (pl.nslices <= 1) {
+                          int *launches, EngineLaunch eng, GradLaunch grd) {
+    if (pl.nslices <= 1 || (!do_engine && !do_grad)) {
         if (do_engine) eng(p, p.B, st);
         if (do_grad) grd(p, p.B, st);
+        launch_collapse(p, st, launches);
         return cudaGetLastError();
     }
     int dev = 0;
@@ -181,6 +190,7 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
             const int nb = (int)((long long)p.B * (k + 1) / ns) - pk.slice0;
             if (pass == 0) eng(pk, nb, sp->side[k]); else grd(pk, nb, sp->side[k]);
         }
+        if (pass == 0) launch_collapse(p, sp->side[ns - 1], launches);
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     for (int k = 0; k < ns; ++k) {
@@ -213,17 +223,13 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         const int nrb = (int)((rows + kPrepRows - 1) / kPrepRows);
         ctc_prep_kernel<<<nrb + p.B + (pl.nslices > 1 ? 1 : 0), kPrepRows, pl.smem_prep, st>>>(p);
         ++*launches;
-        if (p.path && p.dec_ids) {
-            ctc_collapse_kernel<<<p.B, 32, 0, st>>>(p.path, p.act_lens, p.T, p.B, p.blank, p.dec_ids, p.dec_off, p.dec_len);
-            ++*launches;
-        }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
     const bool do_engine = !(phase_mask & 1);
     const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
     return launch_sliced(
-        p, pl, st, do_engine, do_grad,
+        p, pl, st, do_engine, do_grad, launches,
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
             ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
@@ -258,17 +264,13 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         ++*launches;
         ctc_prep_big_kernel<CP><<<(unsigned)rows, kBigThreads, 256, st>>>(p);
         ++*launches;
-        if (p.path && p.dec_ids) {
-            ctc_collapse_kernel<<<p.B, 32, 0, st>>>(p.path, p.act_lens, p.T, p.B, p.blank, p.dec_ids, p.dec_off, p.dec_len);
-            ++*launches;
-        }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
     const bool do_engine = !(phase_mask & 1);
     const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
     e = launch_sliced(
-        p, pl, st, do_engine, do_grad,
+        p, pl, st, do_engine, do_grad, launches,
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
             ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
@@ -475,7 +477,7 @@ extern "C" ctcB200Status ctc_b200_greedy_decode(const float *acts, long long str
                                                                         path);
         ++g_last_launches;
     }
-    ctc_collapse_kernel<<<B, 32, 0, st>>>(path, act_lens_dev, T, B, o.blank, ids, offsets, out_lens);
+    ctc_collapse_kernel<<<B, kCollapseThreads, 0, st>>>(path, act_lens_dev, T, B, o.blank, ids, offsets, out_lens);
     ++g_last_launches;
     return cudaGetLastError() == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }

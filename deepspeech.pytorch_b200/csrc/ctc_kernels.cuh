@@ -1252,29 +1252,52 @@ __global__ void __launch_bounds__(128) ctc_argmax_kernel(const float *acts, long
     if (active && j == 0) path[(size_t)b * T + t] = arg;
 }
 
-// Collapse of the best path, one warp per utterance: keep frame t iff path[t] != blank and (t == 0 or path[t] !=
-// path[t-1]); order-preserving compaction by ballot + popc with a running offset.
-__global__ void __launch_bounds__(32) ctc_collapse_kernel(const int *path, const int *act_lens, int T, int B, int blank,
-                                                          int *ids, int *offsets, int *out_lens) {
-    const int b = blockIdx.x, lane = threadIdx.x;
+// Collapse of the best path, one CTA of 128 threads per utterance: keep frame t iff path[t] != blank and (t == 0 or
+// path[t] != path[t-1]).  Every thread owns a contiguous segment of frames: count its survivors, block-wide exclusive
+// scan of the counts (shuffle scan per warp + 4 partial sums), then write ids / offsets in order.  Two short rounds
+// of independent loads instead of a serial walk over T.
+constexpr int kCollapseThreads = 128;
+__global__ void __launch_bounds__(kCollapseThreads) ctc_collapse_kernel(const int *path, const int *act_lens, int T,
+                                                                        int B, int blank, int *ids, int *offsets,
+                                                                        int *out_lens) {
+    __shared__ int wsum[kCollapseThreads / 32];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int Tb = act_lens ? min(max(act_lens[b], 0), T) : T;
     const int *pb = path + (size_t)b * T;
-    int n = 0;
-    for (int t0 = 0; t0 < Tb; t0 += 32) {
-        const int t = t0 + lane;
-        const int a = t < Tb ? pb[t] : blank;
-        int prev = __shfl_up_sync(kFull, a, 1);
-        if (lane == 0) prev = t0 > 0 ? pb[t0 - 1] : -1;
-        const bool keep = t < Tb && a != blank && a != prev;
-        const unsigned m = __ballot_sync(kFull, keep);
-        if (keep) {
-            const int pos = n + __popc(m & ((1u << lane) - 1u));
-            ids[(size_t)b * T + pos] = a;
-            if (offsets) offsets[(size_t)b * T + pos] = t;
+    const int seg = (Tb + kCollapseThreads - 1) / kCollapseThreads;
+    const int t0 = min(tid * seg, Tb), t1 = min(t0 + seg, Tb);
+    int cnt = 0;
+    {
+        int prev = t0 > 0 ? pb[t0 - 1] : -1;
+        for (int t = t0; t < t1; ++t) {
+            const int a = pb[t];
+            cnt += (a != blank && a != prev) ? 1 : 0;
+            prev = a;
         }
-        n += __popc(m);
     }
-    if (lane == 0) out_lens[b] = n;
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(kFull, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int pos = incl - cnt;
+    for (int w = 0; w < warp; ++w) pos += wsum[w];
+    {
+        int prev = t0 > 0 ? pb[t0 - 1] : -1;
+        for (int t = t0; t < t1; ++t) {
+            const int a = pb[t];
+            if (a != blank && a != prev) {
+                ids[(size_t)b * T + pos] = a;
+                if (offsets) offsets[(size_t)b * T + pos] = t;
+                ++pos;
+            }
+            prev = a;
+        }
+    }
+    if (tid == kCollapseThreads - 1) out_lens[b] = pos;
 }
 
 }  // namespace ctcb200

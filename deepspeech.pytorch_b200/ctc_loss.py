@@ -101,10 +101,7 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
         costs = torch.empty(B, dtype=torch.float32, device=dev)
         grads = (out_grads if out_grads is not None else torch.empty_like(acts_c)) if want_grads else None
         if decode:
-            best = {"path": torch.zeros(B, T, dtype=torch.int32, device=dev),
-                    "ids": torch.zeros(B, T, dtype=torch.int32, device=dev),
-                    "offsets": torch.zeros(B, T, dtype=torch.int32, device=dev),
-                    "lens": torch.zeros(B, dtype=torch.int32, device=dev)}
+            best = _decode_buffers(B, T, dev)
             st = lib.ctc_b200_compute_decode(acts_c.data_ptr(), grads.data_ptr() if want_grads else None,
                                              labels.data_ptr() if labels.numel() else None, label_lens.data_ptr(),
                                              act_lens.data_ptr(), T, B, C, costs.data_ptr(), ws_ptr, ws_len,
@@ -117,6 +114,12 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
                                   act_lens.data_ptr(), T, B, C, costs.data_ptr(), ws_ptr, ws_len, ctypes.byref(opts))
         _lib.check(st, "ctc_b200_compute")
     return costs, grads
+
+
+def _decode_buffers(B: int, T: int, dev) -> dict:
+    """Outputs of the decode entries; only path[b, :act_len], ids/offsets[b, :lens[b]] and lens are defined."""
+    buf = torch.empty(3, B, T, dtype=torch.int32, device=dev)
+    return {"path": buf[0], "ids": buf[1], "offsets": buf[2], "lens": torch.empty(B, dtype=torch.int32, device=dev)}
 
 
 def greedy_decode(acts: torch.Tensor, act_lens=None, blank: int = 0, batch_first: bool = False):
@@ -149,10 +152,7 @@ def greedy_decode(acts: torch.Tensor, act_lens=None, blank: int = 0, batch_first
     with torch.cuda.device(dev):
         opts.stream = torch.cuda.current_stream(dev).cuda_stream
         opts.blank = int(blank)
-        best = {"path": torch.zeros(B, T, dtype=torch.int32, device=dev),
-                "ids": torch.zeros(B, T, dtype=torch.int32, device=dev),
-                "offsets": torch.zeros(B, T, dtype=torch.int32, device=dev),
-                "lens": torch.zeros(B, dtype=torch.int32, device=dev)}
+        best = _decode_buffers(B, T, dev)
         st = lib.ctc_b200_greedy_decode(a.data_ptr(), int(st_), int(sb), lens.data_ptr() if lens is not None else None,
                                         T, B, C, best["path"].data_ptr(), best["ids"].data_ptr(),
                                         best["offsets"].data_ptr(), best["lens"].data_ptr(), ctypes.byref(opts))

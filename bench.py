@@ -161,8 +161,16 @@ def run_b200(args, w):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    # every rank: its own batch of the workload shape (weak scaling); rank r uses seed 1234 + r
-    d = b200ctc.workloads.make(w, seed=1234 + rank)
+    if args.global_batch and world > 1:
+        # BASELINE config 5: ONE global batch of the workload shape, dealt to the ranks by lattice work
+        # (sharding.length_bucketed_shards: LPT, equal shard sizes) -- strong scaling, no data-path collective
+        dg = b200ctc.workloads.make(w, seed=1234)
+        ids = b200ctc.sharding.length_bucketed_shards(dg["act_lens"].tolist(), dg["label_lens"].tolist(), world)[rank]
+        a_, l_, al_, ll_ = b200ctc.sharding.take_shard(dg["acts"], dg["labels"], dg["act_lens"], dg["label_lens"], ids)
+        d = {"acts": a_, "labels": l_, "act_lens": al_, "label_lens": ll_, "T": dg["T"], "B": len(ids), "C": dg["C"]}
+    else:
+        # every rank: its own batch of the workload shape (weak scaling); rank r uses seed 1234 + r
+        d = b200ctc.workloads.make(w, seed=1234 + rank)
     T, B, C = d["T"], d["B"], d["C"]
     frames = T * B
     acts = d["acts"].to(dev)
@@ -172,14 +180,28 @@ def run_b200(args, w):
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
     loss_acc = torch.zeros(1, dtype=torch.float32, device=dev)
 
+    comm = torch.cuda.Stream(device=dev) if world > 1 else None
+    ready = torch.cuda.Event() if world > 1 else None
+
     def step(phase_mask=0):
+        if phase_mask or world == 1:
+            costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
+                                                    phase_mask=phase_mask)
+            if phase_mask == 0:
+                loss_acc.copy_(costs.sum().reshape(1))
+            return
+        # N > 1: the path's one exchange -- the summed loss over NVLink (NCCL) -- starts on a communication stream
+        # as soon as the costs are final (`costs_ready`: recursions done) and overlaps the gradient kernels; the
+        # compute stream joins it at the end of the step, so the step still contains the whole exchange.
         costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
-                                                phase_mask=phase_mask)
-        if phase_mask == 0:
+                                                costs_ready=ready)
+        with torch.cuda.stream(comm):
+            comm.wait_event(ready)
             s = costs.sum().reshape(1)
-            if world > 1:
-                dist.all_reduce(s)  # the path's one exchange: summed loss over NVLink (NCCL)
+            dist.all_reduce(s)
             loss_acc.copy_(s)
+        costs.record_stream(comm)
+        torch.cuda.current_stream(dev).wait_stream(comm)
 
     def timed(nsteps, phase_mask=0):
         evs = []
@@ -277,7 +299,8 @@ def run_b200(args, w):
                    "sample": f"oracle fp32 OpenMP port, full batch B={B} T={T} C={C}, best of 3 ({mean_s:.2f} s each)"}
         line = {"metric": METRIC, "value": frames * world / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_per_step,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "higher_is_better": True, "scaling": "strong" if (args.global_batch and world > 1) else "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": dict(workload_config(w, d), l2="flushed (256 MB memset) between timed steps",
                                lengths="device-resident (no host sync in the step)",
                                launch="8 length-bucket slices on side streams (CTC_B200_SLICES)"),
@@ -303,6 +326,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None)
+    ap.add_argument("--global-batch", action="store_true",
+                    help="N>1: shard ONE global batch of the workload over the ranks (strong scaling, BASELINE config 5)")
     args = ap.parse_args()
     import b200ctc
     w = b200ctc.workloads.CONFIGS[args.workload or b200ctc.workloads.HEADLINE]

@@ -30,8 +30,8 @@ constexpr int kMaxSlices = 8;
 constexpr int kMinSliceB = 8;  // utterances per slice below which slicing stops paying
 struct SidePool {
     bool ok = false;
-    cudaStream_t side[kMaxSlices];
-    cudaEvent_t fork, join[kMaxSlices];
+    cudaStream_t side[kMaxSlices], aux;
+    cudaEvent_t fork, join[kMaxSlices], eng_done[kMaxSlices], aux_done;
 };
 SidePool g_pool[64];
 std::mutex g_pool_mu;  // held while a sliced launch is being enqueued: the pool's events are shared by all callers
@@ -41,9 +41,12 @@ SidePool *side_pool(int dev) {
     SidePool &sp = g_pool[dev];
     if (sp.ok) return &sp;
     if (cudaEventCreateWithFlags(&sp.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&sp.aux_done, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaStreamCreateWithFlags(&sp.aux, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     for (int k = 0; k < kMaxSlices; ++k) {
         if (cudaStreamCreateWithFlags(&sp.side[k], cudaStreamNonBlocking) != cudaSuccess) return nullptr;
         if (cudaEventCreateWithFlags(&sp.join[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&sp.eng_done[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
     }
     sp.ok = true;
     return &sp;
@@ -165,9 +168,10 @@ inline void launch_collapse(const CtcParams &p, cudaStream_t s, int *launches) {
 
 template <typename EngineLaunch, typename GradLaunch>
 cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, bool do_engine, bool do_grad,
-                          int *launches, EngineLaunch eng, GradLaunch grd) {
+                          int *launches, cudaEvent_t costs_ready, EngineLaunch eng, GradLaunch grd) {
     if (pl.nslices <= 1 || (!do_engine && !do_grad)) {
         if (do_engine) eng(p, p.B, st);
+        if (costs_ready && cudaEventRecord(costs_ready, st) != cudaSuccess) return cudaErrorUnknown;
         if (do_grad) grd(p, p.B, st);
         launch_collapse(p, st, launches);
         return cudaGetLastError();
@@ -190,7 +194,20 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
             const int nb = (int)((long long)p.B * (k + 1) / ns) - pk.slice0;
             if (pass == 0) eng(pk, nb, sp->side[k]); else grd(pk, nb, sp->side[k]);
         }
-        if (pass == 0) launch_collapse(p, sp->side[ns - 1], launches);
+        if (pass == 0) {
+            if (costs_ready) {
+                // costs[] is final once every slice's recursion is done: gather those points on the aux stream and
+                // record the caller's event there; the gradient kernels are enqueued behind this and run on
+                for (int k = 0; k < ns; ++k) {
+                    if ((e = cudaEventRecord(sp->eng_done[k], sp->side[k])) != cudaSuccess) return e;
+                    if ((e = cudaStreamWaitEvent(sp->aux, sp->eng_done[k], 0)) != cudaSuccess) return e;
+                }
+                if ((e = cudaEventRecord(costs_ready, sp->aux)) != cudaSuccess) return e;
+                if ((e = cudaEventRecord(sp->aux_done, sp->aux)) != cudaSuccess) return e;
+                if ((e = cudaStreamWaitEvent(st, sp->aux_done, 0)) != cudaSuccess) return e;
+            }
+            launch_collapse(p, sp->side[ns - 1], launches);
+        }
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     for (int k = 0; k < ns; ++k) {
@@ -201,7 +218,8 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
 }
 
 template <int CP>
-cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
+cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
+                          cudaEvent_t costs_ready) {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -229,7 +247,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
     const bool do_engine = !(phase_mask & 1);
     const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
     return launch_sliced(
-        p, pl, st, do_engine, do_grad, launches,
+        p, pl, st, do_engine, do_grad, launches, costs_ready,
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
             ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
@@ -240,7 +258,8 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         });
 }
 
-cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
+cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
+                       cudaEvent_t costs_ready) {
     constexpr int CP = 256;
     static bool attr_set[64] = {false};
     int dev = 0;
@@ -270,7 +289,7 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
     const bool do_engine = !(phase_mask & 1);
     const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
     e = launch_sliced(
-        p, pl, st, do_engine, do_grad, launches,
+        p, pl, st, do_engine, do_grad, launches, costs_ready,
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
             ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
@@ -288,12 +307,13 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
     return e;
 }
 
-cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches) {
-    if (pl.big) return launch_big(p, pl, st, phase_mask, launches);
+cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
+                       cudaEvent_t costs_ready) {
+    if (pl.big) return launch_big(p, pl, st, phase_mask, launches, costs_ready);
     switch (pl.Cp) {
-        case 32: return launch_all_cp<32>(p, pl, st, phase_mask, launches);
-        case 64: return launch_all_cp<64>(p, pl, st, phase_mask, launches);
-        default: return launch_all_cp<128>(p, pl, st, phase_mask, launches);
+        case 32: return launch_all_cp<32>(p, pl, st, phase_mask, launches, costs_ready);
+        case 64: return launch_all_cp<64>(p, pl, st, phase_mask, launches, costs_ready);
+        default: return launch_all_cp<128>(p, pl, st, phase_mask, launches, costs_ready);
     }
 }
 
@@ -441,7 +461,7 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.slice0 = 0;
 
     int launches = 0;
-    cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches);
+    cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches, (cudaEvent_t)o.costs_ready);
     g_last_launches = launches;
     return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }
@@ -642,6 +662,7 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         ctcB200Options ok = o;
         ok.stream = (void *)st;
         ok.lengths_on_device = 1;
+        ok.costs_ready = nullptr;  // meaningless here: the call synchronises before it returns
         ok.max_label_len = mxs[k] > 0 ? mxs[k] : 1;
         ctcB200Status s = compute_impl(da, dg, d_labels + lab_off[k], d_llen + b0, d_alen + b0, T, nb, C,
                                        c->d_costs + b0, static_cast<unsigned char *>(c->d_ws) + ws_off[k],

@@ -50,8 +50,12 @@ def _as_i32(x, name: str) -> torch.Tensor:
 def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank: int = 0,
                          zero_infinity: bool = True, grad_scale: float = 1.0, want_grads: bool = True,
                          max_label_len: Optional[int] = None, phase_mask: int = 0,
-                         out_grads: Optional[torch.Tensor] = None, decode: bool = False):
+                         out_grads: Optional[torch.Tensor] = None, decode: bool = False,
+                         costs_ready: Optional[torch.cuda.Event] = None):
     """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
+
+    costs_ready: an event the library records as soon as `costs` is final (all recursions done, gradient kernels
+    still running) -- wait on it from a communication stream to overlap the loss all-reduce with the gradient pass.
 
     decode=True calls ctc_b200_compute_decode instead and returns (costs, grads, best) where best is the dict
     {"path": int32 [B,T], "ids": int32 [B,T], "offsets": int32 [B,T], "lens": int32 [B]} (all CUDA): the greedy
@@ -92,6 +96,10 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
                 lmax = max(lmax, int(max_label_len))
         opts.max_label_len = lmax
         opts.phase_mask = int(phase_mask)
+        if costs_ready is not None:
+            if not costs_ready.cuda_event:  # torch creates the CUDA event lazily, on its first record
+                costs_ready.record()
+            opts.costs_ready = costs_ready.cuda_event
         nbytes = ctypes.c_size_t(0)
         _lib.check(lib.ctc_b200_workspace_size(T, B, C, lmax, ctypes.byref(opts), ctypes.byref(nbytes)),
                    "ctc_b200_workspace_size")

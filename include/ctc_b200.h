@@ -63,7 +63,12 @@ typedef struct {
                               the gradient kernel, bit2 = skip the softmax/prep kernel; a skipped phase reuses what
                               the previous full call left in the workspace (bench.py times each kernel alone with
                               CUDA events this way) */
-    int reserved[3];       /* must be zero */
+    int reserved0;         /* must be zero */
+    void *costs_ready;     /* cudaEvent_t or NULL.  If set, the event is recorded (on an internal stream) as soon as
+                              costs[] is final, i.e. when the recursion kernels of every slice have finished -- well
+                              before the gradient kernels do.  A caller that all-reduces the summed loss (the path's
+                              one collective) waits on it from its communication stream and overlaps the exchange
+                              with the gradient pass instead of serialising it behind the call. */
 } ctcB200Options;
 
 /* replaces get_warpctc_version() */

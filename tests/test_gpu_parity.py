@@ -324,3 +324,21 @@ def test_fused_decode_large_alphabet(b200):
     _, _, best = b200.ctc_forward_backward(d["acts"].cuda(), d["labels"], d["act_lens"], d["label_lens"], decode=True)
     path, ids, offs = go.decode(d["acts"].numpy(), d["act_lens"].numpy(), 0)
     _greedy_check(best, path, ids, offs, d["act_lens"].numpy())
+
+
+def test_costs_ready_event(oracle, b200):
+    # the event fires when costs[] is final; a consumer on another stream that waits on it reads the right costs
+    d = _wl(b200, "cpu_b16_t500", seed=31, B=24)
+    acts = d["acts"].cuda()
+    ev = torch.cuda.Event()
+    side = torch.cuda.Stream()
+    costs, grads = b200.ctc_forward_backward(acts, d["labels"], d["act_lens"], d["label_lens"], costs_ready=ev)
+    with torch.cuda.stream(side):
+        side.wait_event(ev)
+        total = costs.sum()
+    costs.record_stream(side)
+    side.synchronize()
+    oc, og = oracle.compute(d["acts"].numpy(), d["labels"].numpy(), d["act_lens"].numpy(), d["label_lens"].numpy())
+    assert abs(float(total) - oc.sum()) <= 1e-5 * abs(oc.sum())
+    torch.cuda.synchronize()
+    assert np.abs(grads.cpu().numpy().astype(np.float64) - og).max() <= GRAD_ATOL

@@ -195,13 +195,7 @@ def run_b200(args, w):
         # compute stream joins it at the end of the step, so the step still contains the whole exchange.
         costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
                                                 costs_ready=ready)
-        with torch.cuda.stream(comm):
-            comm.wait_event(ready)
-            s = costs.sum().reshape(1)
-            dist.all_reduce(s)
-            loss_acc.copy_(s)
-        costs.record_stream(comm)
-        torch.cuda.current_stream(dev).wait_stream(comm)
+        b200ctc.sharding.overlapped_loss_all_reduce(costs, ready, comm, loss_acc)
 
     def timed(nsteps, phase_mask=0):
         evs = []

@@ -61,3 +61,22 @@ def all_reduce_loss(loss_sum: torch.Tensor, mean_of_means: bool = False, local_b
     if mean_of_means:
         rt /= dist.get_world_size()
     return rt
+
+
+def overlapped_loss_all_reduce(costs: torch.Tensor, ready: "torch.cuda.Event", comm: "torch.cuda.Stream",
+                               out: torch.Tensor) -> None:
+    """The same collective, off the critical path: `ready` is the event handed to the CTC call as
+    `costs_ready` (recorded when the per-utterance costs are final, while the gradient kernels still run).  The sum and
+    the NCCL all-reduce run on `comm`; the current stream joins `comm` before returning, so work enqueued after this
+    call sees `out` (1-element fp32, global SUM of the costs)."""
+    import torch.distributed as dist
+
+    cur = torch.cuda.current_stream(costs.device)
+    with torch.cuda.stream(comm):
+        comm.wait_event(ready)
+        s = costs.sum().reshape(1)
+        if dist.is_available() and dist.is_initialized():
+            dist.all_reduce(s)
+        out.copy_(s)
+    costs.record_stream(comm)
+    cur.wait_stream(comm)

@@ -459,6 +459,8 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     }
     p.bord = pl.nslices > 1 ? reinterpret_cast<int *>(ws + pl.o_bord) : nullptr;
     p.slice0 = 0;
+    p.nan_to_zero = o.nan_to_zero ? 1 : 0;
+    p.nan_count = o.nan_to_zero ? o.nan_count : nullptr;
 
     int launches = 0;
     cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches, (cudaEvent_t)o.costs_ready);

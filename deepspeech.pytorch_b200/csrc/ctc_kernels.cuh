@@ -70,6 +70,8 @@ struct CtcParams {
     int slice0;         // engine / grad kernels: this launch covers bord[slice0 .. slice0 + gridDim) (bord == 0: b itself)
     int nsplit;         // grad kernel: time blocks are dealt round-robin to this many CTAs per utterance
     int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
+    int nan_to_zero;    // 1: a NaN logit is read as 0 (the reference's train.py:595-598 guard, folded into the softmax pass)
+    int *nan_count;     // optional: += number of NaN logits seen in valid frames (nan_to_zero only)
 #ifdef CTC_PROFILE
     long long *dbg;     // [ctas][16 warps][8] clock counters (tools/ubench/engine_bench.cu only)
 #endif
@@ -255,6 +257,10 @@ __device__ __forceinline__ void sort_by_length(const CtcParams &p, int *keys) {
     }
 }
 
+// NaN guard of the training loop (/root/reference/train.py:595-598: `logits[torch.isnan(logits)] = 0` ahead of the
+// criterion): with nan_to_zero set every read of a logit goes through this, so all passes see the same value.
+__device__ __forceinline__ float nan_fix(float v, bool ntz) { return (ntz && v != v) ? 0.f : v; }
+
 __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -305,6 +311,13 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
         float x[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) x[i] = (valid && 4 * j + i < C) ? xs[r * C + 4 * j + i] : -INFINITY;
+        if (p.nan_to_zero) {
+            int nn = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (x[i] != x[i]) { x[i] = 0.f; ++nn; }
+            if (nn && active && p.nan_count) atomicAdd(p.nan_count, nn);
+        }
         float m = fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3]));
         for (int d = 1; d < lpr; d <<= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
         if (!valid) m = 0.f;
@@ -1127,19 +1140,31 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
     }
     const bool vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
     const int n4 = vec ? (C >> 2) : 0;
+    const bool ntz = p.nan_to_zero != 0;
     float m = -INFINITY;
+    int nn = 0;
     for (int i = tid; i < n4; i += kBigThreads) {
-        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
+        float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
+        if (ntz) {
+            nn += (v.x != v.x) + (v.y != v.y) + (v.z != v.z) + (v.w != v.w);
+            v.x = nan_fix(v.x, true); v.y = nan_fix(v.y, true); v.z = nan_fix(v.z, true); v.w = nan_fix(v.w, true);
+        }
         m = fmaxf(fmaxf(m, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
     }
-    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) m = fmaxf(m, __ldg(x + c));
+    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) {
+        const float v = __ldg(x + c);
+        nn += (ntz && v != v);
+        m = fmaxf(m, nan_fix(v, ntz));
+    }
+    if (nn && p.nan_count) atomicAdd(p.nan_count, nn);
     m = block_reduce(m, red, true);
     float sum = 0.f;
     for (int i = tid; i < n4; i += kBigThreads) {  // second pass hits L1/L2
         const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
-        sum += (expf(v.x - m) + expf(v.y - m)) + (expf(v.z - m) + expf(v.w - m));
+        sum += (expf(nan_fix(v.x, ntz) - m) + expf(nan_fix(v.y, ntz) - m)) +
+               (expf(nan_fix(v.z, ntz) - m) + expf(nan_fix(v.w, ntz) - m));
     }
-    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) sum += expf(__ldg(x + c) - m);
+    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) sum += expf(nan_fix(__ldg(x + c), ntz) - m);
     sum = block_reduce(sum, red, false);
     const float inv = 1.0f / sum;
     if (tid == 0) p.rowstat[row] = make_float2(m, inv);
@@ -1149,7 +1174,7 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
         __syncthreads();
         int cand = 0x7fffffff;
         for (int c = tid; c < C; c += kBigThreads)
-            if (__ldg(x + c) == m) { cand = c; break; }
+            if (nan_fix(__ldg(x + c), ntz) == m) { cand = c; break; }
         if (cand != 0x7fffffff) atomicMin(s_arg, cand);
         __syncthreads();
         if (tid == 0) p.path[(size_t)b * p.T + t] = *s_arg;
@@ -1163,7 +1188,7 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
         float v = 1.17549435e-38f;
         if (j <= L) {
             const int c = (j == 0) ? p.blank : min(max(lab[off + j - 1], 0), C - 1);
-            v = fmaxf(expf(__ldg(x + c) - m) * inv, 1.17549435e-38f);
+            v = fmaxf(expf(nan_fix(__ldg(x + c), ntz) - m) * inv, 1.17549435e-38f);
         }
         ydst[j] = y_hi_word(v);
         ydst[CP + j] = y_lo_word(v);
@@ -1189,17 +1214,18 @@ __global__ void __launch_bounds__(kBigThreads) ctc_final_big_kernel(const CtcPar
     const float m = st.x, inv = st.y, scale = p.grad_scale;
     const bool vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
     const int n4 = vec ? (C >> 2) : 0;
+    const bool ntz = p.nan_to_zero != 0;
     for (int i = tid; i < n4; i += kBigThreads) {
         const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
         float4 o;
-        o.x = scale * fmaxf(expf(v.x - m) * inv, 1.17549435e-38f);
-        o.y = scale * fmaxf(expf(v.y - m) * inv, 1.17549435e-38f);
-        o.z = scale * fmaxf(expf(v.z - m) * inv, 1.17549435e-38f);
-        o.w = scale * fmaxf(expf(v.w - m) * inv, 1.17549435e-38f);
+        o.x = scale * fmaxf(expf(nan_fix(v.x, ntz) - m) * inv, 1.17549435e-38f);
+        o.y = scale * fmaxf(expf(nan_fix(v.y, ntz) - m) * inv, 1.17549435e-38f);
+        o.z = scale * fmaxf(expf(nan_fix(v.z, ntz) - m) * inv, 1.17549435e-38f);
+        o.w = scale * fmaxf(expf(nan_fix(v.w, ntz) - m) * inv, 1.17549435e-38f);
         reinterpret_cast<float4 *>(g)[i] = o;
     }
     for (int c = (n4 << 2) + tid; c < C; c += kBigThreads)
-        g[c] = scale * fmaxf(expf(__ldg(x + c) - m) * inv, 1.17549435e-38f);
+        g[c] = scale * fmaxf(expf(nan_fix(__ldg(x + c), ntz) - m) * inv, 1.17549435e-38f);
     __syncthreads();  // this CTA's own global writes are visible to it after the barrier
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
     const int *lab = p.labels + p.laboff[b];

@@ -51,8 +51,13 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
                          zero_infinity: bool = True, grad_scale: float = 1.0, want_grads: bool = True,
                          max_label_len: Optional[int] = None, phase_mask: int = 0,
                          out_grads: Optional[torch.Tensor] = None, decode: bool = False,
-                         costs_ready: Optional[torch.cuda.Event] = None):
+                         costs_ready: Optional[torch.cuda.Event] = None, nan_to_zero: bool = False,
+                         nan_count: Optional[torch.Tensor] = None):
     """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
+
+    nan_to_zero: NaN logits are read as 0 (the guard at train.py:595-598 of the reference, folded into the softmax
+    pass; `acts` is left untouched).  nan_count: optional CUDA int32 tensor of one element, the number of NaN logits
+    found in valid frames is added to it.
 
     costs_ready: an event the library records as soon as `costs` is final (all recursions done, gradient kernels
     still running) -- wait on it from a communication stream to overlap the loss all-reduce with the gradient pass.
@@ -96,6 +101,11 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
                 lmax = max(lmax, int(max_label_len))
         opts.max_label_len = lmax
         opts.phase_mask = int(phase_mask)
+        opts.nan_to_zero = int(bool(nan_to_zero))
+        if nan_count is not None:
+            if not (nan_count.is_cuda and nan_count.dtype == torch.int32 and nan_count.numel() == 1):
+                raise ValueError("nan_count must be a CUDA int32 tensor with one element")
+            opts.nan_count = nan_count.data_ptr()
         if costs_ready is not None:
             if not costs_ready.cuda_event:  # torch creates the CUDA event lazily, on its first record
                 costs_ready.record()
@@ -208,19 +218,24 @@ def last_launch_count() -> int:
 @torch.library.custom_op("ctc_b200::ctc_loss", mutates_args=(), device_types="cuda")
 def _ctc_loss_op(acts: torch.Tensor, labels: torch.Tensor, act_lens: torch.Tensor, label_lens: torch.Tensor,
                  blank: int, zero_infinity: bool, grad_scale: float, want_grads: bool,
-                 max_label_len: int) -> Tuple[torch.Tensor, torch.Tensor]:
+                 max_label_len: int, nan_to_zero: bool = False) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    # third output: int32 [1] count of NaN logits replaced (empty unless nan_to_zero)
+    nans = (torch.zeros(1, dtype=torch.int32, device=acts.device) if nan_to_zero
+            else torch.empty(0, dtype=torch.int32, device=acts.device))
     costs, grads = ctc_forward_backward(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale,
-                                        want_grads, max_label_len if max_label_len >= 0 else None)
+                                        want_grads, max_label_len if max_label_len >= 0 else None,
+                                        nan_to_zero=nan_to_zero, nan_count=nans if nan_to_zero else None)
     if grads is None:
         grads = torch.empty(0, dtype=torch.float32, device=acts.device)
-    return costs, grads
+    return costs, grads, nans
 
 
 @_ctc_loss_op.register_fake
-def _(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale, want_grads, max_label_len):
+def _(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale, want_grads, max_label_len,
+      nan_to_zero=False):
     costs = acts.new_empty((acts.shape[1],))
     grads = torch.empty_like(acts) if want_grads else acts.new_empty((0,))
-    return costs, grads
+    return costs, grads, acts.new_empty((1 if nan_to_zero else 0,), dtype=torch.int32)
 
 
 class _CTCFunction(torch.autograd.Function):
@@ -228,21 +243,26 @@ class _CTCFunction(torch.autograd.Function):
     binding's autograd contract."""
 
     @staticmethod
-    def forward(ctx, acts, labels, act_lens, label_lens, blank, zero_infinity, scale, max_label_len, want):
-        costs, grads = _ctc_loss_op(acts, labels, act_lens, label_lens, blank, zero_infinity, scale, want,
-                                    -1 if max_label_len is None else int(max_label_len))
+    def forward(ctx, acts, labels, act_lens, label_lens, blank, zero_infinity, scale, max_label_len, want,
+                nan_to_zero=False):
+        costs, grads, nans = _ctc_loss_op(acts, labels, act_lens, label_lens, blank, zero_infinity, scale, want,
+                                          -1 if max_label_len is None else int(max_label_len), nan_to_zero)
         ctx.has_grads = want
         if want:
             ctx.save_for_backward(grads)
         loss = costs.sum().reshape(1)
-        return loss * scale if scale != 1.0 else loss
+        loss = loss * scale if scale != 1.0 else loss
+        if nan_to_zero:
+            ctx.mark_non_differentiable(nans)
+            return loss, nans
+        return loss
 
     @staticmethod
-    def backward(ctx, grad_output):
+    def backward(ctx, grad_output, *unused):
         if not ctx.has_grads:
-            return (None,) * 9
+            return (None,) * 10
         (grads,) = ctx.saved_tensors
-        return (grads * grad_output.reshape(1, 1, 1).to(grads.device),) + (None,) * 8
+        return (grads * grad_output.reshape(1, 1, 1).to(grads.device),) + (None,) * 9
 
 
 class CTCLoss(torch.nn.Module):
@@ -254,16 +274,22 @@ class CTCLoss(torch.nn.Module):
     utterance (L + repeats > T) cost 0 and zero gradient (warp-ctc's CPU behaviour); False gives cost +inf with
     zero gradient.  loss_on_cpu=True returns the loss on the host exactly like the reference binding does
     (`loss.to(device)` at train.py:602 is then a real copy); the default keeps it on the device and avoids a sync.
+    nan_to_zero=True replaces the training loop's NaN guard (train.py:595-598: `if torch.isnan(logits).any(): ...
+    logits[torch.isnan(logits)] = 0`, two sweeps over the logits and a host sync): NaN logits are read as 0 inside
+    the softmax pass, and `self.nan_count` (CUDA int32 [1]) holds how many the last call replaced -- read it only
+    where the reference's warning is wanted, it is the one thing here that synchronises.
     """
 
     def __init__(self, blank: int = 0, size_average: bool = False, length_average: bool = False,
-                 zero_infinity: bool = True, loss_on_cpu: bool = False):
+                 zero_infinity: bool = True, loss_on_cpu: bool = False, nan_to_zero: bool = False):
         super().__init__()
         self.blank = blank
         self.size_average = size_average
         self.length_average = length_average
         self.zero_infinity = zero_infinity
         self.loss_on_cpu = loss_on_cpu
+        self.nan_to_zero = nan_to_zero
+        self.nan_count = None
 
     def forward(self, acts, labels, act_lens, label_lens, max_label_len: Optional[int] = None):
         if labels.dim() != 1:
@@ -275,6 +301,10 @@ class CTCLoss(torch.nn.Module):
             scale = 1.0 / float(acts.shape[1])
         # grad mode is off inside autograd.Function.forward, so decide here whether gradients are wanted
         want = bool(acts.requires_grad and torch.is_grad_enabled())
-        loss = _CTCFunction.apply(acts, labels, act_lens, label_lens, self.blank, self.zero_infinity, scale,
-                                  max_label_len, want)
+        if self.nan_to_zero:
+            loss, self.nan_count = _CTCFunction.apply(acts, labels, act_lens, label_lens, self.blank,
+                                                      self.zero_infinity, scale, max_label_len, want, True)
+        else:
+            loss = _CTCFunction.apply(acts, labels, act_lens, label_lens, self.blank, self.zero_infinity, scale,
+                                      max_label_len, want)
         return loss.cpu() if self.loss_on_cpu else loss

@@ -63,12 +63,18 @@ typedef struct {
                               the gradient kernel, bit2 = skip the softmax/prep kernel; a skipped phase reuses what
                               the previous full call left in the workspace (bench.py times each kernel alone with
                               CUDA events this way) */
-    int reserved0;         /* must be zero */
+    int nan_to_zero;       /* 1: a NaN logit is read as 0 by every pass -- the training loop's guard
+                              (/root/reference/train.py:595-598, `logits[torch.isnan(logits)] = 0` ahead of the
+                              criterion) folded into the softmax pass instead of two extra sweeps over the logits.
+                              `acts` itself is not modified.  0 (default): logits are used as given */
     void *costs_ready;     /* cudaEvent_t or NULL.  If set, the event is recorded (on an internal stream) as soon as
                               costs[] is final, i.e. when the recursion kernels of every slice have finished -- well
                               before the gradient kernels do.  A caller that all-reduces the summed loss (the path's
                               one collective) waits on it from its communication stream and overlaps the exchange
                               with the gradient pass instead of serialising it behind the call. */
+    int *nan_count;        /* DEVICE int32 or NULL; with nan_to_zero, the number of NaN logits found in valid frames
+                              (t < act_lens[b]) is ADDED to it (the caller zeroes it; reading it back is what the
+                              reference's `torch.isnan(logits).any()` warning needs) */
 } ctcB200Options;
 
 /* replaces get_warpctc_version() */

@@ -342,3 +342,59 @@ def test_costs_ready_event(oracle, b200):
     assert abs(float(total) - oc.sum()) <= 1e-5 * abs(oc.sum())
     torch.cuda.synchronize()
     assert np.abs(grads.cpu().numpy().astype(np.float64) - og).max() <= GRAD_ATOL
+
+
+@pytest.mark.parametrize("name,B", [("cpu_b16_t500", 16), ("headline_b64_t1500", 64), ("bigc_b64_t1000_c5000", 3)])
+def test_nan_guard_matches_reference_workaround(oracle, b200, name, B):
+    # train.py:595-598: `logits[torch.isnan(logits)] = 0` ahead of the criterion.  nan_to_zero folds that into the
+    # softmax pass: same costs / gradients as the oracle run on the zeroed logits, NaNs of valid frames counted,
+    # the caller's logits left as they were.
+    d = _wl(b200, name, seed=41, B=B)
+    acts = d["acts"].clone()
+    T, _, C = acts.shape
+    rng = np.random.default_rng(5)
+    al = d["act_lens"].numpy()
+    expected = 0
+    for _ in range(200):
+        t, b, c = int(rng.integers(T)), int(rng.integers(B)), int(rng.integers(C))
+        if not torch.isnan(acts[t, b, c]):
+            acts[t, b, c] = float("nan")
+            expected += int(t < al[b])
+    acts[0, 0, :] = float("nan")  # a whole valid frame of NaNs -> uniform row
+    expected = int((torch.isnan(acts) & (torch.arange(T)[:, None, None] < d["act_lens"][None, :, None])).sum())
+    zeroed = torch.nan_to_num(acts, nan=0.0).numpy()
+    dev = acts.cuda()
+    count = torch.zeros(1, dtype=torch.int32, device="cuda")
+    costs, grads = b200.ctc_forward_backward(dev, d["labels"], d["act_lens"], d["label_lens"], nan_to_zero=True,
+                                             nan_count=count)
+    torch.cuda.synchronize()
+    oc, og = oracle.compute(zeroed, d["labels"].numpy(), d["act_lens"].numpy(), d["label_lens"].numpy())
+    c = costs.cpu().numpy().astype(np.float64)
+    assert np.all(np.isfinite(c))
+    assert (np.abs(c - oc) / np.maximum(np.abs(oc), 1e-30)).max() <= LOSS_RTOL
+    g = grads.cpu().numpy().astype(np.float64)
+    assert np.all(np.isfinite(g)) and np.abs(g - og).max() <= GRAD_ATOL
+    assert int(count.item()) == expected
+    assert torch.equal(torch.isnan(dev).cpu(), torch.isnan(acts))  # input untouched
+
+
+def test_nan_guard_module(oracle, b200):
+    w = b200.workloads.Workload("m", 8, 120, 30, 30, 0.05, 0.2)
+    d = b200.workloads.make(w, seed=22)
+    acts = d["acts"].clone()
+    acts[3, 1, 7] = float("nan")
+    acts[10, 5, 0] = float("nan")
+    logits = acts.cuda().requires_grad_(True)
+    crit = b200.CTCLoss(nan_to_zero=True)
+    loss = crit(logits, d["labels"], d["act_lens"], d["label_lens"])
+    loss.backward()
+    oc, og = oracle.compute(torch.nan_to_num(acts, nan=0.0).numpy(), d["labels"].numpy(), d["act_lens"].numpy(),
+                            d["label_lens"].numpy())
+    assert abs(loss.item() - oc.sum()) <= 1e-5 * oc.sum()
+    assert np.abs(logits.grad.cpu().numpy().astype(np.float64) - og).max() <= GRAD_ATOL
+    assert int(crit.nan_count.item()) == 2
+    # clean data: nothing counted, same result as the plain criterion
+    clean = d["acts"].cuda()
+    l1 = crit(clean, d["labels"], d["act_lens"], d["label_lens"])
+    l0 = b200.CTCLoss()(clean, d["labels"], d["act_lens"], d["label_lens"])
+    assert int(crit.nan_count.item()) == 0 and l1.item() == l0.item()

@@ -7,6 +7,8 @@
 // "max dynamic smem attribute already set" cache and a small pool of internal side streams + events on which the
 // per-slice kernels are forked from and joined back to the caller's stream.
 #include <cuda_runtime.h>
+#include <chrono>
+#include <stdio.h>
 #include <mutex>
 #include <math.h>
 #include <stdint.h>
@@ -588,25 +590,50 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         if (labels[i] < 0 || labels[i] >= C || labels[i] == o.blank) return CTC_B200_STATUS_INVALID_VALUE;
 
     // ---- slices of utterances [b0, b0 + nb)
-    int nch = B / kHostMinChunk;
-    nch = nch < 1 ? 1 : (nch > kHostChunks ? kHostChunks : nch);
-    int b0s[kHostChunks + 1];
+    // Slice widths are kept at multiples of 64 bytes where the batch allows it: the strided 2-D copies run at the full
+    // 50 GB/s of the link for 64-byte-multiple rows and at about half of it otherwise (measured: 16 x 29 floats =
+    // 1856 B rows 60 us per slice, 19 x 29 floats = 2204 B rows 116 us).  g = utterances per 64-byte granule.
+    int g = 16;
+    for (int c2 = C; (c2 & 1) == 0 && g > 1; c2 >>= 1) g >>= 1;
+    int b0s[kHostChunks + 1], nbs[kHostChunks];
+    int nch;
+    if (B / g >= 2 && g >= kHostMinChunk / 2) {
+        const int units = B / g;
+        nch = units > kHostChunks ? kHostChunks : units;
+        for (int k = 0; k < nch; ++k) nbs[k] = g * (units / nch + (k < units % nch ? 1 : 0));
+        nbs[nch - 1] += B % g;  // ragged remainder rides with the last slice
+    } else {
+        nch = B / kHostMinChunk;
+        nch = nch < 1 ? 1 : (nch > kHostChunks ? kHostChunks : nch);
+        for (int k = 0; k < nch; ++k) nbs[k] = B / nch + (k < B % nch ? 1 : 0);
+        if (g > 1 && g < kHostMinChunk)  // small granule (C a multiple of 4 or 8): round the cuts to it
+            for (int k = 0; k + 1 < nch; ++k) {
+                const int r = nbs[k] % g;
+                nbs[k] -= r;
+                nbs[k + 1] += r;
+            }
+    }
     size_t ws_off[kHostChunks + 1], lab_off[kHostChunks + 1];
-    int mxs[kHostChunks];
+    int mxs[kHostChunks], Ts[kHostChunks];
     b0s[0] = 0; ws_off[0] = 0; lab_off[0] = 0;
     for (int k = 0; k < nch; ++k) {
-        const int nb = B / nch + (k < B % nch ? 1 : 0);
+        const int nb = nbs[k];
         b0s[k + 1] = b0s[k] + nb;
-        int mx = 0;
+        int mx = 0, mt = 0;
         size_t nl = 0;
         for (int b = b0s[k]; b < b0s[k + 1]; ++b) {
             mx = label_lens[b] > mx ? label_lens[b] : mx;
+            mt = act_lens[b] > mt ? act_lens[b] : mt;
             nl += (size_t)label_lens[b];
         }
         lab_off[k + 1] = lab_off[k] + nl;
         mxs[k] = mx;
+        // Frames past the slice's longest utterance are padding: they are neither uploaded nor computed nor downloaded
+        // (their gradient rows are zero-filled on the host while the GPU works).  The reference's collate function sorts
+        // every batch by length (data_loader_aug.py:527), so on its batches the later slices are much shorter than T.
+        Ts[k] = mt;
         size_t wsb = 0;
-        ctcB200Status s = ctc_b200_workspace_size(T, nb, C, mx > 0 ? mx : 1, &o, &wsb);
+        ctcB200Status s = ctc_b200_workspace_size(mt, nb, C, mx > 0 ? mx : 1, &o, &wsb);
         if (s != CTC_B200_STATUS_SUCCESS) return s;
         ws_off[k + 1] = ws_off[k] + align256(wsb);
     }
@@ -650,6 +677,18 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
     }
     int launches = 0;
     const size_t host_pitch = (size_t)B * C * sizeof(float);
+    // CTC_B200_HOST_TRACE=1: print the device timeline of this call (per slice: upload done, kernels done, download
+    // done, in us after the call's first enqueue) and the host-side enqueue / wait times.  A diagnostic: the events
+    // are created per call.
+    static const bool trace = env_int("CTC_B200_HOST_TRACE", 0) != 0;
+    cudaEvent_t tr0 = nullptr, tr[kHostChunks][3] = {};
+    const auto wall0 = std::chrono::steady_clock::now();
+    if (trace) {
+        cudaEventCreate(&tr0);
+        for (int k = 0; k < nch; ++k)
+            for (int i = 0; i < 3; ++i) cudaEventCreate(&tr[k][i]);
+        cudaEventRecord(tr0, user);
+    }
     for (int k = 0; k < nch; ++k) {
         const int b0 = b0s[k], nb = b0s[k + 1] - b0;
         cudaStream_t st = nch > 1 ? c->side[k] : user;
@@ -658,32 +697,60 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         float *da = c->d_acts + (size_t)T * b0 * C;
         float *dg = grads_host ? c->d_grads + (size_t)T * b0 * C : nullptr;
         const size_t width = (size_t)nb * C * sizeof(float);
-        if (T > 0 && cudaMemcpy2DAsync(da, width, acts_host + (size_t)b0 * C, host_pitch, width, (size_t)T,
-                                       cudaMemcpyHostToDevice, st) != cudaSuccess)
+        const int Tk = Ts[k];
+        if (Tk > 0 && cudaMemcpy2DAsync(da, width, acts_host + (size_t)b0 * C, host_pitch, width, (size_t)Tk,
+                                        cudaMemcpyHostToDevice, st) != cudaSuccess)
             return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (trace) cudaEventRecord(tr[k][0], st);
         ctcB200Options ok = o;
         ok.stream = (void *)st;
         ok.lengths_on_device = 1;
         ok.costs_ready = nullptr;  // meaningless here: the call synchronises before it returns
         ok.max_label_len = mxs[k] > 0 ? mxs[k] : 1;
-        ctcB200Status s = compute_impl(da, dg, d_labels + lab_off[k], d_llen + b0, d_alen + b0, T, nb, C,
+        ctcB200Status s = compute_impl(da, dg, d_labels + lab_off[k], d_llen + b0, d_alen + b0, Tk, nb, C,
                                        c->d_costs + b0, static_cast<unsigned char *>(c->d_ws) + ws_off[k],
                                        ws_off[k + 1] - ws_off[k], &ok, false);
         if (s != CTC_B200_STATUS_SUCCESS) return s;
         launches += g_last_launches;
-        if (dg && T > 0 && cudaMemcpy2DAsync(grads_host + (size_t)b0 * C, host_pitch, dg, width, width, (size_t)T,
-                                             cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        if (trace) cudaEventRecord(tr[k][1], st);
+        if (dg && Tk > 0 && cudaMemcpy2DAsync(grads_host + (size_t)b0 * C, host_pitch, dg, width, width, (size_t)Tk,
+                                              cudaMemcpyDeviceToHost, st) != cudaSuccess)
             return CTC_B200_STATUS_MEMOPS_FAILED;
         if (cudaMemcpyAsync(costs_host + b0, c->d_costs + b0, sizeof(float) * nb, cudaMemcpyDeviceToHost, st) !=
             cudaSuccess)
             return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (trace) cudaEventRecord(tr[k][2], st);
         if (nch > 1) {
             if (cudaEventRecord(c->done[k], st) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
             if (cudaStreamWaitEvent(user, c->done[k], 0) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
         }
     }
     g_last_launches = launches;
+    if (grads_host)  // padding frames past each slice's longest utterance (disjoint from what the downloads write)
+        for (int k = 0; k < nch; ++k) {
+            const size_t width = (size_t)(b0s[k + 1] - b0s[k]) * C * sizeof(float);
+            for (int t = Ts[k]; t < T; ++t)
+                memset(reinterpret_cast<char *>(grads_host) + (size_t)t * host_pitch + (size_t)b0s[k] * C * sizeof(float),
+                       0, width);
+        }
+    const auto wall1 = std::chrono::steady_clock::now();
     if (cudaStreamSynchronize(user) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+    if (trace) {
+        const auto wall2 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[ctc_b200 host trace] enqueue %.1f us, wait %.1f us;",
+                std::chrono::duration<double, std::micro>(wall1 - wall0).count(),
+                std::chrono::duration<double, std::micro>(wall2 - wall1).count());
+        for (int k = 0; k < nch; ++k) {
+            float a = 0, b = 0, d = 0;
+            cudaEventElapsedTime(&a, tr0, tr[k][0]);
+            cudaEventElapsedTime(&b, tr0, tr[k][1]);
+            cudaEventElapsedTime(&d, tr0, tr[k][2]);
+            fprintf(stderr, " slice %d: up %.0f, kernels %.0f, down %.0f us;", k, a * 1e3, b * 1e3, d * 1e3);
+            for (int i = 0; i < 3; ++i) cudaEventDestroy(tr[k][i]);
+        }
+        fprintf(stderr, "\n");
+        cudaEventDestroy(tr0);
+    }
     if (loss_sum) {
         double acc = 0.0;
         for (int b = 0; b < B; ++b) acc += (double)costs_host[b];

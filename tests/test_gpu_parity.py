@@ -226,14 +226,28 @@ def test_sliced_launch_orders_with_caller_stream(b200):
     assert abs(float(total) - float(g2.abs().sum() + c2.sum())) <= 1e-3 * abs(float(total))
 
 
-@pytest.mark.parametrize("B", [3, 16, 33, 64])
-def test_host_buffer_entry(oracle, b200, B):
+def _sorted_by_length(d):
+    """The batch order the reference's collate function produces (data_loader_aug.py:527): longest utterance first."""
+    order = torch.argsort(d["act_lens"], descending=True, stable=True)
+    offs = torch.cumsum(d["label_lens"], 0) - d["label_lens"]
+    labels = torch.cat([d["labels"][int(offs[b]):int(offs[b]) + int(d["label_lens"][b])] for b in order.tolist()])
+    out = dict(d)
+    out.update(acts=d["acts"][:, order, :].contiguous(), labels=labels, act_lens=d["act_lens"][order].contiguous(),
+               label_lens=d["label_lens"][order].contiguous())
+    return out
+
+
+@pytest.mark.parametrize("B,by_length", [(3, False), (16, False), (33, False), (64, False), (64, True), (40, True)])
+def test_host_buffer_entry(oracle, b200, B, by_length):
     # ctc_b200_compute_host (the C-ABI entry bench.py's e2e leg times): pinned host buffers in and out, the batch
-    # pipelined in utterance slices; must equal the device-resident entry bit for bit
+    # pipelined in utterance slices; must equal the device-resident entry bit for bit.  by_length: the reference's
+    # batch order, where later slices are shorter than T and their padding frames never cross the bus.
     import ctypes
 
     lib = b200.pkg._lib.load()
     d = _wl(b200, "cpu_b16_t500", seed=8, B=B)
+    if by_length:
+        d = _sorted_by_length(d)
     T, C = d["T"], d["C"]
     h_acts = d["acts"].contiguous().pin_memory()
     h_grads = torch.full_like(d["acts"], float("nan")).pin_memory()

@@ -28,7 +28,8 @@ constexpr size_t kSmemLimit = 227 * 1024;
 thread_local int g_last_launches = 0;
 
 // ---- length-bucket slices (see sort_by_length in ctc_kernels.cuh)
-constexpr int kMaxSlices = 8;
+constexpr int kMaxSlices = 16;     // upper bound (CTC_B200_SLICES)
+constexpr int kDefaultSlices = 8;
 constexpr int kMinSliceB = 8;  // utterances per slice below which slicing stops paying
 struct SidePool {
     bool ok = false;
@@ -71,7 +72,8 @@ struct Plan {
     int nqmax;   // grad kernel warps per CTA
     int nsplit;  // grad kernel CTAs per utterance
     int big;     // large-alphabet path (C > kMaxSmallC)
-    size_t o_rowstat, o_occpos, o_order, o_units, o_cu, o_bord;
+    size_t o_ctab, o_units, o_cu, o_bord;
+    size_t smem_rows;  // large alphabets: dynamic shared memory of the row kernel
     int nslices;           // length-bucket slices the engine / grad launches are cut into (1 = unsliced)
     size_t smem_engine_req;  // dynamic shared memory REQUESTED for an engine CTA (>= smem_engine, see make_plan)
     int numax;   // reduction units per utterance (small alphabets)
@@ -101,6 +103,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->R = R;
     pl->nblk = T > 0 ? (T + R - 1) / R : 1;
     pl->smem_prep = pl->big ? prep_big_smem(C, Lmax) : prep_smem(C, Lmax);
+    pl->smem_rows = pl->big ? prep_big_row_smem(C) : 0;
     pl->smem_engine = engine_smem(pl->Cp, nwl).total;
     pl->smem_grad = grad_smem(C, pl->Cp, Lmax, pl->nqmax, kK, pl->big != 0).total;
     {
@@ -117,7 +120,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     {
         // Length-bucket slices: up to kMaxSlices, each at least kMinSliceB utterances.  CTC_B200_SLICES overrides.
         int ns = B / kMinSliceB;
-        ns = ns < 1 ? 1 : (ns > kMaxSlices ? kMaxSlices : ns);
+        ns = ns < 1 ? 1 : (ns > kDefaultSlices ? kDefaultSlices : ns);
         ns = env_int("CTC_B200_SLICES", ns);
         ns = ns < 1 ? 1 : (ns > kMaxSlices ? kMaxSlices : ns);
         if (ns > B || B > kMaxSortB) ns = 1;
@@ -141,9 +144,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->o_feas = o;   o = align256(o + sizeof(int) * B);
     pl->o_laboff = o; o = align256(o + sizeof(int) * B);
     pl->o_tlab = o;   o = align256(o + sizeof(uint4) * (size_t)B * NT);
-    pl->o_rowstat = o; if (pl->big) o = align256(o + sizeof(float2) * (size_t)T * B);
-    pl->o_occpos = o;  if (pl->big) o = align256(o + sizeof(float) * (size_t)T * B * pl->Cp);
-    pl->o_order = o;   if (pl->big) o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
+    pl->o_ctab = o;    if (pl->big) o = align256(o + sizeof(int2) * (size_t)B * (Lmax > 0 ? Lmax : 1));
     pl->o_coff = o;   o = align256(o + sizeof(int) * (size_t)B * (C + 1));
     pl->numax = pl->big ? 0 : grad_max_units(C, Lmax, pl->nqmax);
     pl->o_units = o;  o = align256(o + sizeof(unsigned) * (size_t)B * pl->numax);
@@ -159,6 +160,15 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
 // Engine + gradient launches, cut into length-bucket slices on the pool's side streams (forked from and joined back
 // to the caller's stream with events, so the caller sees ordinary stream semantics and graph capture still works).
 // All engines are enqueued before any gradient kernel: the longest slice (rank 0..) starts first.
+// Slices are equal rank ranges.  Measured and rejected (headline shape): TRIANGULAR slice sizes (few longest
+// utterances in slice 0, its time groups spread over one full wave of CTAs) -- 0.225 against 0.223 ms/step: the end
+// of the step is bound by the total gradient work that only becomes available late (CTC_B200_TRACE shows every
+// slice's gradient kernel finishing ~30 us after its engine), not by the size of the last slice.
+inline int slice_begin(const Plan &pl, int B, int k) {
+    const int ns = pl.nslices;
+    return k <= 0 ? 0 : (k >= ns ? B : (int)((long long)B * k / ns));
+}
+
 // The collapse of the best path (decode by-product of the prep kernel) is independent of the lattice kernels: it is
 // enqueued behind the engine of the LAST slice (the shortest utterances, far from the critical path).
 inline void launch_collapse(const CtcParams &p, cudaStream_t s, int *launches) {
@@ -185,6 +195,15 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
     SidePool *sp = side_pool(dev);
     if (!sp) return cudaErrorUnknown;
     const int ns = pl.nslices;
+    // CTC_B200_TRACE=1 (diagnostic; synchronises the caller's stream): device timeline of the sliced launch, per
+    // slice the time its engine and its gradient kernel finished, in us after the fork point (= end of the prep kernel)
+    static const bool trace = env_int("CTC_B200_TRACE", 0) != 0;
+    cudaEvent_t tr0 = nullptr, tr[kMaxSlices][2] = {};
+    if (trace) {
+        cudaEventCreate(&tr0);
+        for (int k = 0; k < ns; ++k) { cudaEventCreate(&tr[k][0]); cudaEventCreate(&tr[k][1]); }
+        cudaEventRecord(tr0, st);
+    }
     if ((e = cudaEventRecord(sp->fork, st)) != cudaSuccess) return e;
     for (int k = 0; k < ns; ++k)
         if ((e = cudaStreamWaitEvent(sp->side[k], sp->fork, 0)) != cudaSuccess) return e;
@@ -192,9 +211,10 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
         if (pass == 0 ? !do_engine : !do_grad) continue;
         for (int k = 0; k < ns; ++k) {
             CtcParams pk = p;
-            pk.slice0 = (int)((long long)p.B * k / ns);
-            const int nb = (int)((long long)p.B * (k + 1) / ns) - pk.slice0;
+            pk.slice0 = slice_begin(pl, p.B, k);
+            const int nb = slice_begin(pl, p.B, k + 1) - pk.slice0;
             if (pass == 0) eng(pk, nb, sp->side[k]); else grd(pk, nb, sp->side[k]);
+            if (trace) cudaEventRecord(tr[k][pass], sp->side[k]);
         }
         if (pass == 0) {
             if (costs_ready) {
@@ -215,6 +235,21 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
     for (int k = 0; k < ns; ++k) {
         if ((e = cudaEventRecord(sp->join[k], sp->side[k])) != cudaSuccess) return e;
         if ((e = cudaStreamWaitEvent(st, sp->join[k], 0)) != cudaSuccess) return e;
+    }
+    if (trace) {
+        cudaStreamSynchronize(st);
+        fprintf(stderr, "[ctc_b200 trace]");
+        for (int k = 0; k < ns; ++k) {
+            float a = 0, b = 0;
+            if (do_engine) cudaEventElapsedTime(&a, tr0, tr[k][0]);
+            if (do_grad) cudaEventElapsedTime(&b, tr0, tr[k][1]);
+            fprintf(stderr, " s%d[%d..%d) eng %.0f grad %.0f;", k, slice_begin(pl, p.B, k), slice_begin(pl, p.B, k + 1),
+                    a * 1e3, b * 1e3);
+            cudaEventDestroy(tr[k][0]);
+            cudaEventDestroy(tr[k][1]);
+        }
+        fprintf(stderr, "\n");
+        cudaEventDestroy(tr0);
     }
     return cudaSuccess;
 }
@@ -255,20 +290,29 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
             ++*launches;
         },
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
-            ctc_grad_kernel<kK, CP, false><<<dim3(pl.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pk);
+            ctc_grad_kernel<kK, CP, false><<<dim3(pk.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pk);
             ++*launches;
         });
 }
 
+// Large alphabets: ONE row kernel over the whole batch (softmax, dense gradient part, emission gather -- the
+// HBM-bound part, every logit read once and every gradient element written once), then the sliced lattice launches
+// of the small path; the gradient kernel subtracts the occupancies in place.
+// Measured and rejected on B200 (B=64, T=1000, C=5000): a per-slice pipeline (row kernel of slice k+1 on a
+// low-priority stream under the lattice kernels of slice k) -- the row kernels stretched from 0.40 to 0.64 ms under
+// the co-running lattice kernels and the step got slower (0.66-0.71 ms against 0.63).
 cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
                        cudaEvent_t costs_ready) {
     constexpr int CP = 256;
     static bool attr_set[64] = {false};
     int dev = 0;
-    cudaGetDevice(&dev);
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(ctc_prep_utt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)kSmemLimit);
+        e = cudaFuncSetAttribute(ctc_prep_utt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_prep_big_kernel<CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ctc_engine_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
@@ -278,35 +322,47 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    cudaError_t e = cudaSuccess;
-    const long long rows = (long long)p.T * p.B;
-    if (!(phase_mask & 4) && p.T > 0) {
-        ctc_prep_utt_kernel<<<p.B + (pl.nslices > 1 ? 1 : 0), kPrepRows, pl.smem_prep, st>>>(p);
-        ++*launches;
-        ctc_prep_big_kernel<CP><<<(unsigned)rows, kBigThreads, 256, st>>>(p);
-        ++*launches;
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-    }
+    const bool do_rows = !(phase_mask & 4) && p.T > 0;
     const bool do_engine = !(phase_mask & 1);
     const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
-    e = launch_sliced(
-        p, pl, st, do_engine, do_grad, launches, costs_ready,
-        [&](const CtcParams &pk, int nb, cudaStream_t s) {
-            ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
-            ++*launches;
-        },
-        [&](const CtcParams &pk, int nb, cudaStream_t s) {
-            ctc_grad_kernel<kK, CP, true><<<dim3(pl.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pk);
-            ++*launches;
-        });
-    if (e != cudaSuccess) return e;
-    if (do_grad) {
-        ctc_final_big_kernel<CP><<<(unsigned)rows, kBigThreads, 0, st>>>(p);
+    if (do_rows) {
+        ctc_prep_utt_kernel<<<p.B + (pl.nslices > 1 ? 1 : 0), kPrepRows, pl.smem_prep, st>>>(p);
         ++*launches;
-        e = cudaGetLastError();
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
-    return e;
+    // rows that are 16-byte aligned and fit 5 / 8 / 16 float4 per thread stay in registers
+    const bool aligned = (p.C % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.acts) & 15) == 0) &&
+                         (!p.grads || (reinterpret_cast<uintptr_t>(p.grads) & 15) == 0);
+    auto rows = [&](CtcParams pk, int nb, cudaStream_t s) {
+        pk.slice_nb = nb;
+        pk.bord = nullptr;  // whole batch in memory order
+        pk.slice0 = 0;
+        const unsigned grid = (unsigned)((long long)p.T * nb);
+        const bool ntz = p.nan_to_zero != 0;
+#define CTC_ROWS_REG(NV)                                                                              \
+        do {                                                                                              \
+            if (ntz) ctc_prep_big_reg_kernel<CP, NV, true><<<grid, kBigThreads, 0, s>>>(pk);            \
+            else ctc_prep_big_reg_kernel<CP, NV, false><<<grid, kBigThreads, 0, s>>>(pk);               \
+        } while (0)
+        if (aligned && p.C <= 1024 * 5) CTC_ROWS_REG(5);
+        else if (aligned && p.C <= 1024 * 8) CTC_ROWS_REG(8);
+        else if (aligned && p.C <= 1024 * 16) CTC_ROWS_REG(16);
+        else ctc_prep_big_kernel<CP><<<grid, kBigThreads, pl.smem_rows, s>>>(pk);
+#undef CTC_ROWS_REG
+        ++*launches;
+    };
+    auto eng = [&](const CtcParams &pk, int nb, cudaStream_t s) {
+        ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+        ++*launches;
+    };
+    auto grd = [&](const CtcParams &pk, int nb, cudaStream_t s) {
+        ctc_grad_kernel<kK, CP, true><<<dim3(pk.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pk);
+        ++*launches;
+    };
+    if ((long long)p.T * p.B >= (1ll << 31)) return cudaErrorInvalidValue;
+    if (do_rows) rows(p, p.B, st);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    return launch_sliced(p, pl, st, do_engine, do_grad, launches, costs_ready, eng, grd);
 }
 
 cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
@@ -443,9 +499,7 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.tlab = reinterpret_cast<uint4 *>(ws + pl.o_tlab);
     p.big = pl.big;
     p.bpos = pl.big ? 0 : o.blank;
-    p.rowstat = reinterpret_cast<float2 *>(ws + pl.o_rowstat);
-    p.occpos = reinterpret_cast<float *>(ws + pl.o_occpos);
-    p.order = reinterpret_cast<int *>(ws + pl.o_order);
+    p.ctab = reinterpret_cast<int2 *>(ws + pl.o_ctab);
     p.nsplit = pl.nsplit;
     p.nqmax = pl.nqmax;
     p.coff = reinterpret_cast<int *>(ws + pl.o_coff);
@@ -461,6 +515,8 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     }
     p.bord = pl.nslices > 1 ? reinterpret_cast<int *>(ws + pl.o_bord) : nullptr;
     p.slice0 = 0;
+    p.slice_nb = B;
+    p.dbg_flags = env_int("CTC_B200_DBG", 0);
     p.nan_to_zero = o.nan_to_zero ? 1 : 0;
     p.nan_count = o.nan_to_zero ? o.nan_count : nullptr;
 

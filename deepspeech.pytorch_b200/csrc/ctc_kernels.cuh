@@ -19,8 +19,9 @@
 //                       checkpoint into shared memory, sweeps beta backwards from the beta checkpoint forming
 //                       posteriors alpha*betabar/P, then the CTA reduces them per class in equal-sized units and
 //                       writes grad = scale * (softmax - occupancy) once.
-//   large alphabets (C > 128): ctc_prep_utt_kernel + ctc_prep_big_kernel (streaming softmax, emission rows gathered by
-//                       label POSITION) -> the same engine / grad kernels at pitch 256 -> ctc_final_big_kernel.
+//   large alphabets (C > 128): ctc_prep_utt_kernel + ctc_prep_big_kernel (streaming softmax that also writes the dense
+//                       part of the gradient; emission rows gathered by label POSITION) -> the same engine / grad
+//                       kernels at pitch 256, the grad kernel subtracting the occupancies in place.
 //
 // Replaces the arithmetic behind `criterion(logits, targets, output_sizes.cpu(), target_sizes)`
 // (/root/reference/train.py:600; eval :352,:457), i.e. warp-ctc's softmax + compute_alpha + compute_betas_and_grad
@@ -61,17 +62,18 @@ struct CtcParams {
     uint4 *tlab;        // [B][nwl*32] per lattice thread (K = 8): packed label classes, skip/valid bits, lpos
     int bpos;           // index of the blank inside an emission row (class rows: blank; position rows: 0)
     int big;            // 1: large-alphabet path (emission rows indexed by label POSITION, see ctc_prep_big_kernel)
-    float2 *rowstat;    // big: [T*B] (row max, 1/sum) of the softmax
-    float *occpos;      // big: [B][T][Cp] occupancies by position (0: blank, 1+i: label i)
-    int *order;         // big: [B][Lmax] label index at class-sorted position j
+    int2 *ctab;         // big: [B][Lmax] per class-sorted label slot j: (class, run length of the class if j is its
+                        // first slot, else 0) -- the gradient kernel subtracts one merged occupancy per class
     int *path;          // optional [B][T]: argmax class of every valid frame (best path), by-product of the softmax pass
     int *dec_ids, *dec_off, *dec_len;  // with path: collapsed best path [B][T], frame offsets [B][T] (nullable), lengths [B]
     int *bord;          // [B] utterances ordered by decreasing act_len (length bucketing, see sort_by_length)
     int slice0;         // engine / grad kernels: this launch covers bord[slice0 .. slice0 + gridDim) (bord == 0: b itself)
+    int slice_nb;       // utterances of this launch (large-alphabet row kernel: grid = T * slice_nb)
     int nsplit;         // grad kernel: time blocks are dealt round-robin to this many CTAs per utterance
     int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
     int nan_to_zero;    // 1: a NaN logit is read as 0 (the reference's train.py:595-598 guard, folded into the softmax pass)
     int *nan_count;     // optional: += number of NaN logits seen in valid frames (nan_to_zero only)
+    int dbg_flags;      // experiment switches (CTC_B200_DBG); 0 in production
 #ifdef CTC_PROFILE
     long long *dbg;     // [ctas][16 warps][8] clock counters (tools/ubench/engine_bench.cu only)
 #endif
@@ -178,7 +180,24 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
     for (int i = tid; i < L; i += blockDim.x) labs[i] = min(max(p.labels[off + i], 0), C - 1);
     __syncthreads();
     const int *lab = labs;
-    if (warp == 0) sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
+    if (p.big) {
+        // large alphabets: a counting sort would walk C counters; rank the L <= 255 labels against each other instead
+        // (stable: ties by position).  ctab[slot] = (class, run length at the class's first slot, else 0).
+        for (int i = tid; i < L; i += blockDim.x) {
+            const int c = lab[i];
+            int less = 0, eq_before = 0, eq = 0;
+            for (int j = 0; j < L; ++j) {
+                const int cj = lab[j];
+                less += cj < c;
+                eq += cj == c;
+                eq_before += (cj == c) & (j < i);
+            }
+            lps[i] = less + eq_before;
+            p.ctab[(size_t)b * p.Lmax + less + eq_before] = make_int2(c, eq_before == 0 ? eq : 0);
+        }
+    } else if (warp == 0) {
+        sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
+    }
     __syncthreads();
     if (!p.big && warp == 1) {
         // Reduction units of the gradient kernel: every class segment of the sorted posterior row is cut into pieces
@@ -212,8 +231,6 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
         }
         if (lane == 0) cu[C] = base;
     }
-    if (p.big)
-        for (int i = tid; i < L; i += blockDim.x) p.order[(size_t)b * p.Lmax + lps[i]] = i;
     const int NT = p.nwl * 32;
     for (int e = tid; e < NT; e += blockDim.x) {
         unsigned cls = 0, bits = 0, lp[4] = {0, 0, 0, 0};
@@ -228,7 +245,7 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
                 bits |= 1u << (8 + h);
                 if (i == 0 || lab[i - 1] != c) bits |= 1u << h;            // skip into s
                 if (i + 1 < L && lab[i + 1] != c) bits |= 1u << (4 + h);  // skip out of s
-                lp[h] = (unsigned)(p.big ? i : lps[i]);
+                lp[h] = (unsigned)lps[i];  // class-sorted slot of the label's posterior
             }
         }
         p.tlab[(size_t)b * NT + e] = make_uint4(cls, bits, lp[0] | (lp[1] << 16), lp[2] | (lp[3] << 16));
@@ -865,8 +882,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
     const int nblk_b = (Tb + R - 1) / R;
     if (z >= nblk_b) return;  // padding frames were zero-filled by the prep kernel
     const size_t rowstride = (size_t)p.B * C;
-    if (!p.feas[b]) {  // infeasible utterance: zero gradient (large alphabets: written by the final kernel)
-        if (BIG) return;
+    if (!p.feas[b]) {  // infeasible utterance: zero gradient
         for (int blk = z; blk < nblk_b; blk += p.nsplit)
             for (int r = q; r < min(R, Tb - blk * R); r += blockDim.x / 32)
                 for (int c = lane; c < C; c += 32) p.grads[((size_t)(blk * R + r) * p.B + b) * C + c] = 0.f;
@@ -1025,16 +1041,30 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
         PROF(float probe = *reinterpret_cast<volatile float *>(bpart + lane); long long h4b = prof_clk() + (probe > 1e30f ? 1 : 0); gb1 += h4b - h4;)
         // ---- per-class occupancy, gradient rows written once
         if (BIG) {
-            // large alphabets: occupancies stay indexed by POSITION (0: blank, 1+i: label i); ctc_final_big_kernel
-            // folds them into the dense softmax rows
+            // large alphabets: the dense rows scale * softmax are already in place (ctc_prep_big_kernel); subtract the
+            // occupancy of each class on the lattice.  One reduction (RED.ADD, no return value, so no DRAM round trip
+            // on this thread) per (row, distinct class): a single addend per address, hence deterministic and equal
+            // to g - scale * occupancy bit for bit.  Repeated classes sit in adjacent class-sorted slots and are
+            // summed in slot order first.
+            const float nscale = -p.grad_scale;
+            const int2 *ct = p.ctab + (size_t)b * p.Lmax;
             for (int r = q; r < nrow; r += nq) {
-                float *dst = p.occpos + ((size_t)b * p.T + t0 + r) * Cp;
+                float *grow = p.grads + ((size_t)(t0 + r) * p.B + b) * C;
+                const float *prow = psort + r * Lp;
                 float ob = 0.f;
                 for (int j = 0; j < nq; ++j) ob += bpart[r * Lp + j * 32 + lane];
 #pragma unroll
                 for (int d = 16; d; d >>= 1) ob += __shfl_xor_sync(kFull, ob, d);
-                if (lane == 0) dst[0] = ob;
-                for (int i = lane; i < L; i += 32) dst[1 + i] = psort[r * Lp + i];
+                if (p.dbg_flags & 1) continue;
+                if (lane == 0) atomicAdd(grow + p.blank, nscale * ob);
+                for (int j = lane; j < L; j += 32) {
+                    const int2 e = __ldg(ct + j);
+                    if (e.y > 0) {
+                        float sum = prow[j];
+                        for (int k = 1; k < e.y; ++k) sum += prow[j + k];
+                        atomicAdd(grow + e.x, nscale * sum);
+                    }
+                }
             }
         } else {
             // lane = (task slot lane>>3, row lane&7).  Phase A: one task per (unit, row) sums <= 8 adjacent posteriors
@@ -1083,11 +1113,19 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
 
 // ================================================================================================ large alphabets
 // C > 128 (BPE-style vocabularies): the softmax is the HBM-bound part (the row is C floats, the lattice touches only
-// 1 + L of them).  ctc_prep_big_kernel streams each (t,b) row once -- float4 coalesced loads, warp-shuffle + shared
-// memory max / sum reductions -- keeps (max, 1/sum) and gathers the 1 + L emissions the lattice needs into a compact
-// POSITION-indexed row (0: blank, 1+i: label i), so the lattice kernels run unchanged with pitch 256 (L <= 255).
-// ctc_final_big_kernel streams the row a second time and writes grad = scale * (softmax - occupancy) once.
+// 1 + L of them), so every logit is read ONCE and every gradient element is written ONCE:
+//   ctc_prep_big_kernel  one CTA per (t,b) row: float4 streaming loads into a shared-memory copy of the row, max and
+//                        sum by warp shuffles + a shared-memory step, the dense part of the gradient
+//                        scale * softmax written straight from that copy (streaming float4 stores), and the 1 + L
+//                        emissions the lattice needs gathered into a compact POSITION-indexed row (0: blank, 1+i:
+//                        label i), so the lattice kernels run unchanged with pitch 256 (L <= 255).
+//   ctc_grad_kernel<BIG> subtracts the <= 1 + L occupancies of a row in place with one fire-and-forget reduction
+//                        per distinct class (a sparse read-modify-write of 32-byte sectors done by the L2,
+//                        ~ (1+L) * 64 B per row against 8 * C).
+// DRAM traffic per valid frame: 4C read + 4C written + ~64 (1+L) + the position rows; per padding frame 4C written.
 constexpr int kBigThreads = 256;
+constexpr int kBigStageMaxC = 16384;  // rows up to 64 KB are staged in shared memory (>= 3 CTAs per SM); longer rows
+                                      // are re-read (L2) by the later passes
 
 __device__ __forceinline__ float block_reduce(float v, float *red, bool is_max) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1108,6 +1146,9 @@ __host__ __device__ inline size_t prep_big_smem(int C, int Lmax) {
     const size_t utt = 2 * sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1) + sizeof(int) * (C + 2) + 64;
     return utt > 256 ? utt : 256;
 }
+__host__ __device__ inline size_t prep_big_row_smem(int C) {
+    return 256 + (C <= kBigStageMaxC ? align16(sizeof(float) * (size_t)C) : 0);
+}
 
 // label tables only (one CTA per utterance); the large-alphabet path runs it ahead of the row kernel
 __global__ void __launch_bounds__(kPrepRows) ctc_prep_utt_kernel(const CtcParams p) {
@@ -1121,65 +1162,211 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_utt_kernel(const CtcParams
     prep_utterance(p, blockIdx.x, lps, lps + Lp, lps + 2 * Lp);
 }
 
+__device__ __forceinline__ float4 nan_fix4(float4 v, bool ntz, int &nn) {
+    if (ntz) {
+        nn += (v.x != v.x) + (v.y != v.y) + (v.z != v.z) + (v.w != v.w);
+        v.x = nan_fix(v.x, true); v.y = nan_fix(v.y, true); v.z = nan_fix(v.z, true); v.w = nan_fix(v.w, true);
+    }
+    return v;
+}
+
+// Register-resident form of the row kernel for 16-byte-aligned rows of C <= 1024 * NV classes (C % 4 == 0): thread i
+// keeps float4 i, i + 256, ... of the row in registers across the three passes, so the row is read from DRAM once,
+// never staged, and the only re-reads are the 1 + L gathered emissions (L2).  Same arithmetic and summation order
+// as the float4 form of the generic kernel below.
+template <int CP, int NV, bool NTZ>
+__global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const CtcParams p) {
+    __shared__ float red[48];
+    const int tid = threadIdx.x;
+    const int C = p.C;
+    const int t = (int)(blockIdx.x / (unsigned)p.slice_nb), bi = (int)(blockIdx.x - (unsigned)t * (unsigned)p.slice_nb);
+    const int b = p.bord ? p.bord[p.slice0 + bi] : p.slice0 + bi;
+    const long long row = (long long)t * p.B + b;
+    const float4 *x4 = reinterpret_cast<const float4 *>(p.acts + row * C);
+    float4 *g4 = p.grads ? reinterpret_cast<float4 *>(p.grads + row * C) : nullptr;
+    const int n4 = C >> 2;
+    if (t >= min(max(p.act_lens[b], 0), p.T)) {  // padding frame: zero gradient row, nothing else
+        if (g4) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k)
+                if (tid + k * kBigThreads < n4) __stcs(g4 + tid + k * kBigThreads, make_float4(0.f, 0.f, 0.f, 0.f));
+        }
+        return;
+    }
+    float4 v[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int i = tid + k * kBigThreads;
+        v[k] = (i < n4) ? __ldcs(x4 + i) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    }
+    int nn = 0;
+    float m = -INFINITY;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        if (NTZ) v[k] = nan_fix4(v[k], true, nn);
+        m = fmaxf(fmaxf(m, fmaxf(v[k].x, v[k].y)), fmaxf(v[k].z, v[k].w));
+    }
+    if (NTZ && nn && p.nan_count) atomicAdd(p.nan_count, nn);
+    m = block_reduce(m, red, true);
+    if (p.path != nullptr) {  // best path by-product: first class attaining the row maximum
+        int *s_arg = reinterpret_cast<int *>(red) + 40;
+        if (tid == 0) *s_arg = 0x7fffffff;
+        __syncthreads();
+        int cand = 0x7fffffff;
+#pragma unroll
+        for (int k = NV - 1; k >= 0; --k) {
+            const int c0 = 4 * (tid + k * kBigThreads);
+            if (v[k].w == m) cand = c0 + 3;
+            if (v[k].z == m) cand = c0 + 2;
+            if (v[k].y == m) cand = c0 + 1;
+            if (v[k].x == m) cand = c0;
+        }
+        if (cand != 0x7fffffff) atomicMin(s_arg, cand);
+        __syncthreads();
+        if (tid == 0) p.path[(size_t)b * p.T + t] = *s_arg;
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        if (tid + k * kBigThreads < n4) {
+            v[k].x = expf(v[k].x - m); v[k].y = expf(v[k].y - m); v[k].z = expf(v[k].z - m); v[k].w = expf(v[k].w - m);
+            sum += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+        }
+    }
+    sum = block_reduce(sum, red, false);
+    const float inv = 1.0f / sum;
+    if (g4) {
+        const float scale = p.grad_scale;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int i = tid + k * kBigThreads;
+            if (i < n4) {
+                float4 o;
+                o.x = scale * fmaxf(v[k].x * inv, 1.17549435e-38f);
+                o.y = scale * fmaxf(v[k].y * inv, 1.17549435e-38f);
+                o.z = scale * fmaxf(v[k].z * inv, 1.17549435e-38f);
+                o.w = scale * fmaxf(v[k].w * inv, 1.17549435e-38f);
+                __stcs(g4 + i, o);
+            }
+        }
+    }
+    // compact emission row, planar fp64 words (the 1 + L logits are re-read: L2 hits)
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
+    const int off = p.laboff[b];  // written by ctc_prep_utt_kernel, launched before this kernel
+    const float *x = reinterpret_cast<const float *>(x4);
+    unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * CP;
+    for (int j = tid; j < CP; j += kBigThreads) {
+        float y = 1.17549435e-38f;
+        if (j <= L) {
+            const int c = (j == 0) ? p.blank : min(max(p.labels[off + j - 1], 0), C - 1);
+            y = fmaxf(expf(nan_fix(__ldg(x + c), NTZ) - m) * inv, 1.17549435e-38f);
+        }
+        ydst[j] = y_hi_word(y);
+        ydst[CP + j] = y_lo_word(y);
+    }
+}
+
+// grid: T * slice_nb CTAs; CTA i handles frame t = i / slice_nb of utterance bord[slice0 + i % slice_nb]
 template <int CP>
 __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x;
     const int C = p.C;
-    const long long nrows_total = (long long)p.T * p.B;
     float *red = reinterpret_cast<float *>(smem);
-    const long long row = blockIdx.x;
-    const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
+    float *srow = reinterpret_cast<float *>(smem + 256);
+    const bool staged = C <= kBigStageMaxC;
+    const int t = (int)(blockIdx.x / (unsigned)p.slice_nb), bi = (int)(blockIdx.x - (unsigned)t * (unsigned)p.slice_nb);
+    const int b = p.bord ? p.bord[p.slice0 + bi] : p.slice0 + bi;
+    const long long row = (long long)t * p.B + b;
     const float *x = p.acts + row * C;
+    float *g = p.grads ? p.grads + row * C : nullptr;
+    const bool gvec = g && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
     if (t >= min(max(p.act_lens[b], 0), p.T)) {  // padding frame: zero gradient row, nothing else
-        if (p.grads) {
-            float *g = p.grads + row * C;
-            for (int c = tid; c < C; c += kBigThreads) g[c] = 0.f;
+        if (g) {
+            const int n4 = gvec ? (C >> 2) : 0;
+            for (int i = tid; i < n4; i += kBigThreads) __stcs(reinterpret_cast<float4 *>(g) + i, make_float4(0.f, 0.f, 0.f, 0.f));
+            for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) g[c] = 0.f;
         }
         return;
     }
     const bool vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
     const int n4 = vec ? (C >> 2) : 0;
     const bool ntz = p.nan_to_zero != 0;
+    const float4 *x4 = reinterpret_cast<const float4 *>(x);
+    float4 *s4 = reinterpret_cast<float4 *>(srow);
+    // ---- pass 1 (the only DRAM read of the row): NaN guard, row maximum, shared-memory copy
     float m = -INFINITY;
     int nn = 0;
+#pragma unroll 4
     for (int i = tid; i < n4; i += kBigThreads) {
-        float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
-        if (ntz) {
-            nn += (v.x != v.x) + (v.y != v.y) + (v.z != v.z) + (v.w != v.w);
-            v.x = nan_fix(v.x, true); v.y = nan_fix(v.y, true); v.z = nan_fix(v.z, true); v.w = nan_fix(v.w, true);
-        }
+        const float4 v = nan_fix4(__ldcs(x4 + i), ntz, nn);
+        if (staged) s4[i] = v;
         m = fmaxf(fmaxf(m, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
     }
     for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) {
-        const float v = __ldg(x + c);
+        float v = __ldcs(x + c);
         nn += (ntz && v != v);
-        m = fmaxf(m, nan_fix(v, ntz));
+        v = nan_fix(v, ntz);
+        if (staged) srow[c] = v;
+        m = fmaxf(m, v);
     }
     if (nn && p.nan_count) atomicAdd(p.nan_count, nn);
     m = block_reduce(m, red, true);
-    float sum = 0.f;
-    for (int i = tid; i < n4; i += kBigThreads) {  // second pass hits L1/L2
-        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
-        sum += (expf(nan_fix(v.x, ntz) - m) + expf(nan_fix(v.y, ntz) - m)) +
-               (expf(nan_fix(v.z, ntz) - m) + expf(nan_fix(v.w, ntz) - m));
-    }
-    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) sum += expf(nan_fix(__ldg(x + c), ntz) - m);
-    sum = block_reduce(sum, red, false);
-    const float inv = 1.0f / sum;
-    if (tid == 0) p.rowstat[row] = make_float2(m, inv);
-    if (p.path != nullptr) {  // best path by-product: first class attaining the row maximum (third pass hits L1/L2)
+    if (p.path != nullptr) {  // best path by-product: first class attaining the row maximum
         int *s_arg = reinterpret_cast<int *>(red) + 40;
         if (tid == 0) *s_arg = 0x7fffffff;
         __syncthreads();
         int cand = 0x7fffffff;
         for (int c = tid; c < C; c += kBigThreads)
-            if (nan_fix(__ldg(x + c), ntz) == m) { cand = c; break; }
+            if ((staged ? srow[c] : nan_fix(__ldg(x + c), ntz)) == m) { cand = c; break; }
         if (cand != 0x7fffffff) atomicMin(s_arg, cand);
         __syncthreads();
         if (tid == 0) p.path[(size_t)b * p.T + t] = *s_arg;
     }
-    // compact emission row, planar fp64 words
+    // ---- pass 2 (shared memory, or L2 for rows too long to stage): exponentials in place, row sum
+    float sum = 0.f;
+    for (int i = tid; i < n4; i += kBigThreads) {
+        int dummy = 0;
+        const float4 v = staged ? s4[i] : nan_fix4(__ldg(x4 + i), ntz, dummy);
+        float4 e;
+        e.x = expf(v.x - m); e.y = expf(v.y - m); e.z = expf(v.z - m); e.w = expf(v.w - m);
+        if (staged) s4[i] = e;
+        sum += (e.x + e.y) + (e.z + e.w);
+    }
+    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads) {
+        const float e = expf((staged ? srow[c] : nan_fix(__ldg(x + c), ntz)) - m);
+        if (staged) srow[c] = e;
+        sum += e;
+    }
+    sum = block_reduce(sum, red, false);  // its barriers also publish the exponentials to the whole CTA
+    const float inv = 1.0f / sum;
+    // ---- pass 3: the dense part of the gradient, scale * softmax, written once (the occupancies of the <= 1 + L
+    // classes on the lattice are subtracted by the gradient kernel)
+    if (g) {
+        const float scale = p.grad_scale;
+        const int g4 = (vec && gvec) ? n4 : 0;
+        for (int i = tid; i < g4; i += kBigThreads) {
+            float4 e;
+            if (staged) {
+                e = s4[i];
+            } else {
+                int dummy = 0;
+                const float4 v = nan_fix4(__ldg(x4 + i), ntz, dummy);
+                e.x = expf(v.x - m); e.y = expf(v.y - m); e.z = expf(v.z - m); e.w = expf(v.w - m);
+            }
+            float4 o;
+            o.x = scale * fmaxf(e.x * inv, 1.17549435e-38f);
+            o.y = scale * fmaxf(e.y * inv, 1.17549435e-38f);
+            o.z = scale * fmaxf(e.z * inv, 1.17549435e-38f);
+            o.w = scale * fmaxf(e.w * inv, 1.17549435e-38f);
+            __stcs(reinterpret_cast<float4 *>(g) + i, o);
+        }
+        for (int c = (g4 << 2) + tid; c < C; c += kBigThreads) {
+            const float e = staged ? srow[c] : expf(nan_fix(__ldg(x + c), ntz) - m);
+            g[c] = scale * fmaxf(e * inv, 1.17549435e-38f);
+        }
+    }
+    // ---- compact emission row, planar fp64 words
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
     const int *lab = p.labels;
     const int off = p.laboff[b];  // written by ctc_prep_utt_kernel, launched before this kernel
@@ -1188,61 +1375,11 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
         float v = 1.17549435e-38f;
         if (j <= L) {
             const int c = (j == 0) ? p.blank : min(max(lab[off + j - 1], 0), C - 1);
-            v = fmaxf(expf(nan_fix(__ldg(x + c), ntz) - m) * inv, 1.17549435e-38f);
+            const float e = staged ? srow[c] : expf(nan_fix(__ldg(x + c), ntz) - m);
+            v = fmaxf(e * inv, 1.17549435e-38f);
         }
         ydst[j] = y_hi_word(v);
         ydst[CP + j] = y_lo_word(v);
-    }
-}
-
-// One CTA per valid (t,b) row: dense softmax gradient streamed out (float4), then the <= 1 + L occupancies are
-// subtracted in place, one thread per distinct class (class-sorted order => deterministic sums for repeated classes).
-template <int CP>
-__global__ void __launch_bounds__(kBigThreads) ctc_final_big_kernel(const CtcParams p) {
-    const int tid = threadIdx.x;
-    const int C = p.C;
-    const long long row = blockIdx.x;
-    const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
-    if (t >= min(max(p.act_lens[b], 0), p.T)) return;  // zero-filled by the prep kernel
-    float *g = p.grads + row * C;
-    if (!p.feas[b]) {
-        for (int c = tid; c < C; c += kBigThreads) g[c] = 0.f;
-        return;
-    }
-    const float *x = p.acts + row * C;
-    const float2 st = p.rowstat[row];
-    const float m = st.x, inv = st.y, scale = p.grad_scale;
-    const bool vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
-    const int n4 = vec ? (C >> 2) : 0;
-    const bool ntz = p.nan_to_zero != 0;
-    for (int i = tid; i < n4; i += kBigThreads) {
-        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
-        float4 o;
-        o.x = scale * fmaxf(expf(nan_fix(v.x, ntz) - m) * inv, 1.17549435e-38f);
-        o.y = scale * fmaxf(expf(nan_fix(v.y, ntz) - m) * inv, 1.17549435e-38f);
-        o.z = scale * fmaxf(expf(nan_fix(v.z, ntz) - m) * inv, 1.17549435e-38f);
-        o.w = scale * fmaxf(expf(nan_fix(v.w, ntz) - m) * inv, 1.17549435e-38f);
-        reinterpret_cast<float4 *>(g)[i] = o;
-    }
-    for (int c = (n4 << 2) + tid; c < C; c += kBigThreads)
-        g[c] = scale * fmaxf(expf(nan_fix(__ldg(x + c), ntz) - m) * inv, 1.17549435e-38f);
-    __syncthreads();  // this CTA's own global writes are visible to it after the barrier
-    const int L = min(max(p.label_lens[b], 0), p.Lmax);
-    const int *lab = p.labels + p.laboff[b];
-    const int *ord = p.order + (size_t)b * p.Lmax;
-    const float *occ = p.occpos + ((size_t)b * p.T + t) * CP;
-    for (int j = tid; j <= L; j += kBigThreads) {
-        if (j == L) {  // blank
-            g[p.blank] -= scale * occ[0];
-        } else {
-            const int i0 = ord[j];
-            const int c = lab[i0];
-            if (j == 0 || lab[ord[j - 1]] != c) {  // first position of this class in sorted order
-                float sum = occ[1 + i0];
-                for (int jj = j + 1; jj < L && lab[ord[jj]] == c; ++jj) sum += occ[1 + ord[jj]];
-                g[c] -= scale * sum;
-            }
-        }
     }
 }
 

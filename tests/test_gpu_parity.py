@@ -118,6 +118,33 @@ def test_large_alphabet_edges(oracle, b200):
         _check(oracle, b200, d, device_lens=True, grad_scale=0.25)
 
 
+@pytest.mark.parametrize("C", [132, 5120, 6000, 10000, 16388, 20000])
+def test_large_alphabet_row_kernels(oracle, b200, C):
+    # every form of the large-alphabet row kernel: rows kept in registers (5 / 8 / 16 float4 per thread), rows staged
+    # in shared memory (C % 4 != 0 or > 16384 classes), rows too long to stage (re-read through L2); repeated
+    # classes within an utterance, padding frames, an infeasible utterance and gradient scaling
+    T, B = 24, 6
+    g = torch.Generator().manual_seed(C)
+    acts = torch.randn(T, B, C, generator=g) * 3.0
+    targets = [[C - 1, 7, 7, 9, C - 1, 3], [1], [5] * 10, [2, 4, 6, 8, 10, 12, 14, 16], [], [11, 11, 11]]
+    act_lens = torch.tensor([24, 5, 24, 17, 9, 4], dtype=torch.int32)  # utt 5: 3 + 2 repeats > 4 -> infeasible
+    labels, ll = b200.pack_targets(targets)
+    d = {"acts": acts, "labels": labels, "act_lens": act_lens, "label_lens": ll}
+    costs, grads = _check(oracle, b200, d, zero_infinity=True)
+    assert costs[5] == 0.0 and np.all(grads[:, 5] == 0)
+    for b in range(B):
+        assert np.all(grads[int(act_lens[b]):, b, :] == 0.0)
+    _check(oracle, b200, d, device_lens=True, grad_scale=0.125)
+    # a view whose rows are 16-byte aligned but whose base is not: falls back to the generic kernel (scalar loads, another summation order)
+    if C % 4 == 0:
+        pad = torch.zeros(T * B * C + 1, device="cuda")
+        pad[1:] = acts.reshape(-1).cuda()
+        d2 = dict(d, acts=pad[1:].view(T, B, C))
+        assert d2["acts"].data_ptr() % 16 == 4
+        c2, g2 = _run(b200, d2)
+        assert np.abs(c2 - costs).max() <= 1e-5 * np.abs(costs).max() and np.abs(g2 - grads).max() <= 2e-6
+
+
 def test_grad_scale_and_score_only(oracle, b200):
     d = _wl(b200, "cpu_b16_t500")
     _check(oracle, b200, d, grad_scale=1.0 / 16)

@@ -112,6 +112,8 @@ def load_traffic(kernel, workload):
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
+        if workload in t.get("workloads", {}):
+            return t["workloads"][workload]["bytes"][kernel]
         return t["bytes"][kernel] if t.get("workload") == workload else None
     except (OSError, KeyError, ValueError):
         return None

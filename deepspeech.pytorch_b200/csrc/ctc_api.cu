@@ -298,9 +298,12 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
 // Large alphabets: ONE row kernel over the whole batch (softmax, dense gradient part, emission gather -- the
 // HBM-bound part, every logit read once and every gradient element written once), then the sliced lattice launches
 // of the small path; the gradient kernel subtracts the occupancies in place.
-// Measured and rejected on B200 (B=64, T=1000, C=5000): a per-slice pipeline (row kernel of slice k+1 on a
-// low-priority stream under the lattice kernels of slice k) -- the row kernels stretched from 0.40 to 0.64 ms under
-// the co-running lattice kernels and the step got slower (0.66-0.71 ms against 0.63).
+// Measured and rejected on B200 (B=64, T=1000, C=5000; 0.593 ms as shipped): a per-slice pipeline (row kernel of
+// slice k+1 on its own stream under the lattice kernels of slice k; 2 / 3 / 4 / 8 slices, with and without stream
+// priorities, gradient kernels held back until all rows are done or not): 0.586 - 0.66 ms.  The row kernel needs its
+// full occupancy (6 CTAs/SM: 0.357 ms, 5: 0.41, 4: 0.46), so either the lattice kernels wait for free slots until the
+// row kernel drains, or (with priorities) they take the slots and the rows slow down by more than the recursion hides;
+// the gradient kernel's scattered reductions also disturb the streaming.
 cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
                        cudaEvent_t costs_ready) {
     constexpr int CP = 256;
@@ -312,6 +315,12 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         e = cudaFuncSetAttribute(ctc_prep_utt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ctc_prep_big_kernel<CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_prep_big_reg_kernel<CP, 16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_prep_big_reg_kernel<CP, 16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ctc_engine_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -333,16 +342,15 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
     // rows that are 16-byte aligned and fit 5 / 8 / 16 float4 per thread stay in registers
     const bool aligned = (p.C % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.acts) & 15) == 0) &&
                          (!p.grads || (reinterpret_cast<uintptr_t>(p.grads) & 15) == 0);
-    auto rows = [&](CtcParams pk, int nb, cudaStream_t s) {
+    auto rows_at = [&](CtcParams pk, int nb, cudaStream_t s) {
         pk.slice_nb = nb;
-        pk.bord = nullptr;  // whole batch in memory order
-        pk.slice0 = 0;
         const unsigned grid = (unsigned)((long long)p.T * nb);
         const bool ntz = p.nan_to_zero != 0;
+        const size_t smem_reg = 256 + sizeof(float) * (size_t)p.C;
 #define CTC_ROWS_REG(NV)                                                                              \
         do {                                                                                              \
-            if (ntz) ctc_prep_big_reg_kernel<CP, NV, true><<<grid, kBigThreads, 0, s>>>(pk);            \
-            else ctc_prep_big_reg_kernel<CP, NV, false><<<grid, kBigThreads, 0, s>>>(pk);               \
+            if (ntz) ctc_prep_big_reg_kernel<CP, NV, true><<<grid, kBigThreads, smem_reg, s>>>(pk);            \
+            else ctc_prep_big_reg_kernel<CP, NV, false><<<grid, kBigThreads, smem_reg, s>>>(pk);               \
         } while (0)
         if (aligned && p.C <= 1024 * 5) CTC_ROWS_REG(5);
         else if (aligned && p.C <= 1024 * 8) CTC_ROWS_REG(8);
@@ -350,6 +358,11 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         else ctc_prep_big_kernel<CP><<<grid, kBigThreads, pl.smem_rows, s>>>(pk);
 #undef CTC_ROWS_REG
         ++*launches;
+    };
+    auto rows = [&](CtcParams pk, int nb, cudaStream_t s) {
+        pk.bord = nullptr;  // whole batch in memory order
+        pk.slice0 = 0;
+        rows_at(pk, nb, s);
     };
     auto eng = [&](const CtcParams &pk, int nb, cudaStream_t s) {
         ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);

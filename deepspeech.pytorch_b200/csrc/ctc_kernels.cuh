@@ -1171,12 +1171,14 @@ __device__ __forceinline__ float4 nan_fix4(float4 v, bool ntz, int &nn) {
 }
 
 // Register-resident form of the row kernel for 16-byte-aligned rows of C <= 1024 * NV classes (C % 4 == 0): thread i
-// keeps float4 i, i + 256, ... of the row in registers across the three passes, so the row is read from DRAM once,
-// never staged, and the only re-reads are the 1 + L gathered emissions (L2).  Same arithmetic and summation order
+// keeps float4 i, i + 256, ... of the row in registers across the three passes, so the row is read from DRAM once;
+// the exponentials are also dropped into shared memory (one store per float4) for the 1 + L gathered emissions.  Same arithmetic and summation order
 // as the float4 form of the generic kernel below.
 template <int CP, int NV, bool NTZ>
 __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const CtcParams p) {
-    __shared__ float red[48];
+    extern __shared__ __align__(16) unsigned char smem[];
+    float *red = reinterpret_cast<float *>(smem);
+    float4 *s4 = reinterpret_cast<float4 *>(smem + 256);  // exponentials of the row, for the emission gather
     const int tid = threadIdx.x;
     const int C = p.C;
     const int t = (int)(blockIdx.x / (unsigned)p.slice_nb), bi = (int)(blockIdx.x - (unsigned)t * (unsigned)p.slice_nb);
@@ -1231,9 +1233,10 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const Ctc
         if (tid + k * kBigThreads < n4) {
             v[k].x = expf(v[k].x - m); v[k].y = expf(v[k].y - m); v[k].z = expf(v[k].z - m); v[k].w = expf(v[k].w - m);
             sum += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+            s4[tid + k * kBigThreads] = v[k];
         }
     }
-    sum = block_reduce(sum, red, false);
+    sum = block_reduce(sum, red, false);  // its barriers also publish the exponentials to the whole CTA
     const float inv = 1.0f / sum;
     if (g4) {
         const float scale = p.grad_scale;
@@ -1250,16 +1253,17 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const Ctc
             }
         }
     }
-    // compact emission row, planar fp64 words (the 1 + L logits are re-read: L2 hits)
+    // compact emission row, planar fp64 words.  (Re-reading the 1 + L logits from global memory instead cost 240 MB
+    // of DRAM reads per step at C = 5000: the streaming loads above do not keep the row in L2.)
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
     const int off = p.laboff[b];  // written by ctc_prep_utt_kernel, launched before this kernel
-    const float *x = reinterpret_cast<const float *>(x4);
+    const float *srow = reinterpret_cast<const float *>(s4);
     unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * CP;
     for (int j = tid; j < CP; j += kBigThreads) {
         float y = 1.17549435e-38f;
         if (j <= L) {
             const int c = (j == 0) ? p.blank : min(max(p.labels[off + j - 1], 0), C - 1);
-            y = fmaxf(expf(nan_fix(__ldg(x + c), NTZ) - m) * inv, 1.17549435e-38f);
+            y = fmaxf(srow[c] * inv, 1.17549435e-38f);
         }
         ydst[j] = y_hi_word(y);
         ydst[CP + j] = y_lo_word(y);

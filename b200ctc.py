@@ -28,6 +28,7 @@ CTCLoss = pkg.CTCLoss
 ctc_forward_backward = pkg.ctc_forward_backward
 GreedyDecoder = pkg.GreedyDecoder
 greedy_decode = pkg.greedy_decode
+error_counts = pkg.error_counts
 last_launch_count = pkg.last_launch_count
 build = pkg.build
 Labels = pkg.Labels

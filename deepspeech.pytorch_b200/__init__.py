@@ -9,9 +9,9 @@ The directory name contains a dot, so it is imported through the loader in /root
 """
 from . import _lib, packing, sharding, workloads  # noqa: F401
 from ._lib import build  # noqa: F401
-from .ctc_loss import (CTCLoss, GreedyDecoder, ctc_forward_backward, greedy_decode,  # noqa: F401
+from .ctc_loss import (CTCLoss, GreedyDecoder, ctc_forward_backward, error_counts, greedy_decode,  # noqa: F401
                        last_launch_count)
 from .packing import ALPHABET, BLANK_INDEX, Labels, pack_targets  # noqa: F401
 
-__all__ = ["CTCLoss", "GreedyDecoder", "ctc_forward_backward", "greedy_decode", "last_launch_count", "build", "ALPHABET", "BLANK_INDEX", "Labels",
+__all__ = ["CTCLoss", "GreedyDecoder", "ctc_forward_backward", "error_counts", "greedy_decode", "last_launch_count", "build", "ALPHABET", "BLANK_INDEX", "Labels",
            "pack_targets", "packing", "sharding", "workloads"]

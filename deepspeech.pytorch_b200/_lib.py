@@ -13,7 +13,7 @@ import subprocess
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, "libctc_b200.so")
-SOURCES = [os.path.join(_PKG, "csrc", f) for f in ("ctc_api.cu", "ctc_kernels.cuh", "ctc_device.cuh")] + [
+SOURCES = [os.path.join(_PKG, "csrc", f) for f in ("ctc_api.cu", "ctc_kernels.cuh", "ctc_device.cuh", "ctc_metrics.cuh")] + [
     os.path.join(_ROOT, "include", "ctc_b200.h")
 ]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
@@ -21,7 +21,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 EXPORTS = ("ctc_b200_get_version", "ctc_b200_status_string", "ctc_b200_default_options", "ctc_b200_workspace_size",
            "ctc_b200_compute", "ctc_b200_create", "ctc_b200_destroy", "ctc_b200_compute_host",
-           "ctc_b200_compute_decode", "ctc_b200_greedy_decode", "ctc_b200_last_launch_count")
+           "ctc_b200_compute_decode", "ctc_b200_greedy_decode", "ctc_b200_error_counts", "ctc_b200_last_launch_count")
 
 
 class CtcOptions(ctypes.Structure):
@@ -87,6 +87,8 @@ def load():
     lib.ctc_b200_compute_host.restype = I
     lib.ctc_b200_compute_decode.argtypes = [V, V, V, V, V, I, I, I, V, V, ctypes.c_size_t, V, V, V, V, P(CtcOptions)]
     lib.ctc_b200_compute_decode.restype = I
+    lib.ctc_b200_error_counts.argtypes = [V, I, V, V, V, I, I, I, I, V, P(CtcOptions)]
+    lib.ctc_b200_error_counts.restype = I
     lib.ctc_b200_greedy_decode.argtypes = [V, ctypes.c_longlong, ctypes.c_longlong, V, I, I, I, V, V, V, V,
                                            P(CtcOptions)]
     lib.ctc_b200_greedy_decode.restype = I

@@ -18,6 +18,7 @@
 
 #include "../../include/ctc_b200.h"
 #include "ctc_kernels.cuh"
+#include "ctc_metrics.cuh"
 
 using namespace ctcb200;
 
@@ -571,6 +572,35 @@ extern "C" ctcB200Status ctc_b200_greedy_decode(const float *acts, long long str
         ++g_last_launches;
     }
     ctc_collapse_kernel<<<B, kCollapseThreads, 0, st>>>(path, act_lens_dev, T, B, o.blank, ids, offsets, out_lens);
+    ++g_last_launches;
+    return cudaGetLastError() == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
+}
+
+// ------------------------------------------------------------------------------------------------ WER / CER counts
+extern "C" ctcB200Status ctc_b200_error_counts(const int *hyp_ids, int hyp_pitch, const int *hyp_lens,
+                                               const int *ref_labels, const int *ref_lens, int B, int max_hyp_len,
+                                               int max_ref_len, int space_index, int *counts,
+                                               const ctcB200Options *opts_in) {
+    g_last_launches = 0;
+    ctcB200Options o;
+    if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
+    if (!hyp_ids || !hyp_lens || !ref_lens || !counts) return CTC_B200_STATUS_INVALID_VALUE;
+    if (B < 1 || max_hyp_len < 0 || max_ref_len < 0 || hyp_pitch < max_hyp_len) return CTC_B200_STATUS_INVALID_VALUE;
+    if (max_ref_len > 0 && !ref_labels) return CTC_B200_STATUS_INVALID_VALUE;
+    const size_t smem = metrics_smem(max_hyp_len, max_ref_len);
+    if (smem > kSmemLimit) return CTC_B200_STATUS_INVALID_VALUE;  // sequences too long for one CTA's shared memory
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        if (cudaFuncSetAttribute(ctc_error_counts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit) != cudaSuccess)
+            return CTC_B200_STATUS_EXECUTION_FAILED;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    ctc_error_counts_kernel<<<B, kMetricThreads, smem, (cudaStream_t)o.stream>>>(
+        hyp_ids, hyp_pitch, hyp_lens, ref_labels, ref_lens, B, max_hyp_len, max_ref_len, space_index,
+        reinterpret_cast<int4 *>(counts));
     ++g_last_launches;
     return cudaGetLastError() == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }

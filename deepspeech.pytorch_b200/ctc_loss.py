@@ -209,6 +209,43 @@ class GreedyDecoder:
     def decode(self, probs: torch.Tensor, sizes=None):
         return self.strings_from(self.decode_ids(probs, sizes, batch_first=True))
 
+    def error_counts(self, best, targets: torch.Tensor, target_sizes: torch.Tensor, max_target_len: int):
+        """(wer, cer, wer_ref, cer_ref) per utterance, CUDA int32 [B,4], for a `decode_ids` result (or the `best` of
+        ctc_forward_backward(decode=True)) against the criterion's flat targets -- what the reference's loops at
+        train.py:369-385 / 577-591 accumulate through get_cer_wer, without leaving the device."""
+        dev = best["ids"].device
+        return error_counts(best["ids"], best["lens"], _as_i32(targets, "targets").to(dev),
+                            _as_i32(target_sizes, "target_sizes").to(dev), self.space_index, max_target_len)
+
+
+def error_counts(hyp_ids: torch.Tensor, hyp_lens: torch.Tensor, ref_labels: torch.Tensor, ref_lens: torch.Tensor,
+                 space_index: int, max_ref_len: int, max_hyp_len: Optional[int] = None) -> torch.Tensor:
+    """Per-utterance (wer, cer, wer_ref, cer_ref) as a CUDA int32 [B,4] tensor -- the numbers `get_cer_wer`
+    (data/utils.py:47-57 over decoder.py:44-73) returns for transcript b against reference b, computed on the device
+    from the decoder's collapsed ids [B,P] + lens [B] and the criterion's flat targets + target sizes (all CUDA int32).
+    No host synchronisation; one kernel on the current stream."""
+    for name, t in (("hyp_ids", hyp_ids), ("hyp_lens", hyp_lens), ("ref_labels", ref_labels), ("ref_lens", ref_lens)):
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.int32):
+            raise ValueError(f"{name} must be a CUDA int32 tensor (no CPU fallback exists)")
+    if hyp_ids.dim() != 2 or hyp_lens.numel() != hyp_ids.shape[0] or ref_lens.numel() != hyp_ids.shape[0]:
+        raise ValueError("hyp_ids must be [B,P] with one hyp_len and one ref_len per row")
+    lib = _lib.load()
+    hyp_ids, hyp_lens = hyp_ids.contiguous(), hyp_lens.contiguous()
+    ref_labels, ref_lens = ref_labels.contiguous(), ref_lens.contiguous()
+    B, P = hyp_ids.shape
+    dev = hyp_ids.device
+    opts = _lib.CtcOptions()
+    lib.ctc_b200_default_options(ctypes.byref(opts))
+    with torch.cuda.device(dev):
+        opts.stream = torch.cuda.current_stream(dev).cuda_stream
+        counts = torch.empty(B, 4, dtype=torch.int32, device=dev)
+        st = lib.ctc_b200_error_counts(hyp_ids.data_ptr(), P, hyp_lens.data_ptr(),
+                                       ref_labels.data_ptr() if ref_labels.numel() else None, ref_lens.data_ptr(), B,
+                                       P if max_hyp_len is None else int(max_hyp_len), int(max_ref_len),
+                                       int(space_index), counts.data_ptr(), ctypes.byref(opts))
+        _lib.check(st, "ctc_b200_error_counts")
+    return counts
+
 
 def last_launch_count() -> int:
     return int(_lib.load().ctc_b200_last_launch_count())

@@ -145,6 +145,28 @@ ctcB200Status ctc_b200_greedy_decode(const float *acts, long long stride_t, long
                                      const int *act_lens_dev, int T, int B, int C, int *path, int *ids, int *offsets,
                                      int *out_lens, const ctcB200Options *opts);
 
+/*
+ * Word / character error counts of decoded transcripts against the targets -- SURVEY.md 8(f) rank 4.  Replaces, per
+ * utterance, get_cer_wer (/root/reference/data/utils.py:47-57) over Decoder.wer / Decoder.cer
+ * (/root/reference/decoder.py:44-73), which the reference evaluates in Python (python-Levenshtein) for every
+ * utterance of every training and eval batch (train.py:369-385, 577-591):
+ *   counts[4*b + 0] = wer     : edit distance between the WORD sequences (words = maximal runs of non-space ids)
+ *   counts[4*b + 1] = cer     : edit distance between the id sequences with the spaces removed
+ *   counts[4*b + 2] = wer_ref : number of reference words, or 1 if there is none
+ *   counts[4*b + 3] = cer_ref : number of reference non-space ids, or 1 if there is none
+ * (the reference's strings map 1:1 to label ids, decoder.py:165-180, so the counts are computed on ids).
+ *   hyp_ids   : DEVICE int32 [B][hyp_pitch], utterance b in hyp_ids[b*hyp_pitch .. + hyp_lens[b]) -- the `ids` /
+ *               `out_lens` outputs of ctc_b200_compute_decode / ctc_b200_greedy_decode (hyp_pitch = T)
+ *   ref_labels: DEVICE int32 flat targets in batch order, ref_lens: DEVICE int32 [B] -- the criterion's own inputs
+ *   max_hyp_len / max_ref_len: upper bounds on hyp_lens / ref_lens (size the CTA's shared memory; longer sequences
+ *               are truncated); INVALID_VALUE if they do not fit one CTA (about 6*max_hyp + 3*max_ref ints)
+ *   counts    : DEVICE int32 [B][4]
+ * Integer results, bit-exact against oracle/wer_oracle.py.  Enqueues one kernel on opts->stream and returns.
+ */
+ctcB200Status ctc_b200_error_counts(const int *hyp_ids, int hyp_pitch, const int *hyp_lens, const int *ref_labels,
+                                    const int *ref_lens, int B, int max_hyp_len, int max_ref_len, int space_index,
+                                    int *counts, const ctcB200Options *opts);
+
 /* number of kernel launches the last ctc_b200_compute on this thread enqueued (bench.py's gpu_launches claim) */
 int ctc_b200_last_launch_count(void);
 

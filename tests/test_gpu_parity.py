@@ -2,6 +2,8 @@
 
 Tolerance (BASELINE.json north_star): loss rel <= 1e-5, grad abs <= 1e-5 against the fp64 oracle.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -439,3 +441,72 @@ def test_nan_guard_module(oracle, b200):
     l1 = crit(clean, d["labels"], d["act_lens"], d["label_lens"])
     l0 = b200.CTCLoss()(clean, d["labels"], d["act_lens"], d["label_lens"])
     assert int(crit.nan_count.item()) == 0 and l1.item() == l0.item()
+
+
+def test_cuda_graph_capture_of_the_loss_step(oracle, b200):
+    # with lengths and labels resident on the device the whole loss step (prep, sliced engine and
+    # gradient launches on the library's side streams, forked from / joined to the caller's stream by events) is
+    # capturable in a CUDA graph; replaying it on new logits gives the bits of an eager call.
+    for name, B in (("cpu_b16_t500", 32), ("bigc_b64_t1000_c5000", 16)):
+        d = _wl(b200, name, seed=9, B=B)
+        acts = d["acts"].cuda()
+        lab, al, ll = d["labels"].cuda(), d["act_lens"].cuda(), d["label_lens"].cuda()
+        lmax = int(d["label_lens"].max())
+        grads = torch.empty_like(acts)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):  # warm-up outside the capture: pools, attributes, workspace
+            for _ in range(2):
+                b200.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            costs_g, _ = b200.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads)
+        new_acts = torch.randn(acts.shape, generator=torch.Generator().manual_seed(77)) * 2.0
+        acts.copy_(new_acts.cuda())
+        grads.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        c_graph, g_graph = costs_g.cpu().numpy().copy(), grads.cpu().numpy().copy()
+        c_eager, g_eager = b200.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax)
+        torch.cuda.synchronize()
+        assert np.array_equal(c_graph, c_eager.cpu().numpy()) and np.array_equal(g_graph, g_eager.cpu().numpy())
+        oc, og = oracle.compute(new_acts.numpy(), d["labels"].numpy(), d["act_lens"].numpy(), d["label_lens"].numpy())
+        assert np.abs(c_graph - oc).max() <= LOSS_RTOL * np.abs(oc).max()
+        assert np.abs(g_graph - og).max() <= GRAD_ATOL
+
+
+def test_error_counts_match_reference_goldens(b200):
+    # WER / CER counts on the device, bit-exact against the reference's get_cer_wer goldens
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "wer_cases.npz"))
+    hyp = torch.from_numpy(g["hyp_ids"]).cuda()
+    got = b200.error_counts(hyp, torch.from_numpy(g["hyp_lens"]).cuda(), torch.from_numpy(g["ref_flat"]).cuda(),
+                            torch.from_numpy(g["ref_lens"]).cuda(), int(g["space"]), int(g["ref_lens"].max()))
+    torch.cuda.synchronize()
+    assert np.array_equal(got.cpu().numpy(), g["counts"])
+
+
+def test_error_counts_of_the_fused_decode(b200):
+    # the training-loop use: loss + gradient + best path in one call, then error counts of the best path against the
+    # same flat targets, everything on the device; checked against the CPU restatement at the headline shape
+    # (random logits: hypotheses of ~1400 symbols against references of up to 415)
+    from oracle import greedy_oracle, wer_oracle
+
+    d = _wl(b200, "headline_b64_t1500", C=30)
+    labels = "".join(b200.ALPHABET)
+    dec = b200.GreedyDecoder(labels, blank_index=labels.index("_"))
+    costs, grads, best = b200.ctc_forward_backward(d["acts"].cuda(), d["labels"], d["act_lens"], d["label_lens"],
+                                                   decode=True)
+    counts = dec.error_counts(best, d["labels"], d["label_lens"], int(d["label_lens"].max()))
+    torch.cuda.synchronize()
+    _, ids, _ = greedy_oracle.decode(d["acts"].numpy(), d["act_lens"].numpy(), blank=0)
+    P = max(len(i) for i in ids)
+    hyp = np.zeros((len(ids), P), np.int32)
+    for b, i in enumerate(ids):
+        hyp[b, :len(i)] = i
+    want = wer_oracle.batch_counts(hyp, [len(i) for i in ids], d["labels"].numpy(), d["label_lens"].numpy(),
+                                   dec.space_index)
+    assert np.array_equal(counts.cpu().numpy(), np.array(want, np.int32))
+    with pytest.raises(ValueError):
+        b200.error_counts(best["ids"].cpu(), best["lens"], d["labels"].cuda(), d["label_lens"].cuda(), 29, 10)

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 GOLDEN = sorted(f for f in glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz"))
-                if not os.path.basename(f).startswith("greedy_"))
+                if os.path.basename(f).startswith("g_"))
 
 
 def test_golden_present():
@@ -114,3 +114,16 @@ def test_greedy_oracle_against_reference_decoder_goldens():
         assert go.to_strings(ids, str(z["labels"])) == [str(s) for s in z["strings"]]
         assert [len(i) for i in ids] == z["lens"].tolist()
         assert np.array_equal(np.concatenate([np.asarray(o, np.int32) for o in offs]), z["offsets"])
+
+
+def test_wer_oracle_against_reference_goldens():
+    # tests/golden/wer_cases.npz: the reference's own get_cer_wer / Decoder.wer / Decoder.cer (make_golden_wer.py)
+    from oracle import wer_oracle
+
+    # the distance function itself: definition-level known answers
+    lev = wer_oracle.levenshtein
+    assert lev("kitten", "sitting") == 3 and lev("flaw", "lawn") == 2 and lev("", "abc") == 3 and lev("abc", "") == 3
+    assert lev("abc", "abc") == 0 and lev("ab", "ba") == 2 and lev("intention", "execution") == 5
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "wer_cases.npz"))
+    got = wer_oracle.batch_counts(g["hyp_ids"], g["hyp_lens"], g["ref_flat"], g["ref_lens"], int(g["space"]))
+    assert np.array_equal(np.array(got, np.int32), g["counts"])

@@ -65,6 +65,20 @@ def main():
     go.decode(d["acts"][:, :nb].numpy(), d["act_lens"][:nb].numpy(), 0)
     t_cpu = (time.perf_counter() - t0) * w.B / nb * 1e3
     frames = w.B * w.T
+    # error counts of the best path against the targets: device kernel vs the CPU restatement
+    from oracle import wer_oracle as wo  # noqa: E402  (checker / CPU baseline only)
+    _, _, best = b200ctc.ctc_forward_backward(acts, lab, al, ll, decode=True, **kw)
+    space = b200ctc.ALPHABET.index(" ") if w.C >= 30 else w.C - 1
+    t_err_dev = device_time(lambda: b200ctc.error_counts(best["ids"], best["lens"], lab, ll, space, lmax))
+    ids_h, lens_h = best["ids"].cpu().numpy(), best["lens"].cpu().numpy()
+    t0 = time.perf_counter()
+    wo.batch_counts(ids_h[:2], lens_h[:2], d["labels"].numpy(), d["label_lens"][:2].numpy(), space)
+    t_err_cpu = (time.perf_counter() - t0) * w.B / 2 * 1e3
+    print(json.dumps({"op": "error_counts", "workload": w.name, "device_ms": t_err_dev,
+                      "mean_hyp_len": float(lens_h.mean()), "mean_ref_len": float(d["label_lens"].float().mean()),
+                      "cpu_port_ms_full_batch": t_err_cpu,
+                      "cpu_sample": f"2 of {w.B} utterances, pure-Python DP (the reference uses python-Levenshtein's "
+                                    "C implementation, not installed here), scaled"}))
     print(json.dumps({"op": "greedy_decode", "workload": w.name, "frames": frames,
                       "ctc_step_ms": t_plain, "ctc_step_with_decode_ms": t_fused,
                       "fused_extra_ms": t_fused - t_plain, "standalone_ms": t_alone,

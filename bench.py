@@ -181,23 +181,24 @@ def run_b200(args, w):
     grads = torch.empty_like(acts)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
     loss_acc = torch.zeros(1, dtype=torch.float32, device=dev)
+    loss_local = torch.zeros(1, dtype=torch.float32, device=dev)
 
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
     ready = torch.cuda.Event() if world > 1 else None
 
     def step(phase_mask=0):
         if phase_mask or world == 1:
-            costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
-                                                    phase_mask=phase_mask)
-            if phase_mask == 0:
-                loss_acc.copy_(costs.sum().reshape(1))
+            # the summed loss (the criterion's return value) is written to loss_acc by the library itself, by a
+            # one-warp kernel that runs beside the gradient kernels
+            b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
+                                         phase_mask=phase_mask, loss_sum=loss_acc if phase_mask == 0 else None)
             return
         # N > 1: the path's one exchange -- the summed loss over NVLink (NCCL) -- starts on a communication stream
         # as soon as the costs are final (`costs_ready`: recursions done) and overlaps the gradient kernels; the
         # compute stream joins it at the end of the step, so the step still contains the whole exchange.
         costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
-                                                costs_ready=ready)
-        b200ctc.sharding.overlapped_loss_all_reduce(costs, ready, comm, loss_acc)
+                                                costs_ready=ready, loss_sum=loss_local)
+        b200ctc.sharding.overlapped_loss_all_reduce(costs, ready, comm, loss_acc, local_sum=loss_local)
 
     def timed(nsteps, phase_mask=0):
         evs = []

@@ -181,9 +181,13 @@ inline void launch_collapse(const CtcParams &p, cudaStream_t s, int *launches) {
 
 template <typename EngineLaunch, typename GradLaunch>
 cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, bool do_engine, bool do_grad,
-                          int *launches, cudaEvent_t costs_ready, EngineLaunch eng, GradLaunch grd) {
+                          int *launches, cudaEvent_t costs_ready, float *loss_sum, EngineLaunch eng, GradLaunch grd) {
     if (pl.nslices <= 1 || (!do_engine && !do_grad)) {
         if (do_engine) eng(p, p.B, st);
+        if (loss_sum && do_engine) {
+            ctc_sum_costs_kernel<<<1, 32, 0, st>>>(p.costs, p.B, loss_sum);
+            ++*launches;
+        }
         if (costs_ready && cudaEventRecord(costs_ready, st) != cudaSuccess) return cudaErrorUnknown;
         if (do_grad) grd(p, p.B, st);
         launch_collapse(p, st, launches);
@@ -218,14 +222,19 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
             if (trace) cudaEventRecord(tr[k][pass], sp->side[k]);
         }
         if (pass == 0) {
-            if (costs_ready) {
-                // costs[] is final once every slice's recursion is done: gather those points on the aux stream and
-                // record the caller's event there; the gradient kernels are enqueued behind this and run on
+            if (costs_ready || loss_sum) {
+                // costs[] is final once every slice's recursion is done: gather those points on the aux stream, sum
+                // the costs and record the caller's event there; the gradient kernels are enqueued behind this and
+                // run on
                 for (int k = 0; k < ns; ++k) {
                     if ((e = cudaEventRecord(sp->eng_done[k], sp->side[k])) != cudaSuccess) return e;
                     if ((e = cudaStreamWaitEvent(sp->aux, sp->eng_done[k], 0)) != cudaSuccess) return e;
                 }
-                if ((e = cudaEventRecord(costs_ready, sp->aux)) != cudaSuccess) return e;
+                if (loss_sum) {
+                    ctc_sum_costs_kernel<<<1, 32, 0, sp->aux>>>(p.costs, p.B, loss_sum);
+                    ++*launches;
+                }
+                if (costs_ready && (e = cudaEventRecord(costs_ready, sp->aux)) != cudaSuccess) return e;
                 if ((e = cudaEventRecord(sp->aux_done, sp->aux)) != cudaSuccess) return e;
                 if ((e = cudaStreamWaitEvent(st, sp->aux_done, 0)) != cudaSuccess) return e;
             }
@@ -257,7 +266,7 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
 
 template <int CP>
 cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
-                          cudaEvent_t costs_ready) {
+                          cudaEvent_t costs_ready, float *loss_sum) {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -285,7 +294,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
     const bool do_engine = !(phase_mask & 1);
     const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
     return launch_sliced(
-        p, pl, st, do_engine, do_grad, launches, costs_ready,
+        p, pl, st, do_engine, do_grad, launches, costs_ready, loss_sum,
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
             ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
@@ -306,7 +315,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
 // row kernel drains, or (with priorities) they take the slots and the rows slow down by more than the recursion hides;
 // the gradient kernel's scattered reductions also disturb the streaming.
 cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
-                       cudaEvent_t costs_ready) {
+                       cudaEvent_t costs_ready, float *loss_sum) {
     constexpr int CP = 256;
     static bool attr_set[64] = {false};
     int dev = 0;
@@ -376,16 +385,16 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
     if ((long long)p.T * p.B >= (1ll << 31)) return cudaErrorInvalidValue;
     if (do_rows) rows(p, p.B, st);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    return launch_sliced(p, pl, st, do_engine, do_grad, launches, costs_ready, eng, grd);
+    return launch_sliced(p, pl, st, do_engine, do_grad, launches, costs_ready, loss_sum, eng, grd);
 }
 
 cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
-                       cudaEvent_t costs_ready) {
-    if (pl.big) return launch_big(p, pl, st, phase_mask, launches, costs_ready);
+                       cudaEvent_t costs_ready, float *loss_sum) {
+    if (pl.big) return launch_big(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
     switch (pl.Cp) {
-        case 32: return launch_all_cp<32>(p, pl, st, phase_mask, launches, costs_ready);
-        case 64: return launch_all_cp<64>(p, pl, st, phase_mask, launches, costs_ready);
-        default: return launch_all_cp<128>(p, pl, st, phase_mask, launches, costs_ready);
+        case 32: return launch_all_cp<32>(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
+        case 64: return launch_all_cp<64>(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
+        default: return launch_all_cp<128>(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
     }
 }
 
@@ -535,7 +544,7 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.nan_count = o.nan_to_zero ? o.nan_count : nullptr;
 
     int launches = 0;
-    cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches, (cudaEvent_t)o.costs_ready);
+    cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches, (cudaEvent_t)o.costs_ready, o.loss_sum);
     g_last_launches = launches;
     return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }
@@ -805,6 +814,7 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         ok.stream = (void *)st;
         ok.lengths_on_device = 1;
         ok.costs_ready = nullptr;  // meaningless here: the call synchronises before it returns
+        ok.loss_sum = nullptr;     // the host entry sums the downloaded costs itself
         ok.max_label_len = mxs[k] > 0 ? mxs[k] : 1;
         ctcB200Status s = compute_impl(da, dg, d_labels + lab_off[k], d_llen + b0, d_alen + b0, Tk, nb, C,
                                        c->d_costs + b0, static_cast<unsigned char *>(c->d_ws) + ws_off[k],

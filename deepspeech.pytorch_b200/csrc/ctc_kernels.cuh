@@ -1387,6 +1387,21 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
     }
 }
 
+// ================================================================================================ summed loss
+// loss = sum_b costs[b], the one-element value the criterion returns (train.py:600).  One warp, fixed order, fp64
+// accumulation: deterministic and independent of how the batch was sliced.  Runs beside the gradient kernels.
+__global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, int B, float *loss_sum) {
+    double acc = 0.0;
+    for (int base = 0; base < B; base += 32) {
+        const int i = base + (int)threadIdx.x;
+        double v = i < B ? (double)costs[i] : 0.0;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(kFull, v, d);
+        acc += v;
+    }
+    if (threadIdx.x == 0) *loss_sum = (float)acc;
+}
+
 // ================================================================================================ greedy decoding
 // SURVEY 8(f) rank 1 -- replaces GreedyDecoder.decode (/root/reference/decoder.py:182-197: argmax over classes per
 // frame) and process_string (:165-180: drop blanks and frames equal to the previous frame, keep the frame index of

@@ -52,12 +52,16 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
                          max_label_len: Optional[int] = None, phase_mask: int = 0,
                          out_grads: Optional[torch.Tensor] = None, decode: bool = False,
                          costs_ready: Optional[torch.cuda.Event] = None, nan_to_zero: bool = False,
-                         nan_count: Optional[torch.Tensor] = None):
+                         nan_count: Optional[torch.Tensor] = None, loss_sum: Optional[torch.Tensor] = None):
     """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
 
     nan_to_zero: NaN logits are read as 0 (the guard at train.py:595-598 of the reference, folded into the softmax
     pass; `acts` is left untouched).  nan_count: optional CUDA int32 tensor of one element, the number of NaN logits
     found in valid frames is added to it.
+
+    loss_sum: optional CUDA float32 tensor of one element; receives sum(costs) -- the criterion's return value --
+    from a one-warp kernel that runs beside the gradient kernels (fixed order, fp64 accumulation), so no reduction
+    has to be launched after the call.
 
     costs_ready: an event the library records as soon as `costs` is final (all recursions done, gradient kernels
     still running) -- wait on it from a communication stream to overlap the loss all-reduce with the gradient pass.
@@ -106,6 +110,10 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
             if not (nan_count.is_cuda and nan_count.dtype == torch.int32 and nan_count.numel() == 1):
                 raise ValueError("nan_count must be a CUDA int32 tensor with one element")
             opts.nan_count = nan_count.data_ptr()
+        if loss_sum is not None:
+            if not (loss_sum.is_cuda and loss_sum.dtype == torch.float32 and loss_sum.numel() == 1):
+                raise ValueError("loss_sum must be a CUDA float32 tensor with one element")
+            opts.loss_sum = loss_sum.data_ptr()
         if costs_ready is not None:
             if not costs_ready.cuda_event:  # torch creates the CUDA event lazily, on its first record
                 costs_ready.record()
@@ -255,16 +263,20 @@ def last_launch_count() -> int:
 @torch.library.custom_op("ctc_b200::ctc_loss", mutates_args=(), device_types="cuda")
 def _ctc_loss_op(acts: torch.Tensor, labels: torch.Tensor, act_lens: torch.Tensor, label_lens: torch.Tensor,
                  blank: int, zero_infinity: bool, grad_scale: float, want_grads: bool,
-                 max_label_len: int, nan_to_zero: bool = False) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    # third output: int32 [1] count of NaN logits replaced (empty unless nan_to_zero)
+                 max_label_len: int, nan_to_zero: bool = False
+                 ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    # third output: int32 [1] count of NaN logits replaced (empty unless nan_to_zero); fourth: sum(costs), fp32 [1],
+    # produced by the library beside the gradient kernels
     nans = (torch.zeros(1, dtype=torch.int32, device=acts.device) if nan_to_zero
             else torch.empty(0, dtype=torch.int32, device=acts.device))
+    loss = torch.empty(1, dtype=torch.float32, device=acts.device)
     costs, grads = ctc_forward_backward(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale,
                                         want_grads, max_label_len if max_label_len >= 0 else None,
-                                        nan_to_zero=nan_to_zero, nan_count=nans if nan_to_zero else None)
+                                        nan_to_zero=nan_to_zero, nan_count=nans if nan_to_zero else None,
+                                        loss_sum=loss)
     if grads is None:
         grads = torch.empty(0, dtype=torch.float32, device=acts.device)
-    return costs, grads, nans
+    return costs, grads, nans, loss
 
 
 @_ctc_loss_op.register_fake
@@ -272,7 +284,7 @@ def _(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale, want
       nan_to_zero=False):
     costs = acts.new_empty((acts.shape[1],))
     grads = torch.empty_like(acts) if want_grads else acts.new_empty((0,))
-    return costs, grads, acts.new_empty((1 if nan_to_zero else 0,), dtype=torch.int32)
+    return costs, grads, acts.new_empty((1 if nan_to_zero else 0,), dtype=torch.int32), acts.new_empty((1,))
 
 
 class _CTCFunction(torch.autograd.Function):
@@ -282,12 +294,11 @@ class _CTCFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, acts, labels, act_lens, label_lens, blank, zero_infinity, scale, max_label_len, want,
                 nan_to_zero=False):
-        costs, grads, nans = _ctc_loss_op(acts, labels, act_lens, label_lens, blank, zero_infinity, scale, want,
-                                          -1 if max_label_len is None else int(max_label_len), nan_to_zero)
+        costs, grads, nans, loss = _ctc_loss_op(acts, labels, act_lens, label_lens, blank, zero_infinity, scale, want,
+                                                -1 if max_label_len is None else int(max_label_len), nan_to_zero)
         ctx.has_grads = want
         if want:
             ctx.save_for_backward(grads)
-        loss = costs.sum().reshape(1)
         loss = loss * scale if scale != 1.0 else loss
         if nan_to_zero:
             ctx.mark_non_differentiable(nans)

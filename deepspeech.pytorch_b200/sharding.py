@@ -64,17 +64,19 @@ def all_reduce_loss(loss_sum: torch.Tensor, mean_of_means: bool = False, local_b
 
 
 def overlapped_loss_all_reduce(costs: torch.Tensor, ready: "torch.cuda.Event", comm: "torch.cuda.Stream",
-                               out: torch.Tensor) -> None:
+                               out: torch.Tensor, local_sum: "torch.Tensor | None" = None) -> None:
     """The same collective, off the critical path: `ready` is the event handed to the CTC call as
     `costs_ready` (recorded when the per-utterance costs are final, while the gradient kernels still run).  The sum and
     the NCCL all-reduce run on `comm`; the current stream joins `comm` before returning, so work enqueued after this
-    call sees `out` (1-element fp32, global SUM of the costs)."""
+    call sees `out` (1-element fp32, global SUM of the costs).  With `local_sum` (the `loss_sum` tensor handed to the
+    same CTC call) no local reduction is launched at all."""
     import torch.distributed as dist
 
     cur = torch.cuda.current_stream(costs.device)
     with torch.cuda.stream(comm):
         comm.wait_event(ready)
-        s = costs.sum().reshape(1)
+        # local_sum: the library's own loss_sum output of the same call (already final when `ready` fires)
+        s = local_sum.reshape(1).clone() if local_sum is not None else costs.sum().reshape(1)
         if dist.is_available() and dist.is_initialized():
             dist.all_reduce(s)
         out.copy_(s)

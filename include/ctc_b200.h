@@ -75,6 +75,11 @@ typedef struct {
     int *nan_count;        /* DEVICE int32 or NULL; with nan_to_zero, the number of NaN logits found in valid frames
                               (t < act_lens[b]) is ADDED to it (the caller zeroes it; reading it back is what the
                               reference's `torch.isnan(logits).any()` warning needs) */
+    float *loss_sum;       /* DEVICE float or NULL; receives sum_b costs[b] -- the value the reference's criterion
+                              returns (train.py:600: one element, summed over the batch).  Summed in index order in
+                              fp64 by one small kernel that runs as soon as the recursions are done, beside the
+                              gradient kernels (the same point costs_ready marks), so the caller needs no reduction
+                              launch of its own after the call. */
 } ctcB200Options;
 
 /* replaces get_warpctc_version() */

@@ -510,3 +510,21 @@ def test_error_counts_of_the_fused_decode(b200):
     assert np.array_equal(counts.cpu().numpy(), np.array(want, np.int32))
     with pytest.raises(ValueError):
         b200.error_counts(best["ids"].cpu(), best["lens"], d["labels"].cuda(), d["label_lens"].cuda(), 29, 10)
+
+
+def test_loss_sum_output(oracle, b200):
+    # the criterion's one-element return value produced by the library (fixed order, fp64 accumulation), sliced and
+    # unsliced, small and large alphabet; the module's loss is that value
+    for name, B in (("headline_b64_t1500", 64), ("cpu_b16_t500", 5), ("bigc_b64_t1000_c5000", 8)):
+        d = _wl(b200, name, B=B)
+        acts = d["acts"].cuda()
+        loss = torch.full((1,), float("nan"), device="cuda")
+        costs, _ = b200.ctc_forward_backward(acts, d["labels"], d["act_lens"], d["label_lens"], loss_sum=loss)
+        torch.cuda.synchronize()
+        want = np.float32(costs.cpu().numpy().astype(np.float64).sum())
+        assert loss.item() == want
+        a = acts.clone().requires_grad_(True)
+        out = b200.CTCLoss()(a, d["labels"], d["act_lens"], d["label_lens"])
+        assert out.shape == (1,) and out.item() == want
+        out.backward()
+        assert a.grad is not None and torch.isfinite(a.grad).all()

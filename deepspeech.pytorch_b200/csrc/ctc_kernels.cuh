@@ -292,6 +292,7 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     // they are scheduled first and run under the softmax blocks instead of forming the tail of the launch.
     const int nextra = (int)gridDim.x - nrb;  // B utterance blocks (+1 sort block when the launch is sliced)
     if ((int)blockIdx.x < nextra) {
+        if (p.dbg_flags & 2) return;  // experiment: time the row blocks alone
         if ((int)blockIdx.x == p.B)
             sort_by_length(p, reinterpret_cast<int *>(smem));
         else

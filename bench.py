@@ -185,6 +185,26 @@ def run_b200(args, w):
 
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
     ready = torch.cuda.Event() if world > 1 else None
+    # N > 1: the path's one exchange, the all-reduce of the summed loss.  Default: fused into the library's
+    # cost-summing kernel over NVLink peer memory (sharding.PeerLossAllReduce, no collective launch);
+    # CTC_B200_ALLREDUCE=nccl selects one NCCL all-reduce on a communication stream, overlapped with the gradient pass.
+    peer = None
+    exchange = "none (1 GPU)"
+    if world > 1:
+        exchange = "nccl all-reduce on a side stream, overlapped with the gradient kernels"
+        if os.environ.get("CTC_B200_ALLREDUCE", "peer") != "nccl":
+            try:
+                peer = b200ctc.sharding.PeerLossAllReduce()
+                exchange = "fused into the cost-summing kernel over NVLink peer memory (no collective launch)"
+            except Exception as exc:  # no peer access on this box: say so and use NCCL
+                print(f"[bench] peer all-reduce unavailable ({exc}); using NCCL", file=sys.stderr)
+                peer = None
+        ok = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks take the same path
+        if int(ok.item()) == 0 and peer is not None:
+            peer.close()
+            peer = None
+            exchange = "nccl all-reduce on a side stream, overlapped with the gradient kernels"
 
     def step(phase_mask=0):
         if phase_mask or world == 1:
@@ -196,6 +216,10 @@ def run_b200(args, w):
         # N > 1: the path's one exchange -- the summed loss over NVLink (NCCL) -- starts on a communication stream
         # as soon as the costs are final (`costs_ready`: recursions done) and overlaps the gradient kernels; the
         # compute stream joins it at the end of the step, so the step still contains the whole exchange.
+        if peer is not None:
+            b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads, loss_sum=loss_acc,
+                                         comm=peer)
+            return
         costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
                                                 costs_ready=ready, loss_sum=loss_local)
         b200ctc.sharding.overlapped_loss_all_reduce(costs, ready, comm, loss_acc, local_sum=loss_local)
@@ -212,11 +236,23 @@ def run_b200(args, w):
         torch.cuda.synchronize()
         return [a.elapsed_time(b) for a, b in evs]
 
+    if world > 1:
+        dist.barrier()  # ranks start their first exchange together
     for _ in range(max(3, args.warmup)):
         flush.zero_()
         step()
     torch.cuda.synchronize()
     launches_per_step = b200ctc.last_launch_count()
+    if peer is not None:
+        # the fused exchange must give what NCCL gives on the same per-rank sums (fp32 rounding of the total apart)
+        costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
+                                                loss_sum=loss_local)
+        ref = loss_local.clone()
+        dist.all_reduce(ref)
+        step()
+        torch.cuda.synchronize()
+        if not abs(float(loss_acc.item()) - float(ref.item())) <= 1e-6 * abs(float(ref.item())):
+            raise RuntimeError(f"peer all-reduce {loss_acc.item()} != NCCL {ref.item()}")
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -306,7 +342,8 @@ def run_b200(args, w):
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": dict(workload_config(w, d), l2="flushed (256 MB memset) between timed steps",
                                lengths="device-resident (no host sync in the step)",
-                               launch="8 length-bucket slices on side streams (CTC_B200_SLICES)"),
+                               launch="8 length-bucket slices on side streams (CTC_B200_SLICES)",
+                               loss_exchange=exchange),
                 "roofline": {"bound": "hbm", "kernel": dom[0], "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "peak_kind": peak_kind, "traffic": load_traffic(dom[0], w.name),
                              "alg_bytes_per_launch": dom[1], "kernel_ms": dom[2],

@@ -21,7 +21,9 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 EXPORTS = ("ctc_b200_get_version", "ctc_b200_status_string", "ctc_b200_default_options", "ctc_b200_workspace_size",
            "ctc_b200_compute", "ctc_b200_create", "ctc_b200_destroy", "ctc_b200_compute_host",
-           "ctc_b200_compute_decode", "ctc_b200_greedy_decode", "ctc_b200_error_counts", "ctc_b200_last_launch_count")
+           "ctc_b200_compute_decode", "ctc_b200_greedy_decode", "ctc_b200_error_counts", "ctc_b200_last_launch_count",
+           "ctc_b200_comm_create", "ctc_b200_comm_handle", "ctc_b200_comm_local", "ctc_b200_comm_open",
+           "ctc_b200_comm_set_peers", "ctc_b200_comm_destroy")
 
 
 class CtcOptions(ctypes.Structure):
@@ -30,7 +32,7 @@ class CtcOptions(ctypes.Structure):
                 ("grad_scale", ctypes.c_float), ("lengths_on_device", ctypes.c_int),
                 ("max_label_len", ctypes.c_int), ("phase_mask", ctypes.c_int), ("nan_to_zero", ctypes.c_int),
                 ("costs_ready", ctypes.c_void_p), ("nan_count", ctypes.c_void_p),
-                ("loss_sum", ctypes.c_void_p)]
+                ("loss_sum", ctypes.c_void_p), ("comm", ctypes.c_void_p)]
 
 
 def _nvcc() -> str:
@@ -90,6 +92,18 @@ def load():
     lib.ctc_b200_compute_decode.restype = I
     lib.ctc_b200_error_counts.argtypes = [V, I, V, V, V, I, I, I, I, V, P(CtcOptions)]
     lib.ctc_b200_error_counts.restype = I
+    lib.ctc_b200_comm_create.argtypes = [P(V), I, I]
+    lib.ctc_b200_comm_create.restype = I
+    lib.ctc_b200_comm_handle.argtypes = [V, V]
+    lib.ctc_b200_comm_handle.restype = I
+    lib.ctc_b200_comm_local.argtypes = [V]
+    lib.ctc_b200_comm_local.restype = V
+    lib.ctc_b200_comm_open.argtypes = [V, V]
+    lib.ctc_b200_comm_open.restype = I
+    lib.ctc_b200_comm_set_peers.argtypes = [V, P(V)]
+    lib.ctc_b200_comm_set_peers.restype = I
+    lib.ctc_b200_comm_destroy.argtypes = [V]
+    lib.ctc_b200_comm_destroy.restype = I
     lib.ctc_b200_greedy_decode.argtypes = [V, ctypes.c_longlong, ctypes.c_longlong, V, I, I, I, V, V, V, V,
                                            P(CtcOptions)]
     lib.ctc_b200_greedy_decode.restype = I

@@ -22,11 +22,28 @@
 
 using namespace ctcb200;
 
+// Communicator of the fused loss all-reduce (see ctc_sum_costs_kernel): this rank's slot buffer + the peers' buffers
+// mapped through CUDA IPC (or given as raw pointers when all ranks live in one process).
+struct ctcB200Comm {
+    int rank = 0, world = 1;
+    unsigned long long *local = nullptr;       // cudaMalloc: [2][kCommMaxWorld] slots + counter
+    unsigned long long **peers_dev = nullptr;  // device array [world]
+    void *opened[kCommMaxWorld] = {};
+    bool ready = false;
+};
+
 namespace {
 
 constexpr int kK = 8;               // states per lattice thread
 constexpr size_t kSmemLimit = 227 * 1024;
 thread_local int g_last_launches = 0;
+
+// where the summed loss goes, and (multi-GPU) the communicator its kernel all-reduces through
+struct LossOut {
+    float *loss_sum = nullptr;
+    CommArgs comm = {nullptr, nullptr, 0, 1};
+    explicit operator bool() const { return loss_sum != nullptr; }
+};
 
 // ---- length-bucket slices (see sort_by_length in ctc_kernels.cuh)
 constexpr int kMaxSlices = 16;     // upper bound (CTC_B200_SLICES)
@@ -181,11 +198,11 @@ inline void launch_collapse(const CtcParams &p, cudaStream_t s, int *launches) {
 
 template <typename EngineLaunch, typename GradLaunch>
 cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, bool do_engine, bool do_grad,
-                          int *launches, cudaEvent_t costs_ready, float *loss_sum, EngineLaunch eng, GradLaunch grd) {
+                          int *launches, cudaEvent_t costs_ready, const LossOut &loss_sum, EngineLaunch eng, GradLaunch grd) {
     if (pl.nslices <= 1 || (!do_engine && !do_grad)) {
         if (do_engine) eng(p, p.B, st);
         if (loss_sum && do_engine) {
-            ctc_sum_costs_kernel<<<1, 32, 0, st>>>(p.costs, p.B, loss_sum);
+            ctc_sum_costs_kernel<<<1, 32, 0, st>>>(p.costs, p.B, loss_sum.loss_sum, loss_sum.comm);
             ++*launches;
         }
         if (costs_ready && cudaEventRecord(costs_ready, st) != cudaSuccess) return cudaErrorUnknown;
@@ -231,7 +248,7 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
                     if ((e = cudaStreamWaitEvent(sp->aux, sp->eng_done[k], 0)) != cudaSuccess) return e;
                 }
                 if (loss_sum) {
-                    ctc_sum_costs_kernel<<<1, 32, 0, sp->aux>>>(p.costs, p.B, loss_sum);
+                    ctc_sum_costs_kernel<<<1, 32, 0, sp->aux>>>(p.costs, p.B, loss_sum.loss_sum, loss_sum.comm);
                     ++*launches;
                 }
                 if (costs_ready && (e = cudaEventRecord(costs_ready, sp->aux)) != cudaSuccess) return e;
@@ -266,7 +283,7 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
 
 template <int CP>
 cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
-                          cudaEvent_t costs_ready, float *loss_sum) {
+                          cudaEvent_t costs_ready, const LossOut &loss_sum) {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -315,7 +332,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
 // row kernel drains, or (with priorities) they take the slots and the rows slow down by more than the recursion hides;
 // the gradient kernel's scattered reductions also disturb the streaming.
 cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
-                       cudaEvent_t costs_ready, float *loss_sum) {
+                       cudaEvent_t costs_ready, const LossOut &loss_sum) {
     constexpr int CP = 256;
     static bool attr_set[64] = {false};
     int dev = 0;
@@ -389,7 +406,7 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
 }
 
 cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
-                       cudaEvent_t costs_ready, float *loss_sum) {
+                       cudaEvent_t costs_ready, const LossOut &loss_sum) {
     if (pl.big) return launch_big(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
     switch (pl.Cp) {
         case 32: return launch_all_cp<32>(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
@@ -544,7 +561,14 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.nan_count = o.nan_to_zero ? o.nan_count : nullptr;
 
     int launches = 0;
-    cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches, (cudaEvent_t)o.costs_ready, o.loss_sum);
+    LossOut lo;
+    lo.loss_sum = o.loss_sum;
+    if (o.comm) {
+        const ctcB200Comm *cm = static_cast<const ctcB200Comm *>(o.comm);
+        if (!o.loss_sum || !cm->ready) return CTC_B200_STATUS_INVALID_VALUE;
+        lo.comm = CommArgs{cm->local, cm->peers_dev, cm->rank, cm->world};
+    }
+    cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches, (cudaEvent_t)o.costs_ready, lo);
     g_last_launches = launches;
     return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }
@@ -583,6 +607,83 @@ extern "C" ctcB200Status ctc_b200_greedy_decode(const float *acts, long long str
     ctc_collapse_kernel<<<B, kCollapseThreads, 0, st>>>(path, act_lens_dev, T, B, o.blank, ids, offsets, out_lens);
     ++g_last_launches;
     return cudaGetLastError() == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
+}
+
+// ------------------------------------------------------------------------------------------------ loss all-reduce
+constexpr size_t kCommBytes = sizeof(unsigned long long) * 2 * kCommMaxWorld + 64;
+
+extern "C" ctcB200Status ctc_b200_comm_create(ctcB200Comm **out, int rank, int world) {
+    if (!out || world < 1 || world > kCommMaxWorld || rank < 0 || rank >= world) return CTC_B200_STATUS_INVALID_VALUE;
+    ctcB200Comm *c = new (std::nothrow) ctcB200Comm();
+    if (!c) return CTC_B200_STATUS_MEMOPS_FAILED;
+    c->rank = rank;
+    c->world = world;
+    if (cudaMalloc((void **)&c->local, kCommBytes) != cudaSuccess ||
+        cudaMemset(c->local, 0, kCommBytes) != cudaSuccess ||
+        cudaMalloc((void **)&c->peers_dev, sizeof(void *) * kCommMaxWorld) != cudaSuccess ||
+        cudaDeviceSynchronize() != cudaSuccess) {
+        cudaFree(c->local);
+        cudaFree(c->peers_dev);
+        delete c;
+        return CTC_B200_STATUS_MEMOPS_FAILED;
+    }
+    *out = c;
+    return CTC_B200_STATUS_SUCCESS;
+}
+
+extern "C" ctcB200Status ctc_b200_comm_handle(ctcB200Comm *c, void *handle64) {
+    if (!c || !handle64) return CTC_B200_STATUS_INVALID_VALUE;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "the ABI hands the IPC handle around as 64 opaque bytes");
+    cudaIpcMemHandle_t h;
+    if (cudaIpcGetMemHandle(&h, c->local) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+    memcpy(handle64, &h, 64);
+    return CTC_B200_STATUS_SUCCESS;
+}
+
+extern "C" void *ctc_b200_comm_local(ctcB200Comm *c) { return c ? (void *)c->local : nullptr; }
+
+static ctcB200Status comm_finish(ctcB200Comm *c, unsigned long long **ptrs) {
+    ptrs[c->rank] = c->local;
+    if (cudaMemcpy(c->peers_dev, ptrs, sizeof(void *) * c->world, cudaMemcpyHostToDevice) != cudaSuccess)
+        return CTC_B200_STATUS_MEMOPS_FAILED;
+    c->ready = true;
+    return CTC_B200_STATUS_SUCCESS;
+}
+
+// handles: world x 64 bytes, the ctc_b200_comm_handle of every rank in rank order (this rank's own entry is ignored)
+extern "C" ctcB200Status ctc_b200_comm_open(ctcB200Comm *c, const void *handles) {
+    if (!c || !handles || c->ready) return CTC_B200_STATUS_INVALID_VALUE;
+    unsigned long long *ptrs[kCommMaxWorld] = {};
+    for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const char *>(handles) + 64 * (size_t)r, 64);
+        if (cudaIpcOpenMemHandle(&c->opened[r], h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            cudaGetLastError();
+            return CTC_B200_STATUS_EXECUTION_FAILED;
+        }
+        ptrs[r] = static_cast<unsigned long long *>(c->opened[r]);
+    }
+    return comm_finish(c, ptrs);
+}
+
+// all ranks in ONE process (one device, or devices with peer access enabled by the caller): raw slot-buffer pointers
+// (ctc_b200_comm_local of every rank, rank order)
+extern "C" ctcB200Status ctc_b200_comm_set_peers(ctcB200Comm *c, void *const *locals) {
+    if (!c || !locals || c->ready) return CTC_B200_STATUS_INVALID_VALUE;
+    unsigned long long *ptrs[kCommMaxWorld] = {};
+    for (int r = 0; r < c->world; ++r) ptrs[r] = static_cast<unsigned long long *>(locals[r]);
+    return comm_finish(c, ptrs);
+}
+
+extern "C" ctcB200Status ctc_b200_comm_destroy(ctcB200Comm *c) {
+    if (!c) return CTC_B200_STATUS_SUCCESS;
+    for (int r = 0; r < kCommMaxWorld; ++r)
+        if (c->opened[r]) cudaIpcCloseMemHandle(c->opened[r]);
+    cudaFree(c->local);
+    cudaFree(c->peers_dev);
+    delete c;
+    return CTC_B200_STATUS_SUCCESS;
 }
 
 // ------------------------------------------------------------------------------------------------ WER / CER counts
@@ -815,6 +916,7 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         ok.lengths_on_device = 1;
         ok.costs_ready = nullptr;  // meaningless here: the call synchronises before it returns
         ok.loss_sum = nullptr;     // the host entry sums the downloaded costs itself
+        ok.comm = nullptr;
         ok.max_label_len = mxs[k] > 0 ? mxs[k] : 1;
         ctcB200Status s = compute_impl(da, dg, d_labels + lab_off[k], d_llen + b0, d_alen + b0, Tk, nb, C,
                                        c->d_costs + b0, static_cast<unsigned char *>(c->d_ws) + ws_off[k],

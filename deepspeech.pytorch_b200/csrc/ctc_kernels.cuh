@@ -1391,16 +1391,64 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
 // ================================================================================================ summed loss
 // loss = sum_b costs[b], the one-element value the criterion returns (train.py:600).  One warp, fixed order, fp64
 // accumulation: deterministic and independent of how the batch was sliced.  Runs beside the gradient kernels.
-__global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, int B, float *loss_sum) {
+//
+// Multi-GPU (replaces reduce_tensor, /root/reference/data/utils.py:40-44): with a communicator the SAME kernel also
+// performs the path's one exchange, the all-reduce of the summed loss, over NVLink peer memory -- no collective
+// launch follows.  One-shot protocol: every rank owns 2 x kCommMaxWorld slots of 8 bytes; call number e (a counter in
+// the rank's own buffer, so CUDA-graph replays advance it too) stores (e << 32 | float bits of the local sum) with ONE
+// 64-bit store into slot [e & 1][rank] of every peer, then polls its own slots [e & 1][0 .. world) until all carry
+// epoch e and adds the values in rank order (every rank gets the same bits).  Value and epoch travel in one word,
+// so no fence orders them; the two parities make reuse safe (a rank cannot enter call e+2 before every peer has
+// entered call e+1, i.e. finished reading call e).  A peer that never arrives turns the result into NaN after
+// ~10 s instead of hanging the device.
+constexpr int kCommMaxWorld = 32;
+struct CommArgs {
+    unsigned long long *local;          // this rank's slots [2][kCommMaxWorld], then the call counter
+    unsigned long long *const *peers;   // device array [world]: slot base of every rank (peers[rank] == local)
+    int rank, world;
+};
+
+__global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, int B, float *loss_sum, CommArgs ca) {
+    const int lane = threadIdx.x;
     double acc = 0.0;
     for (int base = 0; base < B; base += 32) {
-        const int i = base + (int)threadIdx.x;
+        const int i = base + lane;
         double v = i < B ? (double)costs[i] : 0.0;
 #pragma unroll
         for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(kFull, v, d);
         acc += v;
     }
-    if (threadIdx.x == 0) *loss_sum = (float)acc;
+    if (ca.world <= 1) {
+        if (lane == 0) *loss_sum = (float)acc;
+        return;
+    }
+    unsigned *ctr = reinterpret_cast<unsigned *>(ca.local + 2 * kCommMaxWorld);
+    unsigned e = 0;
+    if (lane == 0) {
+        e = *ctr + 1;
+        *ctr = e;
+    }
+    e = __shfl_sync(kFull, e, 0);
+    const int par = (int)(e & 1u) * kCommMaxWorld;
+    const unsigned long long word = ((unsigned long long)e << 32) | (unsigned long long)__float_as_uint((float)acc);
+    if (lane < ca.world) {
+        volatile unsigned long long *dst = ca.peers[lane] + par + ca.rank;
+        *dst = word;
+    }
+    __threadfence_system();
+    float mine = 0.f;
+    bool ok = true;
+    if (lane < ca.world) {
+        volatile unsigned long long *src = ca.local + par + lane;
+        unsigned long long w = *src;
+        for (long long spins = 0; (unsigned)(w >> 32) != e && spins < 30000000ll; ++spins) w = *src;
+        ok = (unsigned)(w >> 32) == e;
+        mine = __uint_as_float((unsigned)w);
+    }
+    ok = __all_sync(kFull, ok);
+    double tot = 0.0;
+    for (int j = 0; j < ca.world; ++j) tot += (double)__shfl_sync(kFull, mine, j);
+    if (lane == 0) *loss_sum = ok ? (float)tot : __int_as_float(0x7fc00000);
 }
 
 // ================================================================================================ greedy decoding

@@ -52,7 +52,8 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
                          max_label_len: Optional[int] = None, phase_mask: int = 0,
                          out_grads: Optional[torch.Tensor] = None, decode: bool = False,
                          costs_ready: Optional[torch.cuda.Event] = None, nan_to_zero: bool = False,
-                         nan_count: Optional[torch.Tensor] = None, loss_sum: Optional[torch.Tensor] = None):
+                         nan_count: Optional[torch.Tensor] = None, loss_sum: Optional[torch.Tensor] = None,
+                         comm=None):
     """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
 
     nan_to_zero: NaN logits are read as 0 (the guard at train.py:595-598 of the reference, folded into the softmax
@@ -62,6 +63,9 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
     loss_sum: optional CUDA float32 tensor of one element; receives sum(costs) -- the criterion's return value --
     from a one-warp kernel that runs beside the gradient kernels (fixed order, fp64 accumulation), so no reduction
     has to be launched after the call.
+
+    comm: a `sharding.PeerLossAllReduce` (multi-GPU, one process per GPU): `loss_sum` then receives the sum over ALL
+    ranks -- the summing kernel exchanges the per-rank sums over NVLink peer memory, no collective is launched.
 
     costs_ready: an event the library records as soon as `costs` is final (all recursions done, gradient kernels
     still running) -- wait on it from a communication stream to overlap the loss all-reduce with the gradient pass.
@@ -114,6 +118,10 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
             if not (loss_sum.is_cuda and loss_sum.dtype == torch.float32 and loss_sum.numel() == 1):
                 raise ValueError("loss_sum must be a CUDA float32 tensor with one element")
             opts.loss_sum = loss_sum.data_ptr()
+        if comm is not None:
+            if loss_sum is None:
+                raise ValueError("comm needs loss_sum (the tensor that receives the all-reduced loss)")
+            opts.comm = comm.handle
         if costs_ready is not None:
             if not costs_ready.cuda_event:  # torch creates the CUDA event lazily, on its first record
                 costs_ready.record()

@@ -82,3 +82,65 @@ def overlapped_loss_all_reduce(costs: torch.Tensor, ready: "torch.cuda.Event", c
         out.copy_(s)
     costs.record_stream(comm)
     cur.wait_stream(comm)
+
+
+class PeerLossAllReduce:
+    """Communicator of the fused loss all-reduce (include/ctc_b200.h: ctc_b200_comm_*): the kernel that sums the
+    per-utterance costs also exchanges the per-rank sums over NVLink peer memory, so the path's one collective
+    (reduce_tensor, data/utils.py:40-44) costs no launch of its own.  One process per GPU; the CUDA IPC handles of the
+    ranks' slot buffers are exchanged once through torch.distributed (any backend).
+
+        comm = PeerLossAllReduce()                                  # after init_process_group, device set
+        ctc_forward_backward(..., loss_sum=loss, comm=comm)         # loss: sum over all ranks, same bits everywhere
+
+    `PeerLossAllReduce.local_group(n)` builds n communicators inside ONE process (one device) for tests."""
+
+    def __init__(self, rank: int | None = None, world: int | None = None, _exchange: bool = True):
+        import ctypes
+
+        import torch.distributed as dist
+
+        from . import _lib
+
+        self._lib = _lib.load()
+        if rank is None or world is None:
+            if not (dist.is_available() and dist.is_initialized()):
+                raise RuntimeError("PeerLossAllReduce needs an initialised torch.distributed process group")
+            rank, world = dist.get_rank(), dist.get_world_size()
+        self.rank, self.world = int(rank), int(world)
+        h = ctypes.c_void_p()
+        _lib.check(self._lib.ctc_b200_comm_create(ctypes.byref(h), self.rank, self.world), "ctc_b200_comm_create")
+        self.handle = h.value
+        if not _exchange:
+            return
+        buf = ctypes.create_string_buffer(64)
+        _lib.check(self._lib.ctc_b200_comm_handle(self.handle, buf), "ctc_b200_comm_handle")
+        gathered: list = [None] * self.world
+        dist.all_gather_object(gathered, bytes(buf.raw))
+        blob = ctypes.create_string_buffer(b"".join(gathered), 64 * self.world)
+        _lib.check(self._lib.ctc_b200_comm_open(self.handle, blob), "ctc_b200_comm_open")
+        dist.barrier()  # every rank has mapped every buffer before anyone's first call stores into them
+
+    @classmethod
+    def local_group(cls, n: int):
+        import ctypes
+
+        from . import _lib
+
+        comms = [cls(r, n, _exchange=False) for r in range(n)]
+        lib = _lib.load()
+        locals_ = (ctypes.c_void_p * n)(*[lib.ctc_b200_comm_local(c.handle) for c in comms])
+        for c in comms:
+            _lib.check(lib.ctc_b200_comm_set_peers(c.handle, locals_), "ctc_b200_comm_set_peers")
+        return comms
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self._lib.ctc_b200_comm_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

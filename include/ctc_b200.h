@@ -80,6 +80,10 @@ typedef struct {
                               fp64 by one small kernel that runs as soon as the recursions are done, beside the
                               gradient kernels (the same point costs_ready marks), so the caller needs no reduction
                               launch of its own after the call. */
+    void *comm;            /* ctcB200Comm* or NULL.  With a communicator (multi-GPU, one process per GPU) loss_sum
+                              receives the sum over ALL ranks: the same one-warp kernel exchanges the per-rank sums
+                              over NVLink peer memory (see ctc_b200_comm_create).  Requires loss_sum; every rank of
+                              the communicator must make the same sequence of calls. */
 } ctcB200Options;
 
 /* replaces get_warpctc_version() */
@@ -149,6 +153,27 @@ ctcB200Status ctc_b200_compute_decode(const float *acts, float *grads, const int
 ctcB200Status ctc_b200_greedy_decode(const float *acts, long long stride_t, long long stride_b,
                                      const int *act_lens_dev, int T, int B, int C, int *path, int *ids, int *offsets,
                                      int *out_lens, const ctcB200Options *opts);
+
+/*
+ * The path's one exchange step, the all-reduce of the summed loss -- replaces reduce_tensor
+ * (/root/reference/data/utils.py:40-44: dist.all_reduce of the loss, gloo by default, train.py:99,356,461,606).
+ * Fused into the kernel that sums the costs: every rank stores its partial sum straight into every peer's slot buffer
+ * over NVLink (CUDA IPC peer mappings), polls its own buffer until all partials of this call have arrived and adds
+ * them in rank order, so every rank obtains the same bits and no collective kernel is launched.  Set-up (once):
+ *   ctc_b200_comm_create(&c, rank, world)        on every rank, its CUDA device current (world <= 32)
+ *   ctc_b200_comm_handle(c, handle64)            64 opaque bytes (a cudaIpcMemHandle_t); exchange them by any means
+ *                                                (the Python side uses torch.distributed.all_gather_object)
+ *   ctc_b200_comm_open(c, handles)               handles = world x 64 bytes in rank order
+ * then pass `comm` + `loss_sum` in the options of ctc_b200_compute.  ctc_b200_comm_set_peers is the same for ranks
+ * that share one process (raw ctc_b200_comm_local pointers instead of IPC handles).
+ */
+typedef struct ctcB200Comm ctcB200Comm;
+ctcB200Status ctc_b200_comm_create(ctcB200Comm **comm, int rank, int world);
+ctcB200Status ctc_b200_comm_handle(ctcB200Comm *comm, void *handle64);
+void *ctc_b200_comm_local(ctcB200Comm *comm);
+ctcB200Status ctc_b200_comm_open(ctcB200Comm *comm, const void *handles);
+ctcB200Status ctc_b200_comm_set_peers(ctcB200Comm *comm, void *const *locals);
+ctcB200Status ctc_b200_comm_destroy(ctcB200Comm *comm);
 
 /*
  * Word / character error counts of decoded transcripts against the targets -- SURVEY.md 8(f) rank 4.  Replaces, per

@@ -137,6 +137,8 @@ def test_large_alphabet_row_kernels(oracle, b200, C):
     for b in range(B):
         assert np.all(grads[int(act_lens[b]):, b, :] == 0.0)
     _check(oracle, b200, d, device_lens=True, grad_scale=0.125)
+    c_eval, _ = _run(b200, d, want_grads=False)  # eval call sites (train.py:352,457): no gradient buffer at all
+    assert np.array_equal(c_eval, costs)
     # a view whose rows are 16-byte aligned but whose base is not: falls back to the generic kernel (scalar loads, another summation order)
     if C % 4 == 0:
         pad = torch.zeros(T * B * C + 1, device="cuda")
@@ -528,3 +530,29 @@ def test_loss_sum_output(oracle, b200):
         assert out.shape == (1,) and out.item() == want
         out.backward()
         assert a.grad is not None and torch.isfinite(a.grad).all()
+
+
+def test_fused_loss_all_reduce_two_ranks_one_device(b200):
+    # the path's one exchange (reduce_tensor, data/utils.py:40-44) fused into the cost-summing kernel: two logical
+    # ranks in this process, each with its own shard, stream and communicator; both must obtain the same global sum
+    # (their kernels poll each other's stores, so they have to run concurrently), call after call
+    d = _wl(b200, "cpu_b16_t500", seed=11, B=24)
+    shards = b200.sharding.length_bucketed_shards(d["act_lens"].tolist(), d["label_lens"].tolist(), 2)
+    comms = b200.sharding.PeerLossAllReduce.local_group(2)
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    parts = [b200.sharding.take_shard(d["acts"], d["labels"], d["act_lens"], d["label_lens"], ids) for ids in shards]
+    outs = [torch.zeros(1, device="cuda") for _ in range(2)]
+    for it in range(3):
+        costs = []
+        for r in range(2):
+            a, l, al, ll = parts[r]
+            with torch.cuda.stream(streams[r]):
+                c, _ = b200.ctc_forward_backward(a.cuda() * (1.0 + 0.1 * it), l, al, ll, loss_sum=outs[r],
+                                                 comm=comms[r])
+                costs.append(c)
+        torch.cuda.synchronize()
+        local = [np.float32(c.cpu().numpy().astype(np.float64).sum()) for c in costs]
+        want = np.float32(np.float64(local[0]) + np.float64(local[1]))
+        assert outs[0].item() == outs[1].item() == want, (it, outs[0].item(), outs[1].item(), want)
+    for c in comms:
+        c.close()

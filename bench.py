@@ -199,14 +199,9 @@ def run_b200(args, w):
             except Exception as exc:  # no peer access on this box: say so and use NCCL
                 print(f"[bench] peer all-reduce unavailable ({exc}); using NCCL", file=sys.stderr)
                 peer = None
-        ok = torch.tensor([1 if peer is not None else 0], device=dev)
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks take the same path
-        if int(ok.item()) == 0 and peer is not None:
-            peer.close()
-            peer = None
-            exchange = "nccl all-reduce on a side stream, overlapped with the gradient kernels"
 
     def step(phase_mask=0):
+        nonlocal_peer = peer
         if phase_mask or world == 1:
             # the summed loss (the criterion's return value) is written to loss_acc by the library itself, by a
             # one-warp kernel that runs beside the gradient kernels
@@ -216,9 +211,9 @@ def run_b200(args, w):
         # N > 1: the path's one exchange -- the summed loss over NVLink (NCCL) -- starts on a communication stream
         # as soon as the costs are final (`costs_ready`: recursions done) and overlaps the gradient kernels; the
         # compute stream joins it at the end of the step, so the step still contains the whole exchange.
-        if peer is not None:
+        if nonlocal_peer is not None:
             b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads, loss_sum=loss_acc,
-                                         comm=peer)
+                                         comm=nonlocal_peer)
             return
         costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
                                                 costs_ready=ready, loss_sum=loss_local)
@@ -251,8 +246,19 @@ def run_b200(args, w):
         dist.all_reduce(ref)
         step()
         torch.cuda.synchronize()
-        if not abs(float(loss_acc.item()) - float(ref.item())) <= 1e-6 * abs(float(ref.item())):
-            raise RuntimeError(f"peer all-reduce {loss_acc.item()} != NCCL {ref.item()}")
+        good = abs(float(loss_acc.item()) - float(ref.item())) <= 1e-6 * abs(float(ref.item()))
+        ok = torch.tensor([1 if good else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:  # never time a wrong exchange: fall back to NCCL on every rank and say so
+            print(f"[bench] rank {rank}: peer all-reduce {loss_acc.item()} != NCCL {ref.item()}; using NCCL",
+                  file=sys.stderr)
+            peer = None
+            exchange = "nccl all-reduce on a side stream (the fused peer exchange failed its check on this box)"
+            for _ in range(3):
+                flush.zero_()
+                step()
+            torch.cuda.synchronize()
+            launches_per_step = b200ctc.last_launch_count()
 
     sampler = ClockSampler(local_rank)
     if rank == 0:

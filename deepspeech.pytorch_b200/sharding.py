@@ -118,8 +118,15 @@ class PeerLossAllReduce:
         gathered: list = [None] * self.world
         dist.all_gather_object(gathered, bytes(buf.raw))
         blob = ctypes.create_string_buffer(b"".join(gathered), 64 * self.world)
-        _lib.check(self._lib.ctc_b200_comm_open(self.handle, blob), "ctc_b200_comm_open")
-        dist.barrier()  # every rank has mapped every buffer before anyone's first call stores into them
+        st = self._lib.ctc_b200_comm_open(self.handle, blob)
+        # one collective doubles as the barrier (every rank has mapped every buffer before anyone's first call stores
+        # into them) and as the agreement that the mapping worked everywhere
+        ok = torch.tensor([1 if st == 0 else 0], dtype=torch.int32,
+                          device="cuda" if dist.get_backend() == "nccl" else "cpu")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            self.close()
+            raise RuntimeError("CUDA IPC peer mapping of the loss all-reduce buffers failed on at least one rank")
 
     @classmethod
     def local_group(cls, n: int):

@@ -212,8 +212,8 @@ def run_b200(args, w):
         # as soon as the costs are final (`costs_ready`: recursions done) and overlaps the gradient kernels; the
         # compute stream joins it at the end of the step, so the step still contains the whole exchange.
         if nonlocal_peer is not None:
-            b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads, loss_sum=loss_acc,
-                                         comm=nonlocal_peer)
+            b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads, loss_sum=loss_local,
+                                         loss_sum_all=loss_acc, comm=nonlocal_peer)
             return
         costs, _ = b200ctc.ctc_forward_backward(acts, lab, al, ll, max_label_len=lmax, out_grads=grads,
                                                 costs_ready=ready, loss_sum=loss_local)

@@ -32,7 +32,8 @@ class CtcOptions(ctypes.Structure):
                 ("grad_scale", ctypes.c_float), ("lengths_on_device", ctypes.c_int),
                 ("max_label_len", ctypes.c_int), ("phase_mask", ctypes.c_int), ("nan_to_zero", ctypes.c_int),
                 ("costs_ready", ctypes.c_void_p), ("nan_count", ctypes.c_void_p),
-                ("loss_sum", ctypes.c_void_p), ("comm", ctypes.c_void_p)]
+                ("loss_sum", ctypes.c_void_p), ("comm", ctypes.c_void_p),
+                ("loss_sum_all", ctypes.c_void_p)]
 
 
 def _nvcc() -> str:

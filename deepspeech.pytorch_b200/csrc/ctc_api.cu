@@ -40,9 +40,10 @@ thread_local int g_last_launches = 0;
 
 // where the summed loss goes, and (multi-GPU) the communicator its kernel all-reduces through
 struct LossOut {
-    float *loss_sum = nullptr;
+    float *loss_sum = nullptr;  // this rank's sum
+    float *loss_all = nullptr;  // sum over all ranks of the communicator
     CommArgs comm = {nullptr, nullptr, 0, 1};
-    explicit operator bool() const { return loss_sum != nullptr; }
+    explicit operator bool() const { return loss_sum != nullptr || loss_all != nullptr; }
 };
 
 // ---- length-bucket slices (see sort_by_length in ctc_kernels.cuh)
@@ -202,7 +203,7 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
     if (pl.nslices <= 1 || (!do_engine && !do_grad)) {
         if (do_engine) eng(p, p.B, st);
         if (loss_sum && do_engine) {
-            ctc_sum_costs_kernel<<<1, 32, 0, st>>>(p.costs, p.B, loss_sum.loss_sum, loss_sum.comm);
+            ctc_sum_costs_kernel<<<1, 32, 0, st>>>(p.costs, p.B, loss_sum.loss_sum, loss_sum.loss_all, loss_sum.comm);
             ++*launches;
         }
         if (costs_ready && cudaEventRecord(costs_ready, st) != cudaSuccess) return cudaErrorUnknown;
@@ -248,7 +249,7 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
                     if ((e = cudaStreamWaitEvent(sp->aux, sp->eng_done[k], 0)) != cudaSuccess) return e;
                 }
                 if (loss_sum) {
-                    ctc_sum_costs_kernel<<<1, 32, 0, sp->aux>>>(p.costs, p.B, loss_sum.loss_sum, loss_sum.comm);
+                    ctc_sum_costs_kernel<<<1, 32, 0, sp->aux>>>(p.costs, p.B, loss_sum.loss_sum, loss_sum.loss_all, loss_sum.comm);
                     ++*launches;
                 }
                 if (costs_ready && (e = cudaEventRecord(costs_ready, sp->aux)) != cudaSuccess) return e;
@@ -563,9 +564,10 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     int launches = 0;
     LossOut lo;
     lo.loss_sum = o.loss_sum;
+    lo.loss_all = o.loss_sum_all;
     if (o.comm) {
         const ctcB200Comm *cm = static_cast<const ctcB200Comm *>(o.comm);
-        if (!o.loss_sum || !cm->ready) return CTC_B200_STATUS_INVALID_VALUE;
+        if (!o.loss_sum_all || !cm->ready) return CTC_B200_STATUS_INVALID_VALUE;
         lo.comm = CommArgs{cm->local, cm->peers_dev, cm->rank, cm->world};
     }
     cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches, (cudaEvent_t)o.costs_ready, lo);
@@ -917,6 +919,7 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         ok.costs_ready = nullptr;  // meaningless here: the call synchronises before it returns
         ok.loss_sum = nullptr;     // the host entry sums the downloaded costs itself
         ok.comm = nullptr;
+        ok.loss_sum_all = nullptr;
         ok.max_label_len = mxs[k] > 0 ? mxs[k] : 1;
         ctcB200Status s = compute_impl(da, dg, d_labels + lab_off[k], d_llen + b0, d_alen + b0, Tk, nb, C,
                                        c->d_costs + b0, static_cast<unsigned char *>(c->d_ws) + ws_off[k],

@@ -1408,7 +1408,8 @@ struct CommArgs {
     int rank, world;
 };
 
-__global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, int B, float *loss_sum, CommArgs ca) {
+__global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, int B, float *loss_sum,
+                                                           float *loss_all, CommArgs ca) {
     const int lane = threadIdx.x;
     double acc = 0.0;
     for (int base = 0; base < B; base += 32) {
@@ -1418,8 +1419,10 @@ __global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, i
         for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(kFull, v, d);
         acc += v;
     }
+    if (lane == 0 && loss_sum) *loss_sum = (float)acc;  // this rank's own sum
+    if (!loss_all) return;
     if (ca.world <= 1) {
-        if (lane == 0) *loss_sum = (float)acc;
+        if (lane == 0) *loss_all = (float)acc;
         return;
     }
     unsigned *ctr = reinterpret_cast<unsigned *>(ca.local + 2 * kCommMaxWorld);
@@ -1448,7 +1451,7 @@ __global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, i
     ok = __all_sync(kFull, ok);
     double tot = 0.0;
     for (int j = 0; j < ca.world; ++j) tot += (double)__shfl_sync(kFull, mine, j);
-    if (lane == 0) *loss_sum = ok ? (float)tot : __int_as_float(0x7fc00000);
+    if (lane == 0) *loss_all = ok ? (float)tot : __int_as_float(0x7fc00000);
 }
 
 // ================================================================================================ greedy decoding

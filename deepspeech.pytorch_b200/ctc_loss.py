@@ -53,7 +53,7 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
                          out_grads: Optional[torch.Tensor] = None, decode: bool = False,
                          costs_ready: Optional[torch.cuda.Event] = None, nan_to_zero: bool = False,
                          nan_count: Optional[torch.Tensor] = None, loss_sum: Optional[torch.Tensor] = None,
-                         comm=None):
+                         comm=None, loss_sum_all: Optional[torch.Tensor] = None):
     """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
 
     nan_to_zero: NaN logits are read as 0 (the guard at train.py:595-598 of the reference, folded into the softmax
@@ -64,8 +64,9 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
     from a one-warp kernel that runs beside the gradient kernels (fixed order, fp64 accumulation), so no reduction
     has to be launched after the call.
 
-    comm: a `sharding.PeerLossAllReduce` (multi-GPU, one process per GPU): `loss_sum` then receives the sum over ALL
-    ranks -- the summing kernel exchanges the per-rank sums over NVLink peer memory, no collective is launched.
+    comm + loss_sum_all: a `sharding.PeerLossAllReduce` (multi-GPU, one process per GPU) and a CUDA float32 tensor of
+    one element that receives the sum of the loss over ALL ranks -- the summing kernel exchanges the per-rank sums
+    over NVLink peer memory, no collective is launched (replaces reduce_tensor, data/utils.py:40-44).
 
     costs_ready: an event the library records as soon as `costs` is final (all recursions done, gradient kernels
     still running) -- wait on it from a communication stream to overlap the loss all-reduce with the gradient pass.
@@ -118,9 +119,13 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
             if not (loss_sum.is_cuda and loss_sum.dtype == torch.float32 and loss_sum.numel() == 1):
                 raise ValueError("loss_sum must be a CUDA float32 tensor with one element")
             opts.loss_sum = loss_sum.data_ptr()
+        if loss_sum_all is not None:
+            if not (loss_sum_all.is_cuda and loss_sum_all.dtype == torch.float32 and loss_sum_all.numel() == 1):
+                raise ValueError("loss_sum_all must be a CUDA float32 tensor with one element")
+            opts.loss_sum_all = loss_sum_all.data_ptr()
         if comm is not None:
-            if loss_sum is None:
-                raise ValueError("comm needs loss_sum (the tensor that receives the all-reduced loss)")
+            if loss_sum_all is None:
+                raise ValueError("comm needs loss_sum_all (the tensor that receives the all-reduced loss)")
             opts.comm = comm.handle
         if costs_ready is not None:
             if not costs_ready.cuda_event:  # torch creates the CUDA event lazily, on its first record
@@ -268,31 +273,42 @@ def last_launch_count() -> int:
 
 
 # ---------------------------------------------------------------------------------------------- torch custom op
+class _CommRef:
+    """carries a communicator handle through the custom op (whose schema only takes plain types)"""
+
+    def __init__(self, handle: int):
+        self.handle = handle
+
+
 @torch.library.custom_op("ctc_b200::ctc_loss", mutates_args=(), device_types="cuda")
 def _ctc_loss_op(acts: torch.Tensor, labels: torch.Tensor, act_lens: torch.Tensor, label_lens: torch.Tensor,
                  blank: int, zero_infinity: bool, grad_scale: float, want_grads: bool,
-                 max_label_len: int, nan_to_zero: bool = False
-                 ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+                 max_label_len: int, nan_to_zero: bool = False, comm_handle: int = 0
+                 ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
     # third output: int32 [1] count of NaN logits replaced (empty unless nan_to_zero); fourth: sum(costs), fp32 [1],
     # produced by the library beside the gradient kernels
     nans = (torch.zeros(1, dtype=torch.int32, device=acts.device) if nan_to_zero
             else torch.empty(0, dtype=torch.int32, device=acts.device))
+    # fifth: the same sum over all ranks of a PeerLossAllReduce communicator (empty without one)
     loss = torch.empty(1, dtype=torch.float32, device=acts.device)
+    loss_all = torch.empty(1 if comm_handle else 0, dtype=torch.float32, device=acts.device)
     costs, grads = ctc_forward_backward(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale,
                                         want_grads, max_label_len if max_label_len >= 0 else None,
                                         nan_to_zero=nan_to_zero, nan_count=nans if nan_to_zero else None,
-                                        loss_sum=loss)
+                                        loss_sum=loss, loss_sum_all=loss_all if comm_handle else None,
+                                        comm=_CommRef(comm_handle) if comm_handle else None)
     if grads is None:
         grads = torch.empty(0, dtype=torch.float32, device=acts.device)
-    return costs, grads, nans, loss
+    return costs, grads, nans, loss, loss_all
 
 
 @_ctc_loss_op.register_fake
 def _(acts, labels, act_lens, label_lens, blank, zero_infinity, grad_scale, want_grads, max_label_len,
-      nan_to_zero=False):
+      nan_to_zero=False, comm_handle=0):
     costs = acts.new_empty((acts.shape[1],))
     grads = torch.empty_like(acts) if want_grads else acts.new_empty((0,))
-    return costs, grads, acts.new_empty((1 if nan_to_zero else 0,), dtype=torch.int32), acts.new_empty((1,))
+    return (costs, grads, acts.new_empty((1 if nan_to_zero else 0,), dtype=torch.int32), acts.new_empty((1,)),
+            acts.new_empty((1 if comm_handle else 0,)))
 
 
 class _CTCFunction(torch.autograd.Function):
@@ -301,24 +317,24 @@ class _CTCFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, acts, labels, act_lens, label_lens, blank, zero_infinity, scale, max_label_len, want,
-                nan_to_zero=False):
-        costs, grads, nans, loss = _ctc_loss_op(acts, labels, act_lens, label_lens, blank, zero_infinity, scale, want,
-                                                -1 if max_label_len is None else int(max_label_len), nan_to_zero)
+                nan_to_zero=False, comm_handle=0):
+        costs, grads, nans, loss, loss_all = _ctc_loss_op(acts, labels, act_lens, label_lens, blank, zero_infinity,
+                                                          scale, want,
+                                                          -1 if max_label_len is None else int(max_label_len),
+                                                          nan_to_zero, int(comm_handle))
         ctx.has_grads = want
         if want:
             ctx.save_for_backward(grads)
         loss = loss * scale if scale != 1.0 else loss
-        if nan_to_zero:
-            ctx.mark_non_differentiable(nans)
-            return loss, nans
-        return loss
+        ctx.mark_non_differentiable(nans, loss_all)
+        return loss, nans, loss_all
 
     @staticmethod
     def backward(ctx, grad_output, *unused):
         if not ctx.has_grads:
-            return (None,) * 10
+            return (None,) * 11
         (grads,) = ctx.saved_tensors
-        return (grads * grad_output.reshape(1, 1, 1).to(grads.device),) + (None,) * 9
+        return (grads * grad_output.reshape(1, 1, 1).to(grads.device),) + (None,) * 10
 
 
 class CTCLoss(torch.nn.Module):
@@ -334,11 +350,18 @@ class CTCLoss(torch.nn.Module):
     logits[torch.isnan(logits)] = 0`, two sweeps over the logits and a host sync): NaN logits are read as 0 inside
     the softmax pass, and `self.nan_count` (CUDA int32 [1]) holds how many the last call replaced -- read it only
     where the reference's warning is wanted, it is the one thing here that synchronises.
+    comm=sharding.PeerLossAllReduce() (multi-GPU, one process per GPU): after every call `self.loss_all_ranks` holds the
+    returned loss summed over ALL ranks -- what `reduce_tensor(loss, world_size) * world_size` gives in the reference
+    (data/utils.py:40-44, train.py:356,461,606) -- exchanged by the library's cost-summing kernel over NVLink peer
+    memory while the gradient kernels run, with no collective launch.  The returned loss itself stays rank-local,
+    as in the reference.
     """
 
     def __init__(self, blank: int = 0, size_average: bool = False, length_average: bool = False,
-                 zero_infinity: bool = True, loss_on_cpu: bool = False, nan_to_zero: bool = False):
+                 zero_infinity: bool = True, loss_on_cpu: bool = False, nan_to_zero: bool = False, comm=None):
         super().__init__()
+        self.comm = comm
+        self.loss_all_ranks = None
         self.blank = blank
         self.size_average = size_average
         self.length_average = length_average
@@ -357,10 +380,11 @@ class CTCLoss(torch.nn.Module):
             scale = 1.0 / float(acts.shape[1])
         # grad mode is off inside autograd.Function.forward, so decide here whether gradients are wanted
         want = bool(acts.requires_grad and torch.is_grad_enabled())
+        loss, nans, loss_all = _CTCFunction.apply(acts, labels, act_lens, label_lens, self.blank, self.zero_infinity,
+                                                  scale, max_label_len, want, self.nan_to_zero,
+                                                  self.comm.handle if self.comm is not None else 0)
         if self.nan_to_zero:
-            loss, self.nan_count = _CTCFunction.apply(acts, labels, act_lens, label_lens, self.blank,
-                                                      self.zero_infinity, scale, max_label_len, want, True)
-        else:
-            loss = _CTCFunction.apply(acts, labels, act_lens, label_lens, self.blank, self.zero_infinity, scale,
-                                      max_label_len, want)
+            self.nan_count = nans
+        if self.comm is not None:
+            self.loss_all_ranks = loss_all * scale if scale != 1.0 else loss_all
         return loss.cpu() if self.loss_on_cpu else loss

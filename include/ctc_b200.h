@@ -80,10 +80,12 @@ typedef struct {
                               fp64 by one small kernel that runs as soon as the recursions are done, beside the
                               gradient kernels (the same point costs_ready marks), so the caller needs no reduction
                               launch of its own after the call. */
-    void *comm;            /* ctcB200Comm* or NULL.  With a communicator (multi-GPU, one process per GPU) loss_sum
-                              receives the sum over ALL ranks: the same one-warp kernel exchanges the per-rank sums
-                              over NVLink peer memory (see ctc_b200_comm_create).  Requires loss_sum; every rank of
-                              the communicator must make the same sequence of calls. */
+    void *comm;            /* ctcB200Comm* or NULL.  With a communicator (multi-GPU, one process per GPU)
+                              loss_sum_all receives the sum over ALL ranks: the same one-warp kernel exchanges the
+                              per-rank sums over NVLink peer memory (see ctc_b200_comm_create).  Requires
+                              loss_sum_all; every rank of the communicator must make the same sequence of calls. */
+    float *loss_sum_all;   /* DEVICE float or NULL; sum of loss_sum over the ranks of `comm` (without a communicator:
+                              the same value as loss_sum) -- what reduce_tensor (data/utils.py:40-44) all-reduces */
 } ctcB200Options;
 
 /* replaces get_warpctc_version() */
@@ -164,7 +166,7 @@ ctcB200Status ctc_b200_greedy_decode(const float *acts, long long stride_t, long
  *   ctc_b200_comm_handle(c, handle64)            64 opaque bytes (a cudaIpcMemHandle_t); exchange them by any means
  *                                                (the Python side uses torch.distributed.all_gather_object)
  *   ctc_b200_comm_open(c, handles)               handles = world x 64 bytes in rank order
- * then pass `comm` + `loss_sum` in the options of ctc_b200_compute.  ctc_b200_comm_set_peers is the same for ranks
+ * then pass `comm` + `loss_sum_all` in the options of ctc_b200_compute.  ctc_b200_comm_set_peers is the same for ranks
  * that share one process (raw ctc_b200_comm_local pointers instead of IPC handles).
  */
 typedef struct ctcB200Comm ctcB200Comm;

@@ -542,17 +542,32 @@ def test_fused_loss_all_reduce_two_ranks_one_device(b200):
     streams = [torch.cuda.Stream(), torch.cuda.Stream()]
     parts = [b200.sharding.take_shard(d["acts"], d["labels"], d["act_lens"], d["label_lens"], ids) for ids in shards]
     outs = [torch.zeros(1, device="cuda") for _ in range(2)]
+    mine = [torch.zeros(1, device="cuda") for _ in range(2)]
     for it in range(3):
         costs = []
         for r in range(2):
             a, l, al, ll = parts[r]
             with torch.cuda.stream(streams[r]):
-                c, _ = b200.ctc_forward_backward(a.cuda() * (1.0 + 0.1 * it), l, al, ll, loss_sum=outs[r],
-                                                 comm=comms[r])
+                c, _ = b200.ctc_forward_backward(a.cuda() * (1.0 + 0.1 * it), l, al, ll, loss_sum=mine[r],
+                                                 loss_sum_all=outs[r], comm=comms[r])
                 costs.append(c)
         torch.cuda.synchronize()
         local = [np.float32(c.cpu().numpy().astype(np.float64).sum()) for c in costs]
         want = np.float32(np.float64(local[0]) + np.float64(local[1]))
         assert outs[0].item() == outs[1].item() == want, (it, outs[0].item(), outs[1].item(), want)
+        assert [m.item() for m in mine] == local
+    # the drop-in module: the returned loss stays rank-local, criterion.loss_all_ranks is the reduce_tensor value
+    crits = [b200.CTCLoss(comm=comms[r]) for r in range(2)]
+    losses = []
+    for r in range(2):
+        a, l, al, ll = parts[r]
+        with torch.cuda.stream(streams[r]):
+            x = a.cuda().requires_grad_(True)
+            loss = crits[r](x, l, al, ll)
+            (loss / a.shape[1]).backward()
+            losses.append(loss)
+    torch.cuda.synchronize()
+    tot = np.float32(np.float64(losses[0].item()) + np.float64(losses[1].item()))
+    assert crits[0].loss_all_ranks.item() == crits[1].loss_all_ranks.item() == tot
     for c in comms:
         c.close()

@@ -557,7 +557,6 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.bord = pl.nslices > 1 ? reinterpret_cast<int *>(ws + pl.o_bord) : nullptr;
     p.slice0 = 0;
     p.slice_nb = B;
-    p.dbg_flags = env_int("CTC_B200_DBG", 0);
     p.nan_to_zero = o.nan_to_zero ? 1 : 0;
     p.nan_count = o.nan_to_zero ? o.nan_count : nullptr;
 

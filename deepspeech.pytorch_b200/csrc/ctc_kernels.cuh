@@ -73,7 +73,6 @@ struct CtcParams {
     int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
     int nan_to_zero;    // 1: a NaN logit is read as 0 (the reference's train.py:595-598 guard, folded into the softmax pass)
     int *nan_count;     // optional: += number of NaN logits seen in valid frames (nan_to_zero only)
-    int dbg_flags;      // experiment switches (CTC_B200_DBG); 0 in production
 #ifdef CTC_PROFILE
     long long *dbg;     // [ctas][16 warps][8] clock counters (tools/ubench/engine_bench.cu only)
 #endif
@@ -292,7 +291,6 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     // they are scheduled first and run under the softmax blocks instead of forming the tail of the launch.
     const int nextra = (int)gridDim.x - nrb;  // B utterance blocks (+1 sort block when the launch is sliced)
     if ((int)blockIdx.x < nextra) {
-        if (p.dbg_flags & 2) return;  // experiment: time the row blocks alone
         if ((int)blockIdx.x == p.B)
             sort_by_length(p, reinterpret_cast<int *>(smem));
         else
@@ -1056,7 +1054,6 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
                 for (int j = 0; j < nq; ++j) ob += bpart[r * Lp + j * 32 + lane];
 #pragma unroll
                 for (int d = 16; d; d >>= 1) ob += __shfl_xor_sync(kFull, ob, d);
-                if (p.dbg_flags & 1) continue;
                 if (lane == 0) atomicAdd(grow + p.blank, nscale * ob);
                 for (int j = lane; j < L; j += 32) {
                     const int2 e = __ldg(ct + j);

@@ -52,7 +52,6 @@ int main(int argc, char **argv) {
     CK(cudaMalloc(&p.dbg, 8 * 2 * B * 16 * 8 + 8192)); CK(cudaMemset(p.dbg, 0, 8 * 2 * B * 16 * 8 + 8192));
 #endif
     p.nqmax = (2 * Lmax + 1 + 223) / 224;
-    p.dbg_flags = getenv("CTC_B200_DBG") ? atoi(getenv("CTC_B200_DBG")) : 0;
     size_t s_prep = prep_smem(C, Lmax), s_eng = engine_smem(p.Cp, p.nwl).total, s_grad = grad_smem(C, p.Cp, Lmax, p.nqmax, kK, false).total;
     { int resident = (int)(227 * 1024 / s_grad); if (resident < 1) resident = 1; p.nsplit = (2 * 148 * resident + B - 1) / B; if (p.nsplit > p.nblk) p.nsplit = p.nblk; if (argc > 5) p.nsplit = atoi(argv[5]); }
     CK(cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));

@@ -94,14 +94,16 @@ struct __align__(8) Slot {
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
 // Posterior rows of the gradient kernel (one per time step of a group): [0, Lmax) label posteriors at their
-// class-sorted positions, then nq * 32 per-thread partial sums of the blank posteriors.  The pitch is 1 (mod 32) so
+// class-sorted positions, then nq * 32 per-thread partial sums of the blank posteriors.  The pitch is odd so
 // that the 8 rows of a group start in 8 different banks.
 constexpr int kUnit = 8;         // positions per reduction unit
 constexpr int kCoreThreads = 28; // engine threads per gradient-kernel warp (224 states) + 2 halo threads each side
 __host__ __device__ inline int grad_nq(int L) { return (2 * L + 1 + 8 * kCoreThreads - 1) / (8 * kCoreThreads); }
 __host__ __device__ inline int grad_row_pitch(int Lmax, int nqmax) {
     const int n = (Lmax > 0 ? Lmax : 1) + nqmax * 32;
-    return ((n + 30) / 32) * 32 + 1;
+    return n | 1;  // any ODD pitch puts the 8 rows of a group in 8 different residues mod 8, hence (with units 8 banks
+                   // apart) the reduction's (unit, row) lanes in 32 different banks; the smallest one saves up to 31
+                   // floats per row -- at B=64,T=1000,C=5000 (Lmax 183) exactly what lets a 4th CTA fit on the SM
 }
 __host__ __device__ inline int grad_max_units(int C, int Lmax, int nqmax) {
     return ((Lmax > 0 ? Lmax : 1) + kUnit - 1) / kUnit + C + nqmax * (32 / kUnit);

@@ -101,6 +101,11 @@ constexpr int kCoreThreads = 28; // engine threads per gradient-kernel warp (224
 __host__ __device__ inline int grad_nq(int L) { return (2 * L + 1 + 8 * kCoreThreads - 1) / (8 * kCoreThreads); }
 __host__ __device__ inline int grad_row_pitch(int Lmax, int nqmax) {
     const int n = (Lmax > 0 ? Lmax : 1) + nqmax * 32;
+#ifdef CTC_PITCH_EXTRA  // tools/ubench experiment: other odd pitches.  Measured on the headline shape (engine_bench,
+                        // gradient kernel alone): +0 98.4 us, +2 / +4 / +8 / +16 / +24 / +32 floats 105.3-106.5 us --
+                        // a step at 55.5 KB of shared memory per CTA, not a bank-conflict effect
+    return (n | 1) + 2 * (CTC_PITCH_EXTRA);
+#endif
     return n | 1;  // any ODD pitch puts the 8 rows of a group in 8 different residues mod 8, hence (with units 8 banks
                    // apart) the reduction's (unit, row) lanes in 32 different banks; the smallest one saves up to 31
                    // floats per row -- at B=64,T=1000,C=5000 (Lmax 183) exactly what lets a 4th CTA fit on the SM

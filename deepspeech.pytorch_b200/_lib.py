@@ -23,7 +23,8 @@ EXPORTS = ("ctc_b200_get_version", "ctc_b200_status_string", "ctc_b200_default_o
            "ctc_b200_compute", "ctc_b200_create", "ctc_b200_destroy", "ctc_b200_compute_host",
            "ctc_b200_compute_decode", "ctc_b200_greedy_decode", "ctc_b200_error_counts", "ctc_b200_last_launch_count",
            "ctc_b200_comm_create", "ctc_b200_comm_handle", "ctc_b200_comm_local", "ctc_b200_comm_open",
-           "ctc_b200_comm_set_peers", "ctc_b200_comm_destroy")
+           "ctc_b200_comm_set_peers", "ctc_b200_comm_destroy", "ctc_b200_comm_set_timeout",
+           "ctc_b200_comm_timed_out", "ctc_b200_scale_grads", "ctc_b200_last_copy_bytes")
 
 
 class CtcOptions(ctypes.Structure):
@@ -105,10 +106,18 @@ def load():
     lib.ctc_b200_comm_set_peers.restype = I
     lib.ctc_b200_comm_destroy.argtypes = [V]
     lib.ctc_b200_comm_destroy.restype = I
+    lib.ctc_b200_comm_set_timeout.argtypes = [V, ctypes.c_longlong]
+    lib.ctc_b200_comm_set_timeout.restype = I
+    lib.ctc_b200_comm_timed_out.argtypes = [V]
+    lib.ctc_b200_comm_timed_out.restype = I
+    lib.ctc_b200_scale_grads.argtypes = [V, ctypes.c_size_t, V, P(CtcOptions)]
+    lib.ctc_b200_scale_grads.restype = I
     lib.ctc_b200_greedy_decode.argtypes = [V, ctypes.c_longlong, ctypes.c_longlong, V, I, I, I, V, V, V, V,
                                            P(CtcOptions)]
     lib.ctc_b200_greedy_decode.restype = I
     lib.ctc_b200_last_launch_count.restype = I
+    lib.ctc_b200_last_copy_bytes.argtypes = [P(ctypes.c_ulonglong), P(ctypes.c_ulonglong)]
+    lib.ctc_b200_last_copy_bytes.restype = None
     _lib = lib
     return lib
 

@@ -30,6 +30,9 @@ struct ctcB200Comm {
     unsigned long long **peers_dev = nullptr;  // device array [world]
     void *opened[kCommMaxWorld] = {};
     bool ready = false;
+    unsigned long long timeout_ns = 120ull * 1000000000ull;  // wall-clock bound of one exchange
+    int *timed_out_host = nullptr;             // pinned, host-mapped: set by the kernel when a peer never arrived
+    int *timed_out_dev = nullptr;              // the same word as the device sees it
 };
 
 namespace {
@@ -37,12 +40,13 @@ namespace {
 constexpr int kK = 8;               // states per lattice thread
 constexpr size_t kSmemLimit = 227 * 1024;
 thread_local int g_last_launches = 0;
+thread_local unsigned long long g_last_h2d = 0, g_last_d2h = 0;  // bytes the last ctc_b200_compute_host copied
 
 // where the summed loss goes, and (multi-GPU) the communicator its kernel all-reduces through
 struct LossOut {
     float *loss_sum = nullptr;  // this rank's sum
     float *loss_all = nullptr;  // sum over all ranks of the communicator
-    CommArgs comm = {nullptr, nullptr, 0, 1};
+    CommArgs comm = {nullptr, nullptr, 0, 1, 0ull, nullptr};
     explicit operator bool() const { return loss_sum != nullptr || loss_all != nullptr; }
 };
 
@@ -57,6 +61,7 @@ struct SidePool {
 };
 SidePool g_pool[64];
 std::mutex g_pool_mu;  // held while a sliced launch is being enqueued: the pool's events are shared by all callers
+std::mutex g_attr_mu;  // guards the "max dynamic shared memory already raised on this device" caches below
 
 SidePool *side_pool(int dev) {
     if (dev < 0 || dev >= 64) return nullptr;
@@ -288,6 +293,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
+    std::unique_lock<std::mutex> attr_lock(g_attr_mu);
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)kSmemLimit);
@@ -300,6 +306,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
+    attr_lock.unlock();
     cudaError_t e = cudaSuccess;
     if (!(phase_mask & 4) && p.T > 0) {
         const long long rows = (long long)p.T * p.B;
@@ -339,6 +346,7 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
+    std::unique_lock<std::mutex> attr_lock(g_attr_mu);
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         e = cudaFuncSetAttribute(ctc_prep_utt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit);
         if (e != cudaSuccess) return e;
@@ -359,6 +367,7 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
+    attr_lock.unlock();
     const bool do_rows = !(phase_mask & 4) && p.T > 0;
     const bool do_engine = !(phase_mask & 1);
     const bool do_grad = !p.score_only && p.T > 0 && !(phase_mask & 2);
@@ -452,6 +461,11 @@ ctcB200Status ctc_b200_workspace_size(int T, int B, int C, int max_label_len, co
 
 int ctc_b200_last_launch_count(void) { return g_last_launches; }
 
+void ctc_b200_last_copy_bytes(unsigned long long *h2d, unsigned long long *d2h) {
+    if (h2d) *h2d = g_last_h2d;
+    if (d2h) *d2h = g_last_d2h;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------ compute
@@ -492,6 +506,9 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     if (!make_plan(T, B, C, Lmax, &pl)) return CTC_B200_STATUS_INVALID_VALUE;
     if (workspace_bytes < pl.total) return CTC_B200_STATUS_INVALID_VALUE;
     if (!allow_slices) pl.nslices = 1;  // the host-buffer path pipelines whole utterance slices itself
+    // the length ranking (bord) is written by the prep launch: without it (T == 0, or the prep phase masked out on
+    // a call that was not preceded by a full one) the engines must not index through it
+    if (T == 0) pl.nslices = 1;
 
     unsigned char *ws = static_cast<unsigned char *>(workspace);
     CtcParams p;
@@ -567,7 +584,11 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     if (o.comm) {
         const ctcB200Comm *cm = static_cast<const ctcB200Comm *>(o.comm);
         if (!o.loss_sum_all || !cm->ready) return CTC_B200_STATUS_INVALID_VALUE;
-        lo.comm = CommArgs{cm->local, cm->peers_dev, cm->rank, cm->world};
+        // a peer missed an earlier exchange (it skipped a call, or stalled past the timeout): the ranks are out of
+        // step and every further exchange would be wrong -- refuse instead of running the protocol on
+        if (cm->timed_out_host && *reinterpret_cast<volatile int *>(cm->timed_out_host))
+            return CTC_B200_STATUS_EXECUTION_FAILED;
+        lo.comm = CommArgs{cm->local, cm->peers_dev, cm->rank, cm->world, cm->timeout_ns, cm->timed_out_dev};
     }
     cudaError_t e = launch_all(p, pl, st, o.phase_mask, &launches, (cudaEvent_t)o.costs_ready, lo);
     g_last_launches = launches;
@@ -622,14 +643,32 @@ extern "C" ctcB200Status ctc_b200_comm_create(ctcB200Comm **out, int rank, int w
     if (cudaMalloc((void **)&c->local, kCommBytes) != cudaSuccess ||
         cudaMemset(c->local, 0, kCommBytes) != cudaSuccess ||
         cudaMalloc((void **)&c->peers_dev, sizeof(void *) * kCommMaxWorld) != cudaSuccess ||
+        cudaHostAlloc((void **)&c->timed_out_host, sizeof(int), cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostGetDevicePointer((void **)&c->timed_out_dev, c->timed_out_host, 0) != cudaSuccess ||
         cudaDeviceSynchronize() != cudaSuccess) {
         cudaFree(c->local);
         cudaFree(c->peers_dev);
+        if (c->timed_out_host) cudaFreeHost(c->timed_out_host);
         delete c;
         return CTC_B200_STATUS_MEMOPS_FAILED;
     }
+    *c->timed_out_host = 0;
+    if (const char *v = getenv("CTC_B200_COMM_TIMEOUT_MS"))
+        if (*v) c->timeout_ns = (unsigned long long)atoll(v) * 1000000ull;
     *out = c;
     return CTC_B200_STATUS_SUCCESS;
+}
+
+extern "C" ctcB200Status ctc_b200_comm_set_timeout(ctcB200Comm *c, long long milliseconds) {
+    if (!c || milliseconds <= 0) return CTC_B200_STATUS_INVALID_VALUE;
+    c->timeout_ns = (unsigned long long)milliseconds * 1000000ull;
+    return CTC_B200_STATUS_SUCCESS;
+}
+
+// 1 once an exchange of this communicator has timed out (sticky; the communicator is then unusable: destroy it and
+// build a new one on every rank, or continue with the caller's own collective)
+extern "C" int ctc_b200_comm_timed_out(const ctcB200Comm *c) {
+    return (c && c->timed_out_host) ? *reinterpret_cast<volatile int *>(c->timed_out_host) : 0;
 }
 
 extern "C" ctcB200Status ctc_b200_comm_handle(ctcB200Comm *c, void *handle64) {
@@ -683,8 +722,26 @@ extern "C" ctcB200Status ctc_b200_comm_destroy(ctcB200Comm *c) {
         if (c->opened[r]) cudaIpcCloseMemHandle(c->opened[r]);
     cudaFree(c->local);
     cudaFree(c->peers_dev);
+    if (c->timed_out_host) cudaFreeHost(c->timed_out_host);
     delete c;
     return CTC_B200_STATUS_SUCCESS;
+}
+
+// ------------------------------------------------------------------------------------------------ backward scaling
+extern "C" ctcB200Status ctc_b200_scale_grads(float *grads, size_t count, const float *scale_dev,
+                                              const ctcB200Options *opts_in) {
+    g_last_launches = 0;
+    if (!grads || !scale_dev) return CTC_B200_STATUS_INVALID_VALUE;
+    if (count == 0) return CTC_B200_STATUS_SUCCESS;
+    cudaStream_t st = opts_in ? (cudaStream_t)opts_in->stream : nullptr;
+    // enough CTAs to saturate HBM when the pass is needed (8 resident CTAs of 256 threads on each of the 148 SMs),
+    // never more than one float4 per thread would need
+    size_t want = (count / 4 + 255) / 256;
+    if (want < 1) want = 1;
+    const unsigned grid = (unsigned)(want < 148 * 8 ? want : 148 * 8);
+    ctc_scale_grads_kernel<<<grid, 256, 0, st>>>(grads, count, scale_dev);
+    ++g_last_launches;
+    return cudaGetLastError() == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }
 
 // ------------------------------------------------------------------------------------------------ WER / CER counts
@@ -703,12 +760,14 @@ extern "C" ctcB200Status ctc_b200_error_counts(const int *hyp_ids, int hyp_pitch
     static bool attr_set[64] = {false};
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+    std::unique_lock<std::mutex> attr_lock(g_attr_mu);
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         if (cudaFuncSetAttribute(ctc_error_counts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit) != cudaSuccess)
             return CTC_B200_STATUS_EXECUTION_FAILED;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
+    attr_lock.unlock();
     ctc_error_counts_kernel<<<B, kMetricThreads, smem, (cudaStream_t)o.stream>>>(
         hyp_ids, hyp_pitch, hyp_lens, ref_labels, ref_lens, B, max_hyp_len, max_ref_len, space_index,
         reinterpret_cast<int4 *>(counts));
@@ -886,6 +945,7 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         if (cudaEventRecord(c->start, user) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
     }
     int launches = 0;
+    unsigned long long h2d = sizeof(int) * (total_labels + 2 * (size_t)B), d2h = 0;
     const size_t host_pitch = (size_t)B * C * sizeof(float);
     // CTC_B200_HOST_TRACE=1: print the device timeline of this call (per slice: upload done, kernels done, download
     // done, in us after the call's first enqueue) and the host-side enqueue / wait times.  A diagnostic: the events
@@ -911,6 +971,8 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         if (Tk > 0 && cudaMemcpy2DAsync(da, width, acts_host + (size_t)b0 * C, host_pitch, width, (size_t)Tk,
                                         cudaMemcpyHostToDevice, st) != cudaSuccess)
             return CTC_B200_STATUS_MEMOPS_FAILED;
+        h2d += (unsigned long long)width * Tk;
+        d2h += (dg ? (unsigned long long)width * Tk : 0ull) + sizeof(float) * (size_t)nb;
         if (trace) cudaEventRecord(tr[k][0], st);
         ctcB200Options ok = o;
         ok.stream = (void *)st;
@@ -939,6 +1001,8 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         }
     }
     g_last_launches = launches;
+    g_last_h2d = h2d;
+    g_last_d2h = d2h;
     if (grads_host)  // padding frames past each slice's longest utterance (disjoint from what the downloads write)
         for (int k = 0; k < nch; ++k) {
             const size_t width = (size_t)(b0s[k + 1] - b0s[k]) * C * sizeof(float);

@@ -283,6 +283,11 @@ __device__ __forceinline__ void sort_by_length(const CtcParams &p, int *keys) {
 // NaN guard of the training loop (/root/reference/train.py:595-598: `logits[torch.isnan(logits)] = 0` ahead of the
 // criterion): with nan_to_zero set every read of a logit goes through this, so all passes see the same value.
 __device__ __forceinline__ float nan_fix(float v, bool ntz) { return (ntz && v != v) ? 0.f : v; }
+// softmax value clamped to >= 2^-126; a row whose sum is NaN (`bad`) stays NaN instead of collapsing onto the clamp
+constexpr unsigned kNanHi = 0x7ff80000u;  // high word of a quiet fp64 NaN (planar emission rows)
+__device__ __forceinline__ float clamp_y(float v, bool bad) {
+    return bad ? __int_as_float(0x7fc00000) : fmaxf(v, 1.17549435e-38f);
+}
 
 __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -368,6 +373,14 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
             v = fmaxf(e[1] * inv, 1.17549435e-38f); hi.y = y_hi_word(v); lo.y = y_lo_word(v);
             v = fmaxf(e[2] * inv, 1.17549435e-38f); hi.z = y_hi_word(v); lo.z = y_lo_word(v);
             v = fmaxf(e[3] * inv, 1.17549435e-38f); hi.w = y_hi_word(v); lo.w = y_lo_word(v);
+            if (sum != sum) {
+                // a NaN or +Inf logit (not scrubbed by nan_to_zero) makes the row sum NaN: the whole row becomes NaN
+                // and propagates through the recursions into cost and gradient of this utterance, as it would in
+                // the reference's criterion (whose caller then reports it, train.py:604-611) -- never a finite
+                // wrong value (fmaxf would have returned the clamp)
+                hi = make_uint4(kNanHi, kNanHi, kNanHi, kNanHi);
+                lo = make_uint4(0u, 0u, 0u, 0u);
+            }
             *reinterpret_cast<uint4 *>(ydst + 4 * j) = hi;
             *reinterpret_cast<uint4 *>(ydst + Cp + 4 * j) = lo;
         } else if (valid && p.grads) {
@@ -738,16 +751,17 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
             e = em;
         }
         const int ex = expo_field(m);
+        const bool isnan_p = m != m;  // a non-finite emission row reached the lattice: cost and gradient are NaN
         const bool ok = ex != 0 && ex != 2047 && e > kDeadE / 2;
         if (ok) {
             m *= pow2i(1023 - ex);
             e += ex - 1023;
         }
-        p.feas[b] = ok;
-        p.Pm[b] = ok ? m : 1.0;
+        p.feas[b] = ok || isnan_p;
+        p.Pm[b] = (ok || isnan_p) ? m : 1.0;
         p.Pe[b] = ok ? e : 0;
         const double cost = -(log(m) + (double)e * 0.69314718055994530942);
-        p.costs[b] = ok ? (float)cost : (p.zero_infinity ? 0.f : INFINITY);
+        p.costs[b] = isnan_p ? __int_as_float(0x7fc00000) : (ok ? (float)cost : (p.zero_infinity ? 0.f : INFINITY));
     }
 }
 
@@ -1243,6 +1257,7 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const Ctc
     }
     sum = block_reduce(sum, red, false);  // its barriers also publish the exponentials to the whole CTA
     const float inv = 1.0f / sum;
+    const bool bad = sum != sum;  // NaN / +Inf logit in the row: everything derived from it is NaN (see ctc_prep_kernel)
     if (g4) {
         const float scale = p.grad_scale;
 #pragma unroll
@@ -1250,10 +1265,10 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const Ctc
             const int i = tid + k * kBigThreads;
             if (i < n4) {
                 float4 o;
-                o.x = scale * fmaxf(v[k].x * inv, 1.17549435e-38f);
-                o.y = scale * fmaxf(v[k].y * inv, 1.17549435e-38f);
-                o.z = scale * fmaxf(v[k].z * inv, 1.17549435e-38f);
-                o.w = scale * fmaxf(v[k].w * inv, 1.17549435e-38f);
+                o.x = scale * clamp_y(v[k].x * inv, bad);
+                o.y = scale * clamp_y(v[k].y * inv, bad);
+                o.z = scale * clamp_y(v[k].z * inv, bad);
+                o.w = scale * clamp_y(v[k].w * inv, bad);
                 __stcs(g4 + i, o);
             }
         }
@@ -1270,8 +1285,8 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const Ctc
             const int c = (j == 0) ? p.blank : min(max(p.labels[off + j - 1], 0), C - 1);
             y = fmaxf(srow[c] * inv, 1.17549435e-38f);
         }
-        ydst[j] = y_hi_word(y);
-        ydst[CP + j] = y_lo_word(y);
+        ydst[j] = bad ? kNanHi : y_hi_word(y);
+        ydst[CP + j] = bad ? 0u : y_lo_word(y);
     }
 }
 
@@ -1349,6 +1364,7 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
     }
     sum = block_reduce(sum, red, false);  // its barriers also publish the exponentials to the whole CTA
     const float inv = 1.0f / sum;
+    const bool bad = sum != sum;  // NaN / +Inf logit in the row: everything derived from it is NaN (see ctc_prep_kernel)
     // ---- pass 3: the dense part of the gradient, scale * softmax, written once (the occupancies of the <= 1 + L
     // classes on the lattice are subtracted by the gradient kernel)
     if (g) {
@@ -1364,15 +1380,15 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
                 e.x = expf(v.x - m); e.y = expf(v.y - m); e.z = expf(v.z - m); e.w = expf(v.w - m);
             }
             float4 o;
-            o.x = scale * fmaxf(e.x * inv, 1.17549435e-38f);
-            o.y = scale * fmaxf(e.y * inv, 1.17549435e-38f);
-            o.z = scale * fmaxf(e.z * inv, 1.17549435e-38f);
-            o.w = scale * fmaxf(e.w * inv, 1.17549435e-38f);
+            o.x = scale * clamp_y(e.x * inv, bad);
+            o.y = scale * clamp_y(e.y * inv, bad);
+            o.z = scale * clamp_y(e.z * inv, bad);
+            o.w = scale * clamp_y(e.w * inv, bad);
             __stcs(reinterpret_cast<float4 *>(g) + i, o);
         }
         for (int c = (g4 << 2) + tid; c < C; c += kBigThreads) {
             const float e = staged ? srow[c] : expf(nan_fix(__ldg(x + c), ntz) - m);
-            g[c] = scale * fmaxf(e * inv, 1.17549435e-38f);
+            g[c] = scale * clamp_y(e * inv, bad);
         }
     }
     // ---- compact emission row, planar fp64 words
@@ -1387,8 +1403,8 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
             const float e = staged ? srow[c] : expf(nan_fix(__ldg(x + c), ntz) - m);
             v = fmaxf(e * inv, 1.17549435e-38f);
         }
-        ydst[j] = y_hi_word(v);
-        ydst[CP + j] = y_lo_word(v);
+        ydst[j] = bad ? kNanHi : y_hi_word(v);
+        ydst[CP + j] = bad ? 0u : y_lo_word(v);
     }
 }
 
@@ -1403,14 +1419,22 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
 // 64-bit store into slot [e & 1][rank] of every peer, then polls its own slots [e & 1][0 .. world) until all carry
 // epoch e and adds the values in rank order (every rank gets the same bits).  Value and epoch travel in one word,
 // so no fence orders them; the two parities make reuse safe (a rank cannot enter call e+2 before every peer has
-// entered call e+1, i.e. finished reading call e).  A peer that never arrives turns the result into NaN after
-// ~10 s instead of hanging the device.
+// entered call e+1, i.e. finished reading call e).  A late peer is waited for; one that has not arrived after the
+// communicator's wall-clock timeout turns the result into NaN and sets the communicator's sticky flag.
 constexpr int kCommMaxWorld = 32;
 struct CommArgs {
     unsigned long long *local;          // this rank's slots [2][kCommMaxWorld], then the call counter
     unsigned long long *const *peers;   // device array [world]: slot base of every rank (peers[rank] == local)
     int rank, world;
+    unsigned long long timeout_ns;      // wall-clock bound on the wait for the peers (globaltimer)
+    int *timed_out;                     // host-mapped sticky flag: set when a peer never arrived (see ctc_api.cu)
 };
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 __global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, int B, float *loss_sum,
                                                            float *loss_all, CommArgs ca) {
@@ -1448,14 +1472,49 @@ __global__ void __launch_bounds__(32) ctc_sum_costs_kernel(const float *costs, i
     if (lane < ca.world) {
         volatile unsigned long long *src = ca.local + par + lane;
         unsigned long long w = *src;
-        for (long long spins = 0; (unsigned)(w >> 32) != e && spins < 30000000ll; ++spins) w = *src;
+        // A peer that is late (checkpoint save, validation, a data-loader stall) is simply waited for, like a
+        // collective would; only after timeout_ns of WALL-CLOCK time (default 120 s, ctc_b200_comm_set_timeout) is
+        // the exchange given up: the result is NaN and the communicator's sticky flag makes every later call
+        // return an error status instead of running the protocol out of step.
+        if ((unsigned)(w >> 32) != e) {
+            const unsigned long long t0 = global_ns();
+            for (unsigned spins = 0;; ++spins) {
+                w = *src;
+                if ((unsigned)(w >> 32) == e) break;
+                if ((spins & 255u) == 255u && global_ns() - t0 > ca.timeout_ns) break;
+            }
+        }
         ok = (unsigned)(w >> 32) == e;
         mine = __uint_as_float((unsigned)w);
     }
     ok = __all_sync(kFull, ok);
     double tot = 0.0;
     for (int j = 0; j < ca.world; ++j) tot += (double)__shfl_sync(kFull, mine, j);
-    if (lane == 0) *loss_all = ok ? (float)tot : __int_as_float(0x7fc00000);
+    if (lane == 0) {
+        *loss_all = ok ? (float)tot : __int_as_float(0x7fc00000);
+        if (!ok && ca.timed_out) {
+            *reinterpret_cast<volatile int *>(ca.timed_out) = 1;
+            __threadfence_system();
+        }
+    }
+}
+
+// Gradient rows times a DEVICE scalar, in place -- the autograd backward of the drop-in module (the reference
+// binding returns `cached_grads * grad_output`, train.py:619-620 feeding 1/B through `loss / B`).  The scalar is
+// read on the device, so nothing waits on the host; when it is exactly 1 (a caller that folded the 1/B into the
+// criterion: size_average / grad_scale) every CTA leaves at once and the pass costs a launch, not 2 x [T,B,C] bytes.
+__global__ void __launch_bounds__(256) ctc_scale_grads_kernel(float *g, size_t n, const float *scale) {
+    const float s = __ldg(scale);
+    if (s == 1.0f) return;
+    const size_t n4 = (reinterpret_cast<uintptr_t>(g) & 15) == 0 ? n >> 2 : 0;
+    float4 *g4 = reinterpret_cast<float4 *>(g);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 v = g4[i];
+        v.x *= s; v.y *= s; v.z *= s; v.w *= s;
+        g4[i] = v;
+    }
+    for (size_t i = (n4 << 2) + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) g[i] *= s;
 }
 
 // ================================================================================================ greedy decoding

@@ -29,12 +29,42 @@ _ws_cache = {}
 
 
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    """Scratch for one call (contents are meaningless between calls).  Eager calls reuse one buffer per (device,
+    stream), regrown on demand.  While the stream is being CAPTURED into a CUDA graph the buffer is allocated inside
+    the capture instead (from the graph's private pool, so it lives exactly as long as the graph): a captured kernel
+    never points into the shared cache, which a later, larger eager call may regrow and free."""
+    if torch.cuda.is_current_stream_capturing():
+        return torch.empty(nbytes + 256, dtype=torch.uint8, device=device)
     key = (device.index, torch.cuda.current_stream(device).cuda_stream)
     ws = _ws_cache.get(key)
-    if ws is None or ws.numel() < nbytes:
+    if ws is None or ws.numel() < nbytes + 256:
         ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)
         _ws_cache[key] = ws
     return ws
+
+
+def clear_workspace_cache() -> None:
+    """Drop the cached eager workspaces (they are re-created on the next call)."""
+    _ws_cache.clear()
+
+
+def scale_grads_(grads: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
+    """grads *= scale (a CUDA fp32 scalar read on the device) in place through ctc_b200_scale_grads: no host
+    synchronisation, no allocation, and no pass over the tensor at all when the scalar is exactly 1."""
+    if not (grads.is_cuda and grads.dtype == torch.float32 and grads.is_contiguous()):
+        raise ValueError("grads must be a contiguous CUDA float32 tensor")
+    s = scale.detach().reshape(-1)
+    if s.numel() != 1:
+        raise ValueError("scale must have one element")
+    s = s.to(device=grads.device, dtype=torch.float32)
+    lib = _lib.load()
+    opts = _lib.CtcOptions()
+    lib.ctc_b200_default_options(ctypes.byref(opts))
+    with torch.cuda.device(grads.device):
+        opts.stream = torch.cuda.current_stream(grads.device).cuda_stream
+        _lib.check(lib.ctc_b200_scale_grads(grads.data_ptr(), grads.numel(), s.data_ptr(), ctypes.byref(opts)),
+                   "ctc_b200_scale_grads")
+    return grads
 
 
 def _as_i32(x, name: str) -> torch.Tensor:
@@ -334,7 +364,16 @@ class _CTCFunction(torch.autograd.Function):
         if not ctx.has_grads:
             return (None,) * 11
         (grads,) = ctx.saved_tensors
-        return (grads * grad_output.reshape(1, 1, 1).to(grads.device),) + (None,) * 10
+        if getattr(ctx, "consumed", False):
+            # a second backward through the same graph (retain_graph=True): the cached gradients already carry the
+            # first call's factor, so undo it out of place
+            return (grads * (grad_output.reshape(1, 1, 1).to(grads.device) / ctx.applied),) + (None,) * 10
+        # The reference binding's contract (cached grads * grad_output) without its extra [T,B,C] tensor: the cached
+        # gradients are scaled IN PLACE by the device scalar (no host sync), and not touched at all when it is 1.
+        ctx.applied = grad_output.detach().reshape(1, 1, 1).to(grads.device).clone()
+        ctx.consumed = True
+        scale_grads_(grads, grad_output)
+        return (grads,) + (None,) * 10
 
 
 class CTCLoss(torch.nn.Module):

@@ -74,11 +74,23 @@ def input_sizes_from_percentages(input_percentages: torch.Tensor, max_seqlength:
     return (input_percentages.float() * int(max_seqlength)).int()
 
 
-def conv_out_lens(input_lens: torch.Tensor, convs: Sequence[Tuple[int, int, int, int]] = ((11, 2, 5, 1), (11, 1, 5, 1))
-                  ) -> torch.Tensor:
+def conv_out_lens(input_lens: torch.Tensor, convs: Sequence[Tuple[int, int, int, int]] = ((11, 2, 5, 1), (11, 1, 5, 1)),
+                  true_division: bool = False) -> torch.Tensor:
     """act_lens from input lengths through a stack of time-axis convolutions given as (kernel, stride, padding,
     dilation) -- the formula of model.py:382-393.  The default is DeepSpeech2's two Conv2d time axes
-    (k=11,s=2,p=5 then k=11,s=1,p=5), i.e. floor((T_in - 1) / 2) + 1."""
+    (k=11,s=2,p=5 then k=11,s=1,p=5), i.e. floor((T_in - 1) / 2) + 1.
+
+    The reference writes `(n + 2p - d(k-1) - 1) / s + 1` on an IntTensor and truncates once at the end
+    (`seq_len.int()`).  On the torch versions it was written for `/` on integer tensors floors, i.e. every layer
+    floors -- which is also what the convolutions themselves produce and is the default here.  On torch >= 1.5 the
+    same expression is a TRUE division carried through the stack in floating point; `true_division=True` reproduces
+    that reading.  Both agree for the default stack (tests/test_host.py pins them against the reference's own
+    DeepSpeech.get_seq_lens for T_in = 1..4000); they can differ for stacks with more than one strided layer."""
+    if true_division:
+        x = input_lens.to(torch.int32)  # the reference starts from `lengths.cpu().int()` (model.py:345)
+        for k, s, p, d in convs:
+            x = (x + 2 * p - d * (k - 1) - 1) / s + 1
+        return x.int()
     n = input_lens.to(torch.int64)
     for k, s, p, d in convs:
         n = torch.div(n + 2 * p - d * (k - 1) - 1, s, rounding_mode="floor") + 1

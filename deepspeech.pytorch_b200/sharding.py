@@ -141,6 +141,18 @@ class PeerLossAllReduce:
             _lib.check(lib.ctc_b200_comm_set_peers(c.handle, locals_), "ctc_b200_comm_set_peers")
         return comms
 
+    def set_timeout(self, milliseconds: int) -> None:
+        """Wall-clock bound on one exchange (default 120 s): a late peer is waited for that long."""
+        from . import _lib
+
+        _lib.check(self._lib.ctc_b200_comm_set_timeout(self.handle, int(milliseconds)), "ctc_b200_comm_set_timeout")
+
+    @property
+    def timed_out(self) -> bool:
+        """True once an exchange was given up (a peer skipped a call or stalled past the timeout).  Sticky: every
+        later CTC call that names this communicator raises; build a new one on every rank or use NCCL."""
+        return bool(self.handle) and bool(self._lib.ctc_b200_comm_timed_out(self.handle))
+
     def close(self):
         if getattr(self, "handle", None):
             self._lib.ctc_b200_comm_destroy(self.handle)

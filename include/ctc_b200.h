@@ -176,6 +176,25 @@ void *ctc_b200_comm_local(ctcB200Comm *comm);
 ctcB200Status ctc_b200_comm_open(ctcB200Comm *comm, const void *handles);
 ctcB200Status ctc_b200_comm_set_peers(ctcB200Comm *comm, void *const *locals);
 ctcB200Status ctc_b200_comm_destroy(ctcB200Comm *comm);
+/*
+ * A late peer (checkpoint save, validation, a data-loader stall) is WAITED for, as reduce_tensor's collective
+ * would; only after `milliseconds` of wall-clock time (default 120 000, or the environment variable
+ * CTC_B200_COMM_TIMEOUT_MS at creation) is an exchange given up: loss_sum_all then receives NaN, the communicator's
+ * sticky flag is set (ctc_b200_comm_timed_out returns 1) and every later ctc_b200_compute that names this
+ * communicator returns CTC_B200_STATUS_EXECUTION_FAILED without enqueueing anything -- ranks that are out of step
+ * (one of them skipped a call) are reported, not silently summed.  Recover by destroying the communicator on every
+ * rank and creating a new one, or by all-reducing loss_sum with the caller's own collective.
+ */
+ctcB200Status ctc_b200_comm_set_timeout(ctcB200Comm *comm, long long milliseconds);
+int ctc_b200_comm_timed_out(const ctcB200Comm *comm);
+
+/*
+ * grads[i] *= *scale_dev for i in [0, count), in place, enqueued on opts->stream -- the autograd backward of the
+ * reference binding (`cached_grads * grad_output`, reached from loss.backward() at /root/reference/train.py:620
+ * with grad_output = 1/B from train.py:601).  The scalar is read on the DEVICE (no host synchronisation); when it
+ * is exactly 1.0 the kernel returns without touching the gradients.
+ */
+ctcB200Status ctc_b200_scale_grads(float *grads, size_t count, const float *scale_dev, const ctcB200Options *opts);
 
 /*
  * Word / character error counts of decoded transcripts against the targets -- SURVEY.md 8(f) rank 4.  Replaces, per
@@ -201,6 +220,9 @@ ctcB200Status ctc_b200_error_counts(const int *hyp_ids, int hyp_pitch, const int
 
 /* number of kernel launches the last ctc_b200_compute on this thread enqueued (bench.py's gpu_launches claim) */
 int ctc_b200_last_launch_count(void);
+/* bytes the last ctc_b200_compute_host on this thread actually moved over the bus, host->device and device->host
+   (frames past a slice's longest utterance are neither uploaded nor downloaded); bench.py's e2e byte counts */
+void ctc_b200_last_copy_bytes(unsigned long long *h2d, unsigned long long *d2h);
 
 #ifdef __cplusplus
 }

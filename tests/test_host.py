@@ -44,6 +44,7 @@ def test_workspace_query_is_shape_only(b200):
     assert lib.ctc_b200_workspace_size(10, 0, 29, 5, None, ctypes.byref(n)) == 2          # B < 1
     assert lib.ctc_b200_workspace_size(10, 1, 1, 5, None, ctypes.byref(n)) == 2           # C < 2
     assert lib.ctc_b200_workspace_size(10, 1, 29, 5, None, None) == 2
+    assert lib.ctc_b200_workspace_size(0, 16, 29, 5, None, ctypes.byref(n)) == 0          # T == 0 is a valid shape
 
 
 def test_compute_rejects_bad_arguments_before_touching_the_device(b200):
@@ -95,6 +96,33 @@ def test_conv_out_lens_formula(b200):
     t_in = torch.tensor([1, 2, 3, 100, 101, 3001], dtype=torch.int32)
     assert b200.packing.conv_out_lens(t_in).tolist() == [(int(t) - 1) // 2 + 1 for t in t_in]
     assert b200.packing.input_sizes_from_percentages(torch.tensor([1.0, 0.5]), 301).tolist() == [301, 150]
+
+
+def test_conv_out_lens_matches_the_reference_get_seq_lens(b200):
+    # row a7 pinned to the reference itself: DeepSpeech.get_seq_lens (/root/reference/model.py:382-393) imports in
+    # the build container (pure torch); it only walks self.conv, so a small model is enough
+    if not os.path.exists("/root/reference/model.py"):
+        pytest.skip("reference tree only exists in the build container")
+    import importlib.util
+    import sys
+
+    spec = importlib.util.spec_from_file_location("ref_model", "/root/reference/model.py")
+    ref = importlib.util.module_from_spec(spec)
+    sys.path.insert(0, "/root/reference")
+    try:
+        spec.loader.exec_module(ref)
+    finally:
+        sys.path.remove("/root/reference")
+    model = ref.DeepSpeech(rnn_type="gru", labels="".join(b200.ALPHABET), rnn_hidden_size=16, nb_layers=1)
+    t_in = torch.arange(1, 4001, dtype=torch.int32)
+    want = model.get_seq_lens(t_in)
+    assert torch.equal(b200.packing.conv_out_lens(t_in), want.to(torch.int32))
+    assert torch.equal(b200.packing.conv_out_lens(t_in, true_division=True), want.to(torch.int32))
+    # a stack with two strided time axes: the reference's expression as torch evaluates it today (true division)
+    model.conv.seq_module[3] = torch.nn.Conv2d(32, 32, kernel_size=(21, 11), stride=(2, 2), padding=(10, 5))
+    want2 = model.get_seq_lens(t_in)
+    got2 = b200.packing.conv_out_lens(t_in, convs=((11, 2, 5, 1), (11, 2, 5, 1)), true_division=True)
+    assert torch.equal(got2, want2.to(torch.int32))
 
 
 def test_length_bucketed_shards(b200):

@@ -190,7 +190,7 @@ def test_mid_sized_alphabets(oracle, b200, C):
     T = 36
     g = torch.Generator().manual_seed(C)
     acts = torch.randn(T, 5, C, generator=g) * 2.0
-    targets = [[C - 1, C - 1, 7, 7, 9, C - 1, 3, 3], [], [40] * 20, [1, 2, 3, 1, 2, 3, 1, 2, 3], [C - 2]]
+    targets = [[C - 1, C - 1, 7, 7, 9, C - 1, 3, 3], [], [C // 2] * 20, [1, 2, 3, 1, 2, 3, 1, 2, 3], [C - 2]]
     act_lens = torch.tensor([36, 12, 36, 9, 1], dtype=torch.int32)  # utt2: 20 + 19 repeats > 36 -> infeasible
     labels, ll = b200.pack_targets(targets)
     d = {"acts": acts, "labels": labels, "act_lens": act_lens, "label_lens": ll}

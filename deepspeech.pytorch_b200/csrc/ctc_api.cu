@@ -84,6 +84,12 @@ int env_int(const char *name, int dflt) {
     return (v && *v) ? atoi(v) : dflt;
 }
 
+// CTC_B200_ENGINE=1 selects the first form of the recursion kernel (kept for A/B measurements)
+int engine_version() {
+    static const int v = env_int("CTC_B200_ENGINE", 2);
+    return v;
+}
+
 struct Plan {
     int nwl;   // lattice warps per CTA
     int R;     // rows per checkpoint block (16 or 8)
@@ -301,6 +307,9 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         e = cudaFuncSetAttribute(ctc_engine_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_engine2_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ctc_grad_kernel<kK, CP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
@@ -321,7 +330,10 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
     return launch_sliced(
         p, pl, st, do_engine, do_grad, launches, costs_ready, loss_sum,
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
-            ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+            if (engine_version() == 1)
+                ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+            else
+                ctc_engine2_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
         },
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
@@ -360,6 +372,9 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ctc_engine_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_engine2_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ctc_grad_kernel<kK, CP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -402,7 +417,10 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         rows_at(pk, nb, s);
     };
     auto eng = [&](const CtcParams &pk, int nb, cudaStream_t s) {
-        ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+        if (engine_version() == 1)
+            ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+        else
+            ctc_engine2_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
         ++*launches;
     };
     auto grd = [&](const CtcParams &pk, int nb, cudaStream_t s) {

@@ -765,6 +765,427 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
     }
 }
 
+// ================================================================================================ engine, second form
+// Same recursion, same arithmetic and the same shared-memory / checkpoint protocol as ctc_engine_kernel above, with
+// the per-GROUP overhead cut (ncu on the first form, headline shape: of ~1650 clk per group of 8 steps only ~780 were
+// the steps; ~340 went into a prologue that re-derived direction, ring slots and addresses, ~260 into renormalise +
+// settle + send, ~220 into checkpoint + loop bookkeeping):
+//   * one instantiation per DIRECTION (no direction tests, no re-derived block indices inside the loop);
+//   * boundary slots laid out planar and indexed by group parity + step, so every slot address of a group is one base
+//     register plus an immediate;
+//   * threads without an inflow neighbour (state 0's thread for alpha, the last warp's lane 31 for beta) carry
+//     f = 0 instead of having their inflow zeroed every step; alpha starts from a virtual alpha_{-1}(0) = 1;
+//   * renormalise + settle in ONE pass with 3 dependent warp collectives on the fast path (ballot -> indexed shuffle
+//     -> vote) instead of 5: the exponent a dead thread adopts and the exponent of its inflow neighbour are the same
+//     number (the nearest live thread on the inflow side), so one shuffle serves both; the boundary mantissa is
+//     shuffled while the exponents settle; the lift loop is entered only when some lane needs it;
+//   * the first emission row of the NEXT group is fetched before the group barrier (the producer runs one more tile
+//     ahead), so a group no longer starts with an exposed shared-memory latency.
+struct SlotRing {
+    double m0[kRing];
+    double m1[kRing];
+    int E[kRing];
+};
+static_assert(sizeof(SlotRing) <= sizeof(Slot) * kRing, "the v2 rings live in the v1 slot area");
+constexpr int kRingM1 = (int)offsetof(SlotRing, m1), kRingE = (int)offsetof(SlotRing, E);
+
+// The slot rings are addressed through 32-bit shared-window addresses that the compiler cannot see through (it
+// otherwise re-derives them from %tid / the CTA's shared window in EVERY step: measured, ~18 instructions per access)
+// and accessed with predicated instructions, so the one lane per warp that talks to the neighbouring warp costs the
+// other 31 no branch.
+__device__ __forceinline__ uint32_t opaque_u32(uint32_t x) {
+    asm volatile("" : "+r"(x));
+    return x;
+}
+__device__ __forceinline__ void sts_f64_if(uint32_t addr, double v, bool pred) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p st.shared.f64 [%0], %1;\n\t}" ::"r"(addr), "d"(v),
+                 "r"((int)pred));
+}
+__device__ __forceinline__ void sts_b32_if(uint32_t addr, int v, bool pred) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p st.shared.b32 [%0], %1;\n\t}" ::"r"(addr), "r"(v),
+                 "r"((int)pred));
+}
+// v = pred ? *addr : v
+__device__ __forceinline__ void lds_f64_if(double &v, uint32_t addr, bool pred) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p ld.shared.f64 %0, [%1];\n\t}" : "+d"(v) : "r"(addr),
+                 "r"((int)pred));
+}
+__device__ __forceinline__ int lds_b32(uint32_t addr) {
+    int v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+// thread-local renormalisation + exponent settlement (see renorm / settle in ctc_device.cuh for the rules).
+// bnd0 / bnd1: the mantissas the inflow-side neighbour needs next (alpha: a[K-1]; beta: a[0], a[1]); returned in
+// pr0 / pr1 as received from the in-warp neighbour (the caller overrides the warp-edge lane from the slot ring).
+template <int K, bool UP>
+__device__ __forceinline__ double renorm_settle(Cells<K> &c, int E_edge, int lane, double &pr0, double &pr1) {
+    int h[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) h[k] = __double2hiint(c.a[k]);
+#pragma unroll
+    for (int w = 1; w < K; w <<= 1)
+#pragma unroll
+        for (int k = 0; k + w < K; k += 2 * w) h[k] = max(h[k], h[k + w]);
+    const int ex = h[0] >> 20;
+    const bool live = ex != 0;
+    const unsigned lm = __ballot_sync(kFull, live);
+    const double sc = live ? pow2i(1023 - ex) : 0.0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) c.a[k] *= sc;
+    int E = live ? c.E - (1023 - ex) : kDeadE;
+    if (UP) {
+        pr0 = __shfl_up_sync(kFull, c.a[K - 1], 1);
+    } else {
+        pr0 = __shfl_down_sync(kFull, c.a[0], 1);
+        pr1 = __shfl_down_sync(kFull, c.a[1], 1);
+    }
+    // nearest live thread strictly on the inflow side: its exponent is what a dead thread adopts AND what the inflow
+    // neighbour of this thread ends up with (if that neighbour is dead, it adopts exactly this one)
+    const unsigned side = UP ? (lm & ((1u << lane) - 1u)) : (lane == 31 ? 0u : (lm & ~((2u << lane) - 1u)));
+    const int src = side ? (UP ? 31 - __clz(side) : __ffs(side) - 1) : lane;
+    int En = __shfl_sync(kFull, E, src);
+    if (!side) En = E_edge;
+    if (!live) E = En;
+    bool lifted = En != kDeadE && En - E > kLift;
+    if (__any_sync(kFull, lifted)) {
+        // rare: some thread sits more than 2^kLift below its inflow neighbour -- the general loop of settle()
+        do {
+            En = UP ? __shfl_up_sync(kFull, E, 1) : __shfl_down_sync(kFull, E, 1);
+            if (UP ? (lane == 0) : (lane == 31)) En = E_edge;
+            lifted = false;
+            if (En != kDeadE && En - E > kLift) {
+                const double s = pow2i(E - En);
+#pragma unroll
+                for (int k = 0; k < K; ++k) c.a[k] *= s;
+                E = En;
+                lifted = true;
+            }
+        } while (__any_sync(kFull, lifted));
+        if (UP) {
+            pr0 = __shfl_up_sync(kFull, c.a[K - 1], 1);
+        } else {
+            pr0 = __shfl_down_sync(kFull, c.a[0], 1);
+            pr1 = __shfl_down_sync(kFull, c.a[1], 1);
+        }
+    }
+    c.E = E;
+    return (En == kDeadE) ? 0.0 : pow2i(En - E);
+}
+
+// 8 (FULL) or nr < 8 steps of the alpha recursion; y holds the emission values of the group's first row on entry.
+// hb = slot-ring base of this group (0 or 8); send: lane 31 of a warp with an upper neighbour; recv: lane 0 of a warp
+// with a lower neighbour.
+template <int K, int CP, bool FULL>
+__device__ __forceinline__ void alpha_steps(Cells<K> &c, double &pr0, const double f, YRow<K> y, const unsigned *yt,
+                                            int nr, int blank, const int (&idx)[K / 2], const double (&skipA)[K / 2],
+                                            bool send, bool recv, uint32_t mine_m0, uint32_t in_m0) {
+#pragma unroll
+    for (int r = 0; r < kGroup; ++r) {
+        if (FULL || r < nr) {
+            const bool last = FULL ? (r == kGroup - 1) : (r == nr - 1);
+            YRow<K> yn;
+            load_y<K, CP>(yn, yt, FULL ? min(r + 1, kGroup - 1) : min(r + 1, nr - 1), blank, idx);
+            const double p1 = pr0 * f;
+            const double top = alpha_top<K>(c.a, y, skipA);
+            double sh = 0.0;
+            if (!last) {
+                sh = __shfl_up_sync(kFull, top, 1);
+                sts_f64_if(mine_m0 + 8 * r, top, send);
+            }
+            alpha_rest<K>(c.a, top, p1, y, skipA);
+            if (!last) {
+                lds_f64_if(sh, in_m0 + 8 * r, recv);
+                pr0 = sh;
+            }
+            y = yn;
+        }
+    }
+}
+
+template <int K, int CP, bool FULL>
+__device__ __forceinline__ void beta_steps(Cells<K> &c, double &pr0, double &pr1, const double f, YRow<K> y,
+                                           const unsigned *yt, int nr, int blank, const int (&idx)[K / 2],
+                                           const double (&skipB)[K / 2], bool send, bool recv, uint32_t mine_m0,
+                                           uint32_t in_m0) {
+#pragma unroll
+    for (int rr = 0; rr < kGroup; ++rr) {
+        const int r = (FULL ? kGroup : nr) - 1 - rr;
+        if (FULL || r >= 0) {
+            const bool last = (r == 0);
+            YRow<K> yn;
+            load_y<K, CP>(yn, yt, max(r - 1, 0), blank, idx);
+            const double n1 = pr0 * f, n2 = pr1 * f;
+            double b0, b1, s0, s1v;
+            beta_bottom<K>(c.a, y, skipB, b0, b1, s0, s1v);
+            double sh0 = 0.0, sh1 = 0.0;
+            if (!last) {
+                sh0 = __shfl_down_sync(kFull, s0, 1);
+                sh1 = __shfl_down_sync(kFull, s1v, 1);
+                sts_f64_if(mine_m0 + 8 * r, s0, send);
+                sts_f64_if(mine_m0 + kRingM1 + 8 * r, s1v, send);
+            }
+            double bb[K];
+            beta_rest<K>(c.a, bb, b0, b1, s0, s1v, n1, n2, y, skipB);
+            if (!last) {
+                lds_f64_if(sh0, in_m0 + 8 * r, recv);
+                lds_f64_if(sh1, in_m0 + kRingM1 + 8 * r, recv);
+                pr0 = sh0;
+                pr1 = sh1;
+            }
+            y = yn;
+        }
+    }
+}
+
+// the lattice warps of one direction
+template <int K, int CP, bool FWD>
+__device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int warp, int lane, int nwa, int nbar, int Tb,
+                                               int S, unsigned *ytile, int NS, SlotRing *rings, double *pm, int *pe) {
+    constexpr int Cp = CP;
+    const int NT = p.nwl * 32;
+    const int thread = warp * 32 + lane;  // lattice thread index; owns states [thread*K, thread*K+K)
+    const int ngroups = (Tb + kGroup - 1) / kGroup;
+    const int nsuper = ngroups + nwa - 1;
+    int idx[K / 2], lab_i[K / 2];
+    double skipA[K / 2], skipB[K / 2];
+    decode_tlab<K>(p.tlab[(size_t)b * NT + thread], idx, skipA, skipB, lab_i, false, 0);
+    (void)lab_i;
+    const int blank = p.bpos;
+
+    Cells<K> c;
+#pragma unroll
+    for (int k = 0; k < K; ++k) c.a[k] = 0.0;
+    c.E = 0;
+    double pr0 = 0.0, pr1 = 0.0;
+    const int q = FWD ? warp : (nwa - 1 - warp);  // position in the systolic pipeline
+    const bool has_lower = warp > 0, has_upper = warp + 1 < nwa;
+    // the warp-edge lane that talks to the neighbouring warp through the slot rings
+    // (kept opaque: the compiler otherwise re-derives them from %tid inside the loop)
+    const bool send = opaque_u32(FWD ? (lane == 31 && has_upper) : (lane == 0 && has_lower)) != 0;
+    const bool recv = opaque_u32(FWD ? (lane == 0 && has_lower) : (lane == 31 && has_upper)) != 0;
+    const bool edge = FWD ? (lane == 0) : (lane == 31);
+    // shared-window addresses of this warp's ring and of the inflow-side neighbour's (only `recv` lanes / warps with
+    // such a neighbour ever dereference the latter)
+    const uint32_t mine = opaque_u32(smem_u32(rings + warp));
+    const uint32_t in = opaque_u32(smem_u32(rings + (FWD ? warp - 1 : warp + 1)));
+    const bool has_in = FWD ? has_lower : has_upper;
+    // everything starts in scale 2^0; a thread without an inflow neighbour has f = 0 for good
+    double f = (FWD ? (thread == 0) : (edge && !has_upper)) ? 0.0 : 1.0;
+    if (FWD) {
+        if (thread == 0) c.a[0] = 1.0;  // virtual alpha_{-1}: all mass in state 0
+    } else {
+        const int s1 = S - 1;  // virtual beta_T: 1 at state S-1
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+            if (thread * K + k == s1) c.a[k] = 1.0;
+        pr0 = __shfl_down_sync(kFull, c.a[0], 1);
+        pr1 = __shfl_down_sync(kFull, c.a[1], 1);
+        if (lane == 31) {
+            pr0 = ((thread + 1) * K == s1) ? 1.0 : 0.0;  // S-1 is state 0 of the next thread
+            pr1 = 0.0;
+        }
+    }
+    named_bar_sync(1, nbar);
+    for (int i = 0; i < q; ++i) named_bar_sync(1, nbar);
+
+    int st = 0;  // ring slot of this warp's current emission tile
+    const unsigned *yt = ytile;
+    const int ntail = Tb - (ngroups - 1) * kGroup;  // rows of the ragged last group (1..8)
+    int hb = FWD ? 0 : (((ngroups - 1) * kGroup) & (kRing - 1));  // slot-ring base of the current group: t0 & 8
+    // checkpoints: alpha after row t0+7 -> block G+1 ; beta_{t0} -> block G-1 (see ctc_engine_kernel)
+    int *ck = (FWD ? p.ckA : p.ckB) + (size_t)b * p.nblk * NT * K;
+    int *ckE = (FWD ? p.ckAE : p.ckBE) + (size_t)b * p.nblk * NT;
+    const int cb0 = FWD ? 1 : ngroups - 2;
+    int4 *ckp = reinterpret_cast<int4 *>(ck + ((ptrdiff_t)cb0 * NT + warp * 32) * K) + lane;
+    int *ckEp = ckE + (ptrdiff_t)cb0 * NT + thread;
+    const ptrdiff_t ckstep = (FWD ? 1 : -1) * (ptrdiff_t)NT * (K / 4), ckEstep = (FWD ? 1 : -1) * (ptrdiff_t)NT;
+    const bool want_ck = !p.score_only;
+
+    // emission values of the first row this direction visits
+    YRow<K> y;
+    {
+        const int nr0 = FWD ? (ngroups == 1 ? ntail : kGroup) : ntail;  // rows of the first group processed
+        load_y<K, CP>(y, yt, FWD ? 0 : nr0 - 1, blank, idx);
+    }
+    for (int j = 0; j < ngroups; ++j) {
+        const bool tail = FWD ? (j == ngroups - 1) : (j == 0);
+        const int nr = tail ? ntail : kGroup;
+        const uint32_t mg = mine + 8 * hb, ig = in + 8 * hb;  // m0 slots of this group's rows
+        if (FWD) {
+            if (nr == kGroup)
+                alpha_steps<K, CP, true>(c, pr0, f, y, yt, kGroup, blank, idx, skipA, send, recv, mg, ig);
+            else
+                alpha_steps<K, CP, false>(c, pr0, f, y, yt, nr, blank, idx, skipA, send, recv, mg, ig);
+        } else {
+            if (nr == kGroup)
+                beta_steps<K, CP, true>(c, pr0, pr1, f, y, yt, kGroup, blank, idx, skipB, send, recv, mg, ig);
+            else
+                beta_steps<K, CP, false>(c, pr0, pr1, f, y, yt, nr, blank, idx, skipB, send, recv, mg, ig);
+        }
+        // ---- group boundary: slot index of the row the boundary values belong to (alpha: last row; beta: first)
+        const int tl = hb + (FWD ? nr - 1 : 0);
+        // settled exponent of the neighbouring warp's boundary thread (that warp ran this group a super-step ago);
+        // every lane may need it: a lane whose inflow side holds no live thread inside the warp adopts it
+        const int E_edge = has_in ? lds_b32(in + kRingE + 4 * tl) : kDeadE;
+        f = renorm_settle<K, FWD>(c, E_edge, lane, pr0, pr1);
+        if (FWD) {
+            sts_f64_if(mine + 8 * tl, c.a[K - 1], send);
+            lds_f64_if(pr0, in + 8 * tl, recv);
+        } else {
+            sts_f64_if(mine + 8 * tl, c.a[0], send);
+            sts_f64_if(mine + kRingM1 + 8 * tl, c.a[1], send);
+            lds_f64_if(pr0, in + 8 * tl, recv);
+            lds_f64_if(pr1, in + kRingM1 + 8 * tl, recv);
+        }
+        sts_b32_if(mine + kRingE + 4 * tl, c.E, send);
+        if (j < ngroups - 1) {
+            if (want_ck) {
+#pragma unroll
+                for (int k = 0; k < K; k += 4)
+                    ckp[(k / 4) * 32] = make_int4(hi_round(c.a[k]), hi_round(c.a[k + 1]), hi_round(c.a[k + 2]),
+                                                  hi_round(c.a[k + 3]));
+                *ckEp = c.E;
+            }
+            ckp += ckstep;
+            ckEp += ckEstep;
+            // next tile: its first row is fetched here, before the barrier (the producer guarantees tile j + 1 of
+            // this warp has landed: it waits one tile further ahead than the lattice needs)
+            yt += kGroup * 2 * Cp;
+            if (++st == NS) { st = 0; yt = ytile; }
+#ifndef CTC_V2_NOPREFETCH
+            load_y<K, CP>(y, yt, FWD ? 0 : kGroup - 1, blank, idx);
+#endif
+            hb ^= kGroup;
+        } else if (FWD) {
+            // ---- P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2): the owning threads publish (mantissa, exponent)
+            const int s1 = S - 1, s2 = S - 2;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                if (thread * K + k == s1) { pm[0] = c.a[k]; pe[0] = c.E; }
+                if (thread * K + k == s2) { pm[1] = c.a[k]; pe[1] = c.E; }
+            }
+        }
+        named_bar_sync(1, nbar);
+#ifdef CTC_V2_NOPREFETCH
+        if (j < ngroups - 1) load_y<K, CP>(y, yt, FWD ? 0 : kGroup - 1, blank, idx);
+#endif
+    }
+    for (int i = q + ngroups; i < nsuper; ++i) named_bar_sync(1, nbar);
+
+    if (FWD && thread == 0) {
+        double m = pm[0];
+        int e = pe[0];
+        if (S > 1) {
+            const int e2 = pe[1];
+            const int em = max(e, e2);
+            m = pm[0] * pow2i(e - em) + pm[1] * pow2i(e2 - em);
+            e = em;
+        }
+        const int ex = expo_field(m);
+        const bool isnan_p = m != m;  // a non-finite emission row reached the lattice: cost and gradient are NaN
+        const bool ok = ex != 0 && ex != 2047 && e > kDeadE / 2;
+        if (ok) {
+            m *= pow2i(1023 - ex);
+            e += ex - 1023;
+        }
+        p.feas[b] = ok || isnan_p;
+        p.Pm[b] = (ok || isnan_p) ? m : 1.0;
+        p.Pe[b] = ok ? e : 0;
+        const double cost = -(log(m) + (double)e * 0.69314718055994530942);
+        p.costs[b] = isnan_p ? __int_as_float(0x7fc00000) : (ok ? (float)cost : (p.zero_infinity ? 0.f : INFINITY));
+    }
+}
+
+template <int K, int CP>
+__global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine2_kernel(const CtcParams p) {
+    static_assert(K == 8, "label-table entries hold 4 labels = 8 states");
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int bi = p.slice0 + (p.score_only ? blockIdx.x : (blockIdx.x >> 1));
+    const int b = p.bord ? p.bord[bi] : bi;
+    const bool fwd = p.score_only ? true : !(blockIdx.x & 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nwl = p.nwl;
+    constexpr int Cp = CP;
+    const EngineSmem lay = engine_smem(Cp, nwl);
+    const int NS = lay.nstage;
+    unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
+    uint64_t *y_full = reinterpret_cast<uint64_t *>(smem + lay.bars);
+    SlotRing *rings = reinterpret_cast<SlotRing *>(smem + lay.slots);
+    double *pm = reinterpret_cast<double *>(smem + lay.misc);  // [2]
+    int *pe = reinterpret_cast<int *>(smem + lay.misc + 16);   // [2]
+
+    const int Tb = min(max(p.act_lens[b], 0), p.T);
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
+    const int S = 2 * L + 1;
+    const int nwa = min(nwl, (S + 32 * K - 1) / (32 * K));  // lattice warps this utterance needs
+
+    if (Tb == 0) {  // nothing to recurse over
+        if (fwd && tid == 0) {
+            const bool ok = (L == 0);
+            p.feas[b] = ok;
+            p.Pm[b] = 1.0;
+            p.Pe[b] = 0;
+            p.costs[b] = ok ? 0.f : (p.zero_infinity ? 0.f : INFINITY);
+        }
+        return;
+    }
+    if (warp >= nwa && warp != nwl) return;  // lattice warps beyond this utterance's S
+    const int ngroups = (Tb + kGroup - 1) / kGroup;
+    const int nsuper = ngroups + nwa - 1;
+    const int nbar = (nwa + 1) * 32;
+
+    if (warp == nwl) {
+        // =========================================================== producer warp: TMA emission-tile prefetch
+        // (as in ctc_engine_kernel, but the tile the lattice may touch is waited for one super-step EARLIER: lattice
+        // warps fetch the first row of their next tile before the group barrier)
+        if (lane == 0) {
+            for (int i = 0; i < NS; ++i) mbar_init(&y_full[i], 1);
+            fence_mbar_init();
+        }
+        __syncwarp();
+        const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
+        const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
+        int ist = 0;
+        auto issue = [&](int j) {
+            const int st = ist;
+            ist = (ist + 1 == NS) ? 0 : ist + 1;
+            if (j < ngroups && lane == 0) {
+                const int G = fwd ? j : (ngroups - 1 - j);
+                const int t0 = G * kGroup;
+                const int nr = min(kGroup, Tb - t0);
+                mbar_arrive_expect_tx(&y_full[st], rowbytes * nr);
+                tma_bulk_g2s(ytile + (size_t)(st * kGroup) * 2 * Cp, ybase + (size_t)t0 * 2 * Cp, rowbytes * nr,
+                             &y_full[st]);
+            }
+        };
+        int wst = 0, wph = 0, nwaited = 0;
+        auto wait_tile = [&]() {
+            if (nwaited < ngroups) {
+                mbar_wait(&y_full[wst], wph);
+                if (++wst == NS) { wst = 0; wph ^= 1; }
+                ++nwaited;
+            }
+        };
+        for (int j = 0; j <= kLookAhead; ++j) issue(j);
+        wait_tile();  // tile 0
+        wait_tile();  // tile 1: its first row is read during super-step 0
+        named_bar_sync(1, nbar);
+        for (int i = 0; i < nsuper; ++i) {
+            fence_proxy_async();
+            issue(i + kLookAhead + 1);
+            wait_tile();  // tile i + 2
+            named_bar_sync(1, nbar);
+        }
+        return;
+    }
+    if (fwd)
+        engine_lattice<K, CP, true>(p, b, warp, lane, nwa, nbar, Tb, S, ytile, NS, rings, pm, pe);
+    else
+        engine_lattice<K, CP, false>(p, b, warp, lane, nwa, nbar, Tb, S, ytile, NS, rings, pm, pe);
+}
+
 // ================================================================================================ grad
 // One CTA per (utterance, every nsplit-th group of 8 time steps).  Warp q owns the 224 lattice states
 // [224q, 224q+224) (28 core threads) and recomputes a HALO of 16 states (2 threads) on either side, which is exactly

@@ -56,6 +56,9 @@ int main(int argc, char **argv) {
     { int resident = (int)(227 * 1024 / s_grad); if (resident < 1) resident = 1; p.nsplit = (2 * 148 * resident + B - 1) / B; if (p.nsplit > p.nblk) p.nsplit = p.nblk; if (argc > 5) p.nsplit = atoi(argv[5]); }
     CK(cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     CK(cudaFuncSetAttribute(ctc_engine_kernel<kK, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    CK(cudaFuncSetAttribute(ctc_engine2_kernel<kK, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    const int engv = getenv("ENGINE") ? atoi(getenv("ENGINE")) : 2;
+    printf("engine form %d\n", engv);
 #if KK == 8
     CK(cudaFuncSetAttribute(ctc_grad_kernel<kK, 32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
 #endif
@@ -70,7 +73,8 @@ int main(int argc, char **argv) {
         cudaEventRecord(e[0]);
         ctc_prep_kernel<<<nrb + B, kPrepRows, s_prep>>>(p);
         cudaEventRecord(e[1]);
-        ctc_engine_kernel<kK, 32><<<2 * B, (p.nwl + 1) * 32, s_eng>>>(p);
+        if (engv == 1) ctc_engine_kernel<kK, 32><<<2 * B, (p.nwl + 1) * 32, s_eng>>>(p);
+        else ctc_engine2_kernel<kK, 32><<<2 * B, (p.nwl + 1) * 32, s_eng>>>(p);
         cudaEventRecord(e[2]);
         if (getenv("SCORE_ONLY")) { CtcParams q = p; q.score_only = 1; cudaEventRecord(e[1]); ctc_engine_kernel<kK, 32><<<B, (p.nwl + 1) * 32, s_eng>>>(q); cudaEventRecord(e[2]); }
 #if KK == 8

@@ -108,6 +108,9 @@ struct Plan {
     size_t smem_engine_req;  // dynamic shared memory REQUESTED for an engine CTA (>= smem_engine, see make_plan)
     int numax;   // reduction units per utterance (small alphabets)
     size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_tlab, o_coff, o_labels, o_llen, o_alen;
+    size_t o_Pm2, o_Pe2;
+    int cluster;           // 1: engines run as 2-CTA clusters (more than 4 lattice warps, see ctc_engine2c_kernel)
+    size_t smem_engine_c;  // dynamic shared memory of one CTA of such a cluster
     size_t total;
 };
 
@@ -147,6 +150,10 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         pl->nsplit = ns;
     }
     if (pl->smem_engine > kSmemLimit || pl->smem_prep > kSmemLimit) return false;
+    // more than 4 lattice warps (L > 511): split them over the two CTAs of a cluster so that each has an SMSP to
+    // itself.  CTC_B200_CLUSTER=0 keeps everything in one CTA (A/B measurements).
+    pl->cluster = (nwl > 4 && engine_version() != 1 && env_int("CTC_B200_CLUSTER", 1) != 0) ? 1 : 0;
+    pl->smem_engine_c = engine_smem(pl->Cp, (nwl + 1) / 2).total;
     {
         // Length-bucket slices: up to kMaxSlices, each at least kMinSliceB utterances.  CTC_B200_SLICES overrides.
         int ns = B / kMinSliceB;
@@ -169,6 +176,8 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->o_ckB = o;    o = align256(o + ck);
     pl->o_ckAE = o;   o = align256(o + ckE);
     pl->o_ckBE = o;   o = align256(o + ckE);
+    pl->o_Pm2 = o;    o = align256(o + sizeof(double) * 2 * B);
+    pl->o_Pe2 = o;    o = align256(o + sizeof(int) * 2 * B);
     pl->o_Pm = o;     o = align256(o + sizeof(double) * B);
     pl->o_Pe = o;     o = align256(o + sizeof(int) * B);
     pl->o_feas = o;   o = align256(o + sizeof(int) * B);
@@ -310,6 +319,9 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         e = cudaFuncSetAttribute(ctc_engine2_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_engine2c_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ctc_grad_kernel<kK, CP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
@@ -332,6 +344,9 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
             if (engine_version() == 1)
                 ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+            else if (pl.cluster)
+                ctc_engine2c_kernel<kK, CP><<<2 * (pk.score_only ? nb : 2 * nb), ((pl.nwl + 1) / 2 + 1) * 32,
+                                              pl.smem_engine_c, s>>>(pk);
             else
                 ctc_engine2_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
@@ -377,6 +392,9 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         e = cudaFuncSetAttribute(ctc_engine2_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ctc_engine2c_kernel<kK, CP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)kSmemLimit);
+        if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ctc_grad_kernel<kK, CP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)kSmemLimit);
         if (e != cudaSuccess) return e;
@@ -419,6 +437,9 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
     auto eng = [&](const CtcParams &pk, int nb, cudaStream_t s) {
         if (engine_version() == 1)
             ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
+        else if (pl.cluster)
+            ctc_engine2c_kernel<kK, CP><<<2 * (pk.score_only ? nb : 2 * nb), ((pl.nwl + 1) / 2 + 1) * 32,
+                                          pl.smem_engine_c, s>>>(pk);
         else
             ctc_engine2_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
         ++*launches;
@@ -568,6 +589,8 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.ckB = reinterpret_cast<int *>(ws + pl.o_ckB);
     p.ckAE = reinterpret_cast<int *>(ws + pl.o_ckAE);
     p.ckBE = reinterpret_cast<int *>(ws + pl.o_ckBE);
+    p.Pm2 = reinterpret_cast<double *>(ws + pl.o_Pm2);
+    p.Pe2 = reinterpret_cast<int *>(ws + pl.o_Pe2);
     p.Pm = reinterpret_cast<double *>(ws + pl.o_Pm);
     p.Pe = reinterpret_cast<int *>(ws + pl.o_Pe);
     p.feas = reinterpret_cast<int *>(ws + pl.o_feas);

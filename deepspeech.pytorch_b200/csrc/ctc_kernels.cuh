@@ -51,6 +51,8 @@ struct CtcParams {
                         // of the fp32 softmax, clamped to >= 2^-126)
     int *ckA, *ckB;     // [B][nblk][nwl][K/4][32] int4: checkpoint mantissas as rounded high words (hi_round)
     int *ckAE, *ckBE;   // [B][nblk][nwl*32]   exponents
+    double *Pm2;        // [B][2] cluster engine: mantissas of alpha_{T-1}(S-1), alpha_{T-1}(S-2)
+    int *Pe2;           // [B][2] ... and their exponents
     double *Pm;         // [B] mantissa of p(l|x) in [1,2)
     int *Pe;            // [B] exponent of p(l|x)
     int *feas;          // [B] 1 = feasible
@@ -416,7 +418,7 @@ __device__ __forceinline__ void decode_tlab(const uint4 tl, int (&idx)[K / 2], d
 constexpr int kLookAhead = CTC_LOOKAHEAD;  // emission tiles in flight ahead of the first lattice warp
 
 struct EngineSmem {
-    size_t ytile, bars, slots, misc, total;
+    size_t ytile, bars, slots, misc, xlink, total;
     int nstage;
 };
 __host__ __device__ inline EngineSmem engine_smem(int Cp, int nwl) {
@@ -427,6 +429,8 @@ __host__ __device__ inline EngineSmem engine_smem(int Cp, int nwl) {
     s.bars = o;  o = align16(o + sizeof(uint64_t) * s.nstage);
     s.slots = o; o = align16(o + sizeof(Slot) * kMaxLatticeWarps * kRing);
     s.misc = o;  o = align16(o + 64);
+    // cluster form only: receive ring of the cross-CTA link (2 rings of 320 B) + 8 mbarriers
+    s.xlink = o; o = align16(o + 2 * 320 + 8 * sizeof(uint64_t));
     s.total = o;
     return s;
 }
@@ -816,6 +820,67 @@ __device__ __forceinline__ int lds_b32(uint32_t addr) {
     return v;
 }
 
+// ---- thread-block cluster / distributed shared memory (long label sequences: the lattice warps of one utterance and
+// direction are split over the two CTAs of a cluster, see ctc_engine2c_kernel)
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+// shared-window address of the SAME variable in CTA `rank` of the cluster (a shared::cluster address)
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void stc_f64_if(uint32_t caddr, double v, bool pred) {  // store into a peer CTA's smem
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p st.shared::cluster.f64 [%0], %1;\n\t}" ::"r"(caddr),
+                 "d"(v), "r"((int)pred));
+}
+__device__ __forceinline__ void stc_b32_if(uint32_t caddr, int v, bool pred) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p st.shared::cluster.b32 [%0], %1;\n\t}" ::"r"(caddr),
+                 "r"(v), "r"((int)pred));
+}
+// arrive on an mbarrier of a peer CTA; release at cluster scope: this thread's earlier DSMEM stores are visible to
+// whoever acquires the completed phase
+__device__ __forceinline__ void mbar_arrive_remote_if(uint32_t caddr, bool pred) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %1, 0;\n\t"
+                 "@p mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n\t}" ::"r"(caddr), "r"((int)pred)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t addr, uint32_t parity) {  // local mbarrier, cluster acquire
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+
+// Link between the two CTAs of a cluster (CL instantiations of engine_lattice only).  The boundary values that cross
+// from the last lattice warp of one CTA to the first of the other travel as DSMEM stores into a ring that lives in
+// the RECEIVER's shared memory (stores are fire-and-forget; a remote load would put ~200 clk on the receiver), four
+// groups deep (two SlotRings back to back), guarded by one "full" mbarrier per group slot in the receiver (the sender
+// arrives remotely, release.cluster, once a group's 8 step values + boundary mantissa + exponent are written) and one
+// "empty" mbarrier per slot in the sender (the receiver arrives remotely when it is done with the slot).
+constexpr int kXSlots = 4;
+struct EngLink {
+    int rank;           // this CTA's rank in the cluster
+    int gw0;            // global index of this CTA's lattice warp 0
+    int nwa_l;          // lattice warps of this CTA that this utterance needs
+    uint32_t xring;     // local shared address: SlotRing[2], the receive ring of this CTA
+    uint32_t xbars;     // local shared address: uint64 full[kXSlots], then empty[kXSlots]
+    double *Pm2;        // global [2]: mantissas of alpha_{T-1}(S-1), alpha_{T-1}(S-2)
+    int *Pe2;           // global [2]: their exponents
+};
+
 // thread-local renormalisation + exponent settlement (see renorm / settle in ctc_device.cuh for the rules).
 // bnd0 / bnd1: the mantissas the inflow-side neighbour needs next (alpha: a[K-1]; beta: a[0], a[1]); returned in
 // pr0 / pr1 as received from the in-warp neighbour (the caller overrides the warp-edge lane from the slot ring).
@@ -877,10 +942,11 @@ __device__ __forceinline__ double renorm_settle(Cells<K> &c, int E_edge, int lan
 // 8 (FULL) or nr < 8 steps of the alpha recursion; y holds the emission values of the group's first row on entry.
 // hb = slot-ring base of this group (0 or 8); send: lane 31 of a warp with an upper neighbour; recv: lane 0 of a warp
 // with a lower neighbour.
-template <int K, int CP, bool FULL>
+template <int K, int CP, bool FULL, bool CL>
 __device__ __forceinline__ void alpha_steps(Cells<K> &c, double &pr0, const double f, YRow<K> y, const unsigned *yt,
                                             int nr, int blank, const int (&idx)[K / 2], const double (&skipA)[K / 2],
-                                            bool send, bool recv, uint32_t mine_m0, uint32_t in_m0) {
+                                            bool send, bool recv, uint32_t mine_m0, uint32_t in_m0, bool sendx,
+                                            uint32_t peer_m0) {
 #pragma unroll
     for (int r = 0; r < kGroup; ++r) {
         if (FULL || r < nr) {
@@ -893,6 +959,7 @@ __device__ __forceinline__ void alpha_steps(Cells<K> &c, double &pr0, const doub
             if (!last) {
                 sh = __shfl_up_sync(kFull, top, 1);
                 sts_f64_if(mine_m0 + 8 * r, top, send);
+                if (CL) stc_f64_if(peer_m0 + 8 * r, top, sendx);
             }
             alpha_rest<K>(c.a, top, p1, y, skipA);
             if (!last) {
@@ -904,11 +971,11 @@ __device__ __forceinline__ void alpha_steps(Cells<K> &c, double &pr0, const doub
     }
 }
 
-template <int K, int CP, bool FULL>
+template <int K, int CP, bool FULL, bool CL>
 __device__ __forceinline__ void beta_steps(Cells<K> &c, double &pr0, double &pr1, const double f, YRow<K> y,
                                            const unsigned *yt, int nr, int blank, const int (&idx)[K / 2],
                                            const double (&skipB)[K / 2], bool send, bool recv, uint32_t mine_m0,
-                                           uint32_t in_m0) {
+                                           uint32_t in_m0, bool sendx, uint32_t peer_m0) {
 #pragma unroll
     for (int rr = 0; rr < kGroup; ++rr) {
         const int r = (FULL ? kGroup : nr) - 1 - rr;
@@ -925,6 +992,10 @@ __device__ __forceinline__ void beta_steps(Cells<K> &c, double &pr0, double &pr1
                 sh1 = __shfl_down_sync(kFull, s1v, 1);
                 sts_f64_if(mine_m0 + 8 * r, s0, send);
                 sts_f64_if(mine_m0 + kRingM1 + 8 * r, s1v, send);
+                if (CL) {
+                    stc_f64_if(peer_m0 + 8 * r, s0, sendx);
+                    stc_f64_if(peer_m0 + kRingM1 + 8 * r, s1v, sendx);
+                }
             }
             double bb[K];
             beta_rest<K>(c.a, bb, b0, b1, s0, s1v, n1, n2, y, skipB);
@@ -939,15 +1010,20 @@ __device__ __forceinline__ void beta_steps(Cells<K> &c, double &pr0, double &pr1
     }
 }
 
-// the lattice warps of one direction
-template <int K, int CP, bool FWD>
-__device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int warp, int lane, int nwa, int nbar, int Tb,
-                                               int S, unsigned *ytile, int NS, SlotRing *rings, double *pm, int *pe) {
+// the lattice warps of one direction.  CL: the utterance's lattice warps are split over the two CTAs of a cluster
+// (`warp` is then the CTA-local index, lk.gw0 + warp the global one); nwa = lattice warps the utterance needs in all.
+template <int K, int CP, bool FWD, bool CL>
+__device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int warp, int lane, int nwa, int Tb, int S,
+                                               unsigned *ytile, int NS, SlotRing *rings, double *pm, int *pe,
+                                               const EngLink &lk) {
     constexpr int Cp = CP;
     const int NT = p.nwl * 32;
-    const int thread = warp * 32 + lane;  // lattice thread index; owns states [thread*K, thread*K+K)
+    const int gw = CL ? lk.gw0 + warp : warp;      // global lattice warp
+    const int nwa_l = CL ? lk.nwa_l : nwa;         // lattice warps of this CTA
+    const int nbar = (nwa_l + 1) * 32;
+    const int thread = gw * 32 + lane;  // lattice thread index; owns states [thread*K, thread*K+K)
     const int ngroups = (Tb + kGroup - 1) / kGroup;
-    const int nsuper = ngroups + nwa - 1;
+    const int nsuper = ngroups + nwa_l - 1;
     int idx[K / 2], lab_i[K / 2];
     double skipA[K / 2], skipB[K / 2];
     decode_tlab<K>(p.tlab[(size_t)b * NT + thread], idx, skipA, skipB, lab_i, false, 0);
@@ -959,18 +1035,24 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
     for (int k = 0; k < K; ++k) c.a[k] = 0.0;
     c.E = 0;
     double pr0 = 0.0, pr1 = 0.0;
-    const int q = FWD ? warp : (nwa - 1 - warp);  // position in the systolic pipeline
-    const bool has_lower = warp > 0, has_upper = warp + 1 < nwa;
+    const int q = FWD ? warp : (nwa_l - 1 - warp);  // position in this CTA's systolic pipeline
+    const bool has_lower = gw > 0, has_upper = gw + 1 < nwa;
+    const bool has_in = FWD ? has_lower : has_upper, has_out = FWD ? has_upper : has_lower;
+    // does the inflow / outflow neighbour live in the peer CTA?
+    const bool in_x = CL && has_in && (FWD ? warp == 0 : warp == nwa_l - 1);
+    const bool out_x = CL && has_out && (FWD ? warp == nwa_l - 1 : warp == 0);
     // the warp-edge lane that talks to the neighbouring warp through the slot rings
     // (kept opaque: the compiler otherwise re-derives them from %tid inside the loop)
-    const bool send = opaque_u32(FWD ? (lane == 31 && has_upper) : (lane == 0 && has_lower)) != 0;
-    const bool recv = opaque_u32(FWD ? (lane == 0 && has_lower) : (lane == 31 && has_upper)) != 0;
-    const bool edge = FWD ? (lane == 0) : (lane == 31);
-    // shared-window addresses of this warp's ring and of the inflow-side neighbour's (only `recv` lanes / warps with
-    // such a neighbour ever dereference the latter)
+    const bool send_lane = FWD ? (lane == 31) : (lane == 0), recv_lane = FWD ? (lane == 0) : (lane == 31);
+    const bool send = opaque_u32(send_lane && has_out && !out_x) != 0;   // into this CTA's own ring
+    const bool sendx = CL && opaque_u32(send_lane && out_x) != 0;        // into the peer CTA's receive ring
+    const bool recv = opaque_u32(recv_lane && has_in) != 0;
+    const bool edge = recv_lane;
+    // shared-window addresses of this warp's ring and of the ring it reads (the inflow-side neighbour's, or this
+    // CTA's receive ring when that neighbour is in the peer CTA); only lanes / warps with such a neighbour use it
     const uint32_t mine = opaque_u32(smem_u32(rings + warp));
-    const uint32_t in = opaque_u32(smem_u32(rings + (FWD ? warp - 1 : warp + 1)));
-    const bool has_in = FWD ? has_lower : has_upper;
+    const uint32_t in_l = opaque_u32(in_x ? lk.xring : smem_u32(rings + (FWD ? warp - 1 : warp + 1)));
+    const uint32_t peer_ring = CL ? opaque_u32(mapa_u32(lk.xring, lk.rank ^ 1)) : 0u;
     // everything starts in scale 2^0; a thread without an inflow neighbour has f = 0 for good
     double f = (FWD ? (thread == 0) : (edge && !has_upper)) ? 0.0 : 1.0;
     if (FWD) {
@@ -993,12 +1075,11 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
     int st = 0;  // ring slot of this warp's current emission tile
     const unsigned *yt = ytile;
     const int ntail = Tb - (ngroups - 1) * kGroup;  // rows of the ragged last group (1..8)
-    int hb = FWD ? 0 : (((ngroups - 1) * kGroup) & (kRing - 1));  // slot-ring base of the current group: t0 & 8
     // checkpoints: alpha after row t0+7 -> block G+1 ; beta_{t0} -> block G-1 (see ctc_engine_kernel)
     int *ck = (FWD ? p.ckA : p.ckB) + (size_t)b * p.nblk * NT * K;
     int *ckE = (FWD ? p.ckAE : p.ckBE) + (size_t)b * p.nblk * NT;
     const int cb0 = FWD ? 1 : ngroups - 2;
-    int4 *ckp = reinterpret_cast<int4 *>(ck + ((ptrdiff_t)cb0 * NT + warp * 32) * K) + lane;
+    int4 *ckp = reinterpret_cast<int4 *>(ck + ((ptrdiff_t)cb0 * NT + gw * 32) * K) + lane;
     int *ckEp = ckE + (ptrdiff_t)cb0 * NT + thread;
     const ptrdiff_t ckstep = (FWD ? 1 : -1) * (ptrdiff_t)NT * (K / 4), ckEstep = (FWD ? 1 : -1) * (ptrdiff_t)NT;
     const bool want_ck = !p.score_only;
@@ -1012,34 +1093,56 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
     for (int j = 0; j < ngroups; ++j) {
         const bool tail = FWD ? (j == ngroups - 1) : (j == 0);
         const int nr = tail ? ntail : kGroup;
-        const uint32_t mg = mine + 8 * hb, ig = in + 8 * hb;  // m0 slots of this group's rows
+        // slots of this group's rows: the j-th group this direction processes uses half (j & 1) of a ring; the
+        // cross-CTA ring is two rings back to back, group j in ring (j >> 1) & 1
+        const int hb = (j & 1) * kGroup;
+        const uint32_t xo = (uint32_t)((j >> 1) & 1) * (uint32_t)sizeof(SlotRing);
+        const uint32_t mg = mine + 8 * hb;
+        const uint32_t ig = in_l + (in_x ? xo : 0u) + 8 * hb;
+        const uint32_t pg = CL ? peer_ring + xo + 8 * hb : 0u;
+        // (CL: that the peer's values for group j have landed in the receive ring, and that the peer is done with the
+        // slot this group's values go to, was established by this CTA's producer warp before the group barrier that
+        // started this super-step -- the lattice warps themselves never touch a cluster-scope operation)
         if (FWD) {
             if (nr == kGroup)
-                alpha_steps<K, CP, true>(c, pr0, f, y, yt, kGroup, blank, idx, skipA, send, recv, mg, ig);
+                alpha_steps<K, CP, true, CL>(c, pr0, f, y, yt, kGroup, blank, idx, skipA, send, recv, mg, ig, sendx, pg);
             else
-                alpha_steps<K, CP, false>(c, pr0, f, y, yt, nr, blank, idx, skipA, send, recv, mg, ig);
+                alpha_steps<K, CP, false, CL>(c, pr0, f, y, yt, nr, blank, idx, skipA, send, recv, mg, ig, sendx, pg);
         } else {
             if (nr == kGroup)
-                beta_steps<K, CP, true>(c, pr0, pr1, f, y, yt, kGroup, blank, idx, skipB, send, recv, mg, ig);
+                beta_steps<K, CP, true, CL>(c, pr0, pr1, f, y, yt, kGroup, blank, idx, skipB, send, recv, mg, ig, sendx,
+                                            pg);
             else
-                beta_steps<K, CP, false>(c, pr0, pr1, f, y, yt, nr, blank, idx, skipB, send, recv, mg, ig);
+                beta_steps<K, CP, false, CL>(c, pr0, pr1, f, y, yt, nr, blank, idx, skipB, send, recv, mg, ig, sendx,
+                                             pg);
         }
         // ---- group boundary: slot index of the row the boundary values belong to (alpha: last row; beta: first)
         const int tl = hb + (FWD ? nr - 1 : 0);
         // settled exponent of the neighbouring warp's boundary thread (that warp ran this group a super-step ago);
         // every lane may need it: a lane whose inflow side holds no live thread inside the warp adopts it
-        const int E_edge = has_in ? lds_b32(in + kRingE + 4 * tl) : kDeadE;
+        const uint32_t in_g = in_l + (in_x ? xo : 0u);
+        const int E_edge = has_in ? lds_b32(in_g + kRingE + 4 * tl) : kDeadE;
         f = renorm_settle<K, FWD>(c, E_edge, lane, pr0, pr1);
         if (FWD) {
             sts_f64_if(mine + 8 * tl, c.a[K - 1], send);
-            lds_f64_if(pr0, in + 8 * tl, recv);
+            lds_f64_if(pr0, in_g + 8 * tl, recv);
         } else {
             sts_f64_if(mine + 8 * tl, c.a[0], send);
             sts_f64_if(mine + kRingM1 + 8 * tl, c.a[1], send);
-            lds_f64_if(pr0, in + 8 * tl, recv);
-            lds_f64_if(pr1, in + kRingM1 + 8 * tl, recv);
+            lds_f64_if(pr0, in_g + 8 * tl, recv);
+            lds_f64_if(pr1, in_g + kRingM1 + 8 * tl, recv);
         }
         sts_b32_if(mine + kRingE + 4 * tl, c.E, send);
+        if (CL) {
+            const uint32_t pr = peer_ring + xo;
+            if (FWD) {
+                stc_f64_if(pr + 8 * tl, c.a[K - 1], sendx);
+            } else {
+                stc_f64_if(pr + 8 * tl, c.a[0], sendx);
+                stc_f64_if(pr + kRingM1 + 8 * tl, c.a[1], sendx);
+            }
+            stc_b32_if(pr + kRingE + 4 * tl, c.E, sendx);
+        }
         if (j < ngroups - 1) {
             if (want_ck) {
 #pragma unroll
@@ -1057,14 +1160,17 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
 #ifndef CTC_V2_NOPREFETCH
             load_y<K, CP>(y, yt, FWD ? 0 : kGroup - 1, blank, idx);
 #endif
-            hb ^= kGroup;
         } else if (FWD) {
             // ---- P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2): the owning threads publish (mantissa, exponent)
             const int s1 = S - 1, s2 = S - 2;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                if (thread * K + k == s1) { pm[0] = c.a[k]; pe[0] = c.E; }
-                if (thread * K + k == s2) { pm[1] = c.a[k]; pe[1] = c.E; }
+                if (thread * K + k == s1) {
+                    if (CL) { lk.Pm2[0] = c.a[k]; lk.Pe2[0] = c.E; } else { pm[0] = c.a[k]; pe[0] = c.E; }
+                }
+                if (thread * K + k == s2) {
+                    if (CL) { lk.Pm2[1] = c.a[k]; lk.Pe2[1] = c.E; } else { pm[1] = c.a[k]; pe[1] = c.E; }
+                }
             }
         }
         named_bar_sync(1, nbar);
@@ -1073,28 +1179,108 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
 #endif
     }
     for (int i = q + ngroups; i < nsuper; ++i) named_bar_sync(1, nbar);
+}
 
-    if (FWD && thread == 0) {
-        double m = pm[0];
-        int e = pe[0];
-        if (S > 1) {
-            const int e2 = pe[1];
-            const int em = max(e, e2);
-            m = pm[0] * pow2i(e - em) + pm[1] * pow2i(e2 - em);
-            e = em;
+// cost and p(l|x) of one utterance from the published (mantissa, exponent) pairs of alpha_{T-1}(S-1), alpha_{T-1}(S-2)
+__device__ __forceinline__ void engine_finish(const CtcParams &p, int b, int S, double m0, int e0, double m1, int e1) {
+    double m = m0;
+    int e = e0;
+    if (S > 1) {
+        const int em = max(e0, e1);
+        m = m0 * pow2i(e0 - em) + m1 * pow2i(e1 - em);
+        e = em;
+    }
+    const int ex = expo_field(m);
+    const bool isnan_p = m != m;  // a non-finite emission row reached the lattice: cost and gradient are NaN
+    const bool ok = ex != 0 && ex != 2047 && e > kDeadE / 2;
+    if (ok) {
+        m *= pow2i(1023 - ex);
+        e += ex - 1023;
+    }
+    p.feas[b] = ok || isnan_p;
+    p.Pm[b] = (ok || isnan_p) ? m : 1.0;
+    p.Pe[b] = ok ? e : 0;
+    const double cost = -(log(m) + (double)e * 0.69314718055994530942);
+    p.costs[b] = isnan_p ? __int_as_float(0x7fc00000) : (ok ? (float)cost : (p.zero_infinity ? 0.f : INFINITY));
+}
+
+// emission-tile producer warp of the second engine form (TMA bulk copies into a ring of NS tiles, kLookAhead + 1
+// tiles in flight; the tile the lattice may touch is waited for one super-step EARLIER than in ctc_engine_kernel:
+// lattice warps fetch the first row of their next tile before the group barrier).  nwa_l: lattice warps of this CTA.
+// CL (cluster form): the producer warp also performs every cluster-scope operation of the cross-CTA link, so that the
+// lattice warps only issue plain DSMEM stores / local loads.  xrecv: this CTA's first pipeline warp reads from the
+// peer (before the barrier that starts the super-step in which that warp runs group j the producer has seen the peer's
+// "full" arrival for group j, acquire.cluster; after the barrier that ends it, it returns the slot with a remote
+// "empty" arrival).  xsend: this CTA's last pipeline warp writes to the peer (before the barrier that starts group j
+// there, j >= 4, the producer has seen the peer's "empty" arrival for group j - 4; after the barrier that ends it, it
+// publishes the group with a remote "full" arrival, release.cluster -- the CTA barrier orders the lattice warp's
+// DSMEM stores before it, and release is cumulative).
+template <int CP, bool CL>
+__device__ __forceinline__ void engine_producer(const CtcParams &p, int b, bool fwd, int lane, int nwa_l, int Tb,
+                                                unsigned *ytile, uint64_t *y_full, int NS, const EngLink &lk,
+                                                bool xrecv, bool xsend) {
+    constexpr int Cp = CP;
+    const int ngroups = (Tb + kGroup - 1) / kGroup;
+    const int nsuper = ngroups + nwa_l - 1;
+    const int nbar = (nwa_l + 1) * 32;
+    const uint32_t full_l = CL ? lk.xbars : 0u, empty_l = CL ? lk.xbars + 8 * kXSlots : 0u;
+    const uint32_t full_p = CL ? mapa_u32(full_l, lk.rank ^ 1) : 0u, empty_p = CL ? mapa_u32(empty_l, lk.rank ^ 1) : 0u;
+    // group the link-side lattice warp runs in super-step i: the first pipeline warp (receiver) runs group i, the
+    // last one (sender) group i - (nwa_l - 1)
+    auto link_before = [&](int inext) {  // ahead of the barrier that STARTS super-step inext
+        if (!CL) return;
+        if (xrecv && inext < ngroups)
+            mbar_wait_cluster(full_l + 8 * (inext & (kXSlots - 1)), (uint32_t)(inext / kXSlots) & 1u);
+        const int js = inext - (nwa_l - 1);
+        if (xsend && js >= kXSlots && js < ngroups)
+            mbar_wait_cluster(empty_l + 8 * (js & (kXSlots - 1)), (uint32_t)(js / kXSlots - 1) & 1u);
+    };
+    auto link_after = [&](int idone) {  // behind the barrier that ENDS super-step idone
+        if (!CL) return;
+        if (xrecv && idone < ngroups) mbar_arrive_remote_if(empty_p + 8 * (idone & (kXSlots - 1)), lane == 0);
+        const int js = idone - (nwa_l - 1);
+        if (xsend && js >= 0 && js < ngroups) mbar_arrive_remote_if(full_p + 8 * (js & (kXSlots - 1)), lane == 0);
+    };
+    if (lane == 0) {
+        for (int i = 0; i < NS; ++i) mbar_init(&y_full[i], 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
+    const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
+    int ist = 0;
+    auto issue = [&](int j) {
+        const int st = ist;
+        ist = (ist + 1 == NS) ? 0 : ist + 1;
+        if (j < ngroups && lane == 0) {
+            const int G = fwd ? j : (ngroups - 1 - j);
+            const int t0 = G * kGroup;
+            const int nr = min(kGroup, Tb - t0);
+            mbar_arrive_expect_tx(&y_full[st], rowbytes * nr);
+            tma_bulk_g2s(ytile + (size_t)(st * kGroup) * 2 * Cp, ybase + (size_t)t0 * 2 * Cp, rowbytes * nr,
+                         &y_full[st]);
         }
-        const int ex = expo_field(m);
-        const bool isnan_p = m != m;  // a non-finite emission row reached the lattice: cost and gradient are NaN
-        const bool ok = ex != 0 && ex != 2047 && e > kDeadE / 2;
-        if (ok) {
-            m *= pow2i(1023 - ex);
-            e += ex - 1023;
+    };
+    int wst = 0, wph = 0, nwaited = 0;
+    auto wait_tile = [&]() {
+        if (nwaited < ngroups) {
+            mbar_wait(&y_full[wst], wph);
+            if (++wst == NS) { wst = 0; wph ^= 1; }
+            ++nwaited;
         }
-        p.feas[b] = ok || isnan_p;
-        p.Pm[b] = (ok || isnan_p) ? m : 1.0;
-        p.Pe[b] = ok ? e : 0;
-        const double cost = -(log(m) + (double)e * 0.69314718055994530942);
-        p.costs[b] = isnan_p ? __int_as_float(0x7fc00000) : (ok ? (float)cost : (p.zero_infinity ? 0.f : INFINITY));
+    };
+    for (int j = 0; j <= kLookAhead; ++j) issue(j);
+    wait_tile();  // tile 0
+    wait_tile();  // tile 1: its first row is read during super-step 0
+    link_before(0);
+    named_bar_sync(1, nbar);
+    for (int i = 0; i < nsuper; ++i) {
+        fence_proxy_async();
+        issue(i + kLookAhead + 1);
+        wait_tile();  // tile i + 2
+        link_before(i + 1);
+        named_bar_sync(1, nbar);
+        link_after(i);
     }
 }
 
@@ -1107,8 +1293,7 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine2_kerne
     const bool fwd = p.score_only ? true : !(blockIdx.x & 1);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nwl = p.nwl;
-    constexpr int Cp = CP;
-    const EngineSmem lay = engine_smem(Cp, nwl);
+    const EngineSmem lay = engine_smem(CP, nwl);
     const int NS = lay.nstage;
     unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
     uint64_t *y_full = reinterpret_cast<uint64_t *>(smem + lay.bars);
@@ -1132,58 +1317,90 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine2_kerne
         return;
     }
     if (warp >= nwa && warp != nwl) return;  // lattice warps beyond this utterance's S
-    const int ngroups = (Tb + kGroup - 1) / kGroup;
-    const int nsuper = ngroups + nwa - 1;
-    const int nbar = (nwa + 1) * 32;
-
     if (warp == nwl) {
-        // =========================================================== producer warp: TMA emission-tile prefetch
-        // (as in ctc_engine_kernel, but the tile the lattice may touch is waited for one super-step EARLIER: lattice
-        // warps fetch the first row of their next tile before the group barrier)
-        if (lane == 0) {
-            for (int i = 0; i < NS; ++i) mbar_init(&y_full[i], 1);
-            fence_mbar_init();
-        }
-        __syncwarp();
-        const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
-        const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
-        int ist = 0;
-        auto issue = [&](int j) {
-            const int st = ist;
-            ist = (ist + 1 == NS) ? 0 : ist + 1;
-            if (j < ngroups && lane == 0) {
-                const int G = fwd ? j : (ngroups - 1 - j);
-                const int t0 = G * kGroup;
-                const int nr = min(kGroup, Tb - t0);
-                mbar_arrive_expect_tx(&y_full[st], rowbytes * nr);
-                tma_bulk_g2s(ytile + (size_t)(st * kGroup) * 2 * Cp, ybase + (size_t)t0 * 2 * Cp, rowbytes * nr,
-                             &y_full[st]);
-            }
-        };
-        int wst = 0, wph = 0, nwaited = 0;
-        auto wait_tile = [&]() {
-            if (nwaited < ngroups) {
-                mbar_wait(&y_full[wst], wph);
-                if (++wst == NS) { wst = 0; wph ^= 1; }
-                ++nwaited;
-            }
-        };
-        for (int j = 0; j <= kLookAhead; ++j) issue(j);
-        wait_tile();  // tile 0
-        wait_tile();  // tile 1: its first row is read during super-step 0
-        named_bar_sync(1, nbar);
-        for (int i = 0; i < nsuper; ++i) {
-            fence_proxy_async();
-            issue(i + kLookAhead + 1);
-            wait_tile();  // tile i + 2
-            named_bar_sync(1, nbar);
+        const EngLink nolink = {0, 0, nwa, 0u, 0u, nullptr, nullptr};
+        engine_producer<CP, false>(p, b, fwd, lane, nwa, Tb, ytile, y_full, NS, nolink, false, false);
+        return;
+    }
+    const EngLink nolink = {0, 0, nwa, 0u, 0u, nullptr, nullptr};
+    if (fwd)
+        engine_lattice<K, CP, true, false>(p, b, warp, lane, nwa, Tb, S, ytile, NS, rings, pm, pe, nolink);
+    else
+        engine_lattice<K, CP, false, false>(p, b, warp, lane, nwa, Tb, S, ytile, NS, rings, pm, pe, nolink);
+    if (fwd && tid == 0) engine_finish(p, b, S, pm[0], pe[0], pm[1], pe[1]);
+}
+
+// Long label sequences (more than 4 lattice warps, L > 511): the lattice warps of one (utterance, direction) are split
+// over the TWO CTAs of a thread-block cluster, so that every lattice warp has a scheduler (SMSP) and an FP64 pipe to
+// itself (5 warps in one CTA put two of them on one SMSP: +21 % per step on the first engine form).  Each CTA runs
+// its own systolic pipeline over its W = ceil(nwl / 2) warps with its own producer warp, emission-tile ring and
+// group barrier; the one boundary that crosses the CTAs goes through distributed shared memory (EngLink): DSMEM
+// stores into the receiver's ring + remote mbarrier arrivals, no cluster-wide barrier inside the loop.  The systolic
+// skew means the receiver consumes a group a whole super-step after it was sent, so neither the ~200 clk DSMEM
+// latency nor the mbarrier wake-up sits on the critical path.
+template <int K, int CP>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((kMaxLatticeWarps / 2 + 1) * 32)
+    ctc_engine2c_kernel(const CtcParams p) {
+    static_assert(K == 8, "label-table entries hold 4 labels = 8 states");
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int rank = (int)cluster_ctarank();
+    const int ud = (int)(blockIdx.x >> 1);  // (utterance, direction) of this cluster
+    const int bi = p.slice0 + (p.score_only ? ud : (ud >> 1));
+    const int b = p.bord ? p.bord[bi] : bi;
+    const bool fwd = p.score_only ? true : !(ud & 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nwl = p.nwl, W = (nwl + 1) >> 1;  // lattice warps per CTA
+    const EngineSmem lay = engine_smem(CP, W);
+    const int NS = lay.nstage;
+    unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
+    uint64_t *y_full = reinterpret_cast<uint64_t *>(smem + lay.bars);
+    SlotRing *rings = reinterpret_cast<SlotRing *>(smem + lay.slots);
+    unsigned char *xr = smem + lay.xlink;  // SlotRing[2] receive ring, then full[4] / empty[4] mbarriers
+
+    const int Tb = min(max(p.act_lens[b], 0), p.T);
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
+    const int S = 2 * L + 1;
+    const int nwa = min(nwl, (S + 32 * K - 1) / (32 * K));  // lattice warps this utterance needs (both CTAs)
+    const int nwa_l = min(max(nwa - rank * W, 0), W);       // ... of which this CTA runs
+    if (Tb == 0) {  // nothing to recurse over (the whole cluster leaves: no cluster barrier has been touched yet)
+        if (fwd && tid == 0 && rank == 0) {
+            const bool ok = (L == 0);
+            p.feas[b] = ok;
+            p.Pm[b] = 1.0;
+            p.Pe[b] = 0;
+            p.costs[b] = ok ? 0.f : (p.zero_infinity ? 0.f : INFINITY);
         }
         return;
     }
-    if (fwd)
-        engine_lattice<K, CP, true>(p, b, warp, lane, nwa, nbar, Tb, S, ytile, NS, rings, pm, pe);
-    else
-        engine_lattice<K, CP, false>(p, b, warp, lane, nwa, nbar, Tb, S, ytile, NS, rings, pm, pe);
+    EngLink lk;
+    lk.rank = rank;
+    lk.gw0 = rank * W;
+    lk.nwa_l = nwa_l;
+    lk.xring = smem_u32(xr);
+    lk.xbars = smem_u32(xr + 2 * sizeof(SlotRing));
+    lk.Pm2 = p.Pm2 + 2 * (size_t)b;
+    lk.Pe2 = p.Pe2 + 2 * (size_t)b;
+    if (tid == 0) {
+        uint64_t *xb = reinterpret_cast<uint64_t *>(xr + 2 * sizeof(SlotRing));
+        for (int i = 0; i < 2 * kXSlots; ++i) mbar_init(&xb[i], 1);
+        fence_mbar_init();
+    }
+    cluster_sync_all();  // both CTAs' link barriers exist before either sends
+    if (warp < nwa_l) {
+        if (fwd)
+            engine_lattice<K, CP, true, true>(p, b, warp, lane, nwa, Tb, S, ytile, NS, rings, nullptr, nullptr, lk);
+        else
+            engine_lattice<K, CP, false, true>(p, b, warp, lane, nwa, Tb, S, ytile, NS, rings, nullptr, nullptr, lk);
+    } else if (warp == W && nwa_l > 0) {
+        // the link exists iff the utterance needs warps in both CTAs; alpha flows rank 0 -> 1, beta rank 1 -> 0
+        const bool linked = nwa > W;
+        const bool xrecv = linked && (fwd ? rank == 1 : rank == 0), xsend = linked && (fwd ? rank == 0 : rank == 1);
+        engine_producer<CP, true>(p, b, fwd, lane, nwa_l, Tb, ytile, y_full, NS, lk, xrecv, xsend);
+    }
+    // no CTA leaves while its peer may still store into its shared memory; also publishes Pm2 / Pe2 (global memory,
+    // written by whichever CTA owns states S-1 and S-2) to rank 0
+    cluster_sync_all();
+    if (fwd && rank == 0 && tid == 0) engine_finish(p, b, S, lk.Pm2[0], lk.Pe2[0], lk.Pm2[1], lk.Pe2[1]);
 }
 
 // ================================================================================================ grad

@@ -829,3 +829,31 @@ def test_zero_frames_with_a_sliceable_batch(b200):
         torch.cuda.synchronize()
         c = costs.cpu().numpy()
         assert np.all(c[0::2] == 0.0) and np.all(c[1::2] == want)
+
+
+def test_cluster_engine_matches_single_cta_engine(oracle, b200, monkeypatch):
+    # more than 4 lattice warps (L > 511): the recursion runs as 2-CTA clusters whose boundary crosses through
+    # distributed shared memory (ctc_engine2c_kernel); it must reproduce the one-CTA engine bit for bit, in both
+    # directions, for utterances that need 5..8 lattice warps as well as short ones that leave the second CTA idle,
+    # ragged last groups included
+    T, C = 2300, 29
+    g = torch.Generator().manual_seed(101)
+    lens = [(2300, 1023), (2299, 900), (2041, 770), (1800, 640), (1700, 513), (1500, 512), (900, 300), (77, 20),
+            (1300, 600), (8, 2), (9, 3), (1, 1)]
+    B = len(lens)
+    acts = torch.randn(T, B, C, generator=g)
+    act_lens = torch.tensor([t for t, _ in lens], dtype=torch.int32)
+    ll = torch.tensor([l for _, l in lens], dtype=torch.int32)
+    labels = torch.randint(1, C, (int(ll.sum()),), generator=g, dtype=torch.int32)
+    # no repeats, so that every utterance is feasible (L + repeats <= T)
+    for i in range(1, labels.numel()):
+        if labels[i] == labels[i - 1]:
+            labels[i] = 1 + (int(labels[i]) % (C - 1))
+    d = {"acts": acts, "labels": labels, "act_lens": act_lens, "label_lens": ll}
+    monkeypatch.setenv("CTC_B200_CLUSTER", "0")
+    c0, g0 = _run(b200, d)
+    monkeypatch.setenv("CTC_B200_CLUSTER", "1")
+    c1, g1 = _check(oracle, b200, d)
+    assert np.array_equal(c0, c1) and np.array_equal(g0, g1)
+    ce, _ = _run(b200, d, want_grads=False)  # score-only launch: alpha clusters only
+    assert np.array_equal(ce, c1)

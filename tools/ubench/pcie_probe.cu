@@ -11,6 +11,24 @@ __global__ void copy_k(const float4 *__restrict__ src, float4 *__restrict__ dst,
         dst[i] = __ldg(src + i);
 }
 
+// one warp per (utterance-in-slice, frame): rows of C floats, `B*C` floats apart in the host tensor [T][B][C],
+// gathered into / scattered from a compact [nb][T][C] device buffer (what a length-bucketed slice needs when the
+// batch is not sorted by length)
+__global__ void gather_rows_k(const float *__restrict__ host, float *__restrict__ dev, const int *ids, int nb, int T,
+                              int B, int C, int to_host) {
+    const int lane = threadIdx.x & 31;
+    const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long r = w; r < (long long)nb * T; r += nw) {
+        const int u = (int)(r / T), t = (int)(r - (long long)u * T);
+        const float *h = host + ((size_t)t * B + ids[u]) * C;
+        float *d = dev + r * C;
+        if (lane < C) {
+            if (to_host) const_cast<float *>(h)[lane] = d[lane];
+            else d[lane] = __ldg(h + lane);
+        }
+    }
+}
+
 int main() {
     const int T = 1500, B = 64, C = 29, NCH = 4;
     const size_t n = (size_t)T * B * C, bytes = n * 4;
@@ -81,6 +99,46 @@ int main() {
         CK(cudaEventRecord(j, s1));
         CK(cudaStreamWaitEvent(s0, j, 0));
     });
+    {
+        // 16 of the 64 utterances (every 4th), all T frames: 16 * 1500 * 116 B = 2.78 MB per direction
+        const int nb = 16;
+        int hid[nb], *did;
+        for (int i = 0; i < nb; ++i) hid[i] = 4 * i + 1;
+        CK(cudaMalloc(&did, sizeof(hid)));
+        CK(cudaMemcpy(did, hid, sizeof(hid), cudaMemcpyHostToDevice));
+        const double gb = (double)nb * T * C * 4;
+        for (int grid : {148, 592, 1184}) {
+            float best[2] = {1e9f, 1e9f};
+            for (int dir = 0; dir < 2; ++dir)
+                for (int it = 0; it < 6; ++it) {
+                    CK(cudaDeviceSynchronize());
+                    CK(cudaEventRecord(e0, s0));
+                    gather_rows_k<<<grid, 256, 0, s0>>>(dir ? h_out : h_in, d_b, did, nb, T, B, C, dir);
+                    CK(cudaEventRecord(e1, s0));
+                    CK(cudaEventSynchronize(e1));
+                    float ms;
+                    CK(cudaEventElapsedTime(&ms, e0, e1));
+                    if (it >= 2 && ms < best[dir]) best[dir] = ms;
+                }
+            printf("kernel row gather host->HBM (116 B rows), grid %4d  %8.1f us %6.1f GB/s | scatter HBM->host %8.1f us %6.1f GB/s\n",
+                   grid, best[0] * 1e3, gb / (best[0] * 1e-3) / 1e9, best[1] * 1e3, gb / (best[1] * 1e-3) / 1e9);
+        }
+        // the same 16 utterances as 16 DMA 2-D copies of 116-byte rows
+        float best = 1e9f;
+        for (int it = 0; it < 5; ++it) {
+            CK(cudaDeviceSynchronize());
+            CK(cudaEventRecord(e0, s0));
+            for (int i = 0; i < nb; ++i)
+                CK(cudaMemcpy2DAsync((char *)d_b + (size_t)i * T * C * 4, C * 4, (char *)h_in + (size_t)hid[i] * C * 4, pitch,
+                                     C * 4, T, cudaMemcpyHostToDevice, s0));
+            CK(cudaEventRecord(e1, s0));
+            CK(cudaEventSynchronize(e1));
+            float ms;
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            if (it >= 1 && ms < best) best = ms;
+        }
+        printf("DMA 16 x 2-D copies of 116 B rows              %8.1f us %6.1f GB/s\n", best * 1e3, gb / (best * 1e-3) / 1e9);
+    }
     size_t bad = 0;
     for (size_t i = 0; i < n; ++i) bad += (h_out[i] != h_in[i]);
     printf("mismatches %zu\n", bad);

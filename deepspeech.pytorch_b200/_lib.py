@@ -24,7 +24,8 @@ EXPORTS = ("ctc_b200_get_version", "ctc_b200_status_string", "ctc_b200_default_o
            "ctc_b200_compute_decode", "ctc_b200_greedy_decode", "ctc_b200_error_counts", "ctc_b200_last_launch_count",
            "ctc_b200_comm_create", "ctc_b200_comm_handle", "ctc_b200_comm_local", "ctc_b200_comm_open",
            "ctc_b200_comm_set_peers", "ctc_b200_comm_destroy", "ctc_b200_comm_set_timeout",
-           "ctc_b200_comm_timed_out", "ctc_b200_scale_grads", "ctc_b200_last_copy_bytes")
+           "ctc_b200_comm_timed_out", "ctc_b200_scale_grads", "ctc_b200_last_copy_bytes",
+           "ctc_b200_compute_static")
 
 
 class CtcOptions(ctypes.Structure):
@@ -84,6 +85,8 @@ def load():
     lib.ctc_b200_workspace_size.restype = I
     lib.ctc_b200_compute.argtypes = [V, V, V, V, V, I, I, I, V, V, ctypes.c_size_t, P(CtcOptions)]
     lib.ctc_b200_compute.restype = I
+    lib.ctc_b200_compute_static.argtypes = [V, V, V, V, V, I, I, I, V, P(CtcOptions)]
+    lib.ctc_b200_compute_static.restype = I
     lib.ctc_b200_create.argtypes = [P(V)]
     lib.ctc_b200_create.restype = I
     lib.ctc_b200_destroy.argtypes = [V]

@@ -672,6 +672,64 @@ extern "C" ctcB200Status ctc_b200_greedy_decode(const float *acts, long long str
     return cudaGetLastError() == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }
 
+// ------------------------------------------------------------------------------------------------ no-allocation entry
+// Scratch of ctc_b200_compute_static: a file-scope device array (every GPU that loads the library holds these
+// CTC_B200_STATIC_WORKSPACE_BYTES until the process exits).  In HOST code the name `g_static_ws` is only a stand-in
+// for the symbol, never a device address: the address is taken once per device with cudaGetSymbolAddress (that
+// device current) and cached.
+static __device__ __align__(256) unsigned char g_static_ws[CTC_B200_STATIC_WORKSPACE_BYTES];
+
+namespace {
+std::mutex g_static_mu;
+void *g_static_ptr[64] = {};
+
+// device address of g_static_ws on the CURRENT device (nullptr on failure)
+void *static_workspace() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void *ptr = nullptr;
+        if (cudaGetSymbolAddress(&ptr, g_static_ws) != cudaSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        g_static_ptr[dev] = ptr;
+    }
+    return g_static_ptr[dev];
+}
+}  // namespace
+
+extern "C" ctcB200Status ctc_b200_compute_static(const float *acts, float *grads, const int *labels,
+                                                 const int *label_lens, const int *act_lens, int T, int B, int C,
+                                                 float *costs, const ctcB200Options *opts_in) {
+    g_last_launches = 0;
+    ctcB200Options o;
+    if (opts_in) o = *opts_in; else ctc_b200_default_options(&o);
+    if (!label_lens || B < 1) return CTC_B200_STATUS_INVALID_VALUE;
+    // the shape's scratch must fit the static array: same bound the workspace query reports
+    int Lmax = o.max_label_len;
+    if (!o.lengths_on_device) {
+        Lmax = 0;
+        for (int b = 0; b < B; ++b) Lmax = label_lens[b] > Lmax ? label_lens[b] : Lmax;
+    }
+    size_t need = 0;
+    if (ctc_b200_workspace_size(T, B, C, Lmax, &o, &need) != CTC_B200_STATUS_SUCCESS)
+        return CTC_B200_STATUS_INVALID_VALUE;
+    if (need > (size_t)CTC_B200_STATIC_WORKSPACE_BYTES) {
+        fprintf(stderr,
+                "ctc_b200_compute_static: T=%d B=%d C=%d max_label_len=%d needs %zu bytes of scratch, the static "
+                "array holds %zu (CTC_B200_STATIC_WORKSPACE_BYTES); use ctc_b200_compute with a caller-owned workspace\n",
+                T, B, C, Lmax, need, (size_t)CTC_B200_STATIC_WORKSPACE_BYTES);
+        return CTC_B200_STATUS_INVALID_VALUE;
+    }
+    void *ws = static_workspace();
+    if (!ws) return CTC_B200_STATUS_EXECUTION_FAILED;
+    // unsliced: every kernel goes to opts->stream itself, so not even the side-stream pool is created
+    return compute_impl(acts, grads, labels, label_lens, act_lens, T, B, C, costs, ws,
+                        (size_t)CTC_B200_STATIC_WORKSPACE_BYTES, &o, false);
+}
+
 // ------------------------------------------------------------------------------------------------ loss all-reduce
 constexpr size_t kCommBytes = sizeof(unsigned long long) * 2 * kCommMaxWorld + 64;
 

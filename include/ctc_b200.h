@@ -218,6 +218,25 @@ ctcB200Status ctc_b200_error_counts(const int *hyp_ids, int hyp_pitch, const int
                                     const int *ref_lens, int B, int max_hyp_len, int max_ref_len, int space_index,
                                     int *counts, const ctcB200Options *opts);
 
+/*
+ * ctc_b200_compute without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments and results as ctc_b200_compute, minus the workspace: the scratch is a file-scope
+ * `static __device__` array of CTC_B200_STATIC_WORKSPACE_BYTES inside the library (held by every GPU that loads the
+ * library until the process exits).  The call performs no cudaMalloc / cudaFree and calls no allocating library
+ * routine; every kernel is enqueued on opts->stream itself (no length-bucket slices, no internal streams).
+ *   Limit: shapes whose ctc_b200_workspace_size exceeds CTC_B200_STATIC_WORKSPACE_BYTES are rejected with
+ *   CTC_B200_STATUS_INVALID_VALUE and a message on stderr naming the bytes needed (B=16,T=500,C=29 needs 4.2 MiB,
+ *   B=32,T=500 8.4 MiB; the B=64,T=1500 headline needs 129 MiB and must use ctc_b200_compute).
+ *   Sharing: ALL calls on a device use the same array, and it keeps the previous call's contents.  Nothing in it has
+ *   to start at zero (every kernel writes what it later reads), but two calls that overlap on the GPU -- different
+ *   streams, or a captured graph replayed beside an eager call -- RACE on it: serialise them.
+ */
+#define CTC_B200_STATIC_WORKSPACE_BYTES (16u << 20)
+ctcB200Status ctc_b200_compute_static(const float *acts, float *grads, const int *labels, const int *label_lens,
+                                      const int *act_lens, int T, int B, int C, float *costs,
+                                      const ctcB200Options *opts);
+
 /* number of kernel launches the last ctc_b200_compute on this thread enqueued (bench.py's gpu_launches claim) */
 int ctc_b200_last_launch_count(void);
 /* bytes the last ctc_b200_compute_host on this thread actually moved over the bus, host->device and device->host

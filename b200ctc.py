@@ -37,3 +37,4 @@ ALPHABET = pkg.ALPHABET
 workloads = pkg.workloads
 sharding = pkg.sharding
 packing = pkg.packing
+fc = pkg.fc

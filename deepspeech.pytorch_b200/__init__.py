@@ -7,7 +7,7 @@ sm_100a CUDA (csrc/) behind a C ABI (include/ctc_b200.h), plus the host-side mir
 The directory name contains a dot, so it is imported through the loader in /root/repo/b200ctc.py
 (`import b200ctc`), which registers this package as `deepspeech_pytorch_b200`.
 """
-from . import _lib, packing, sharding, workloads  # noqa: F401
+from . import _lib, fc, packing, sharding, workloads  # noqa: F401
 from ._lib import build  # noqa: F401
 from .ctc_loss import (CTCLoss, GreedyDecoder, ctc_forward_backward, error_counts, greedy_decode,  # noqa: F401
                        last_launch_count)

@@ -13,7 +13,8 @@ import subprocess
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, "libctc_b200.so")
-SOURCES = [os.path.join(_PKG, "csrc", f) for f in ("ctc_api.cu", "ctc_kernels.cuh", "ctc_device.cuh", "ctc_metrics.cuh")] + [
+SOURCES = [os.path.join(_PKG, "csrc", f) for f in ("ctc_api.cu", "ctc_kernels.cuh", "ctc_device.cuh", "ctc_metrics.cuh",
+                                                   "fc_kernels.cuh")] + [
     os.path.join(_ROOT, "include", "ctc_b200.h")
 ]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
@@ -25,7 +26,7 @@ EXPORTS = ("ctc_b200_get_version", "ctc_b200_status_string", "ctc_b200_default_o
            "ctc_b200_comm_create", "ctc_b200_comm_handle", "ctc_b200_comm_local", "ctc_b200_comm_open",
            "ctc_b200_comm_set_peers", "ctc_b200_comm_destroy", "ctc_b200_comm_set_timeout",
            "ctc_b200_comm_timed_out", "ctc_b200_scale_grads", "ctc_b200_last_copy_bytes",
-           "ctc_b200_compute_static")
+           "ctc_b200_compute_static", "ctc_b200_fc_workspace_size", "ctc_b200_fc_forward")
 
 
 class CtcOptions(ctypes.Structure):
@@ -35,7 +36,15 @@ class CtcOptions(ctypes.Structure):
                 ("max_label_len", ctypes.c_int), ("phase_mask", ctypes.c_int), ("nan_to_zero", ctypes.c_int),
                 ("costs_ready", ctypes.c_void_p), ("nan_count", ctypes.c_void_p),
                 ("loss_sum", ctypes.c_void_p), ("comm", ctypes.c_void_p),
-                ("loss_sum_all", ctypes.c_void_p)]
+                ("loss_sum_all", ctypes.c_void_p), ("emissions_ready", ctypes.c_int)]
+
+
+class FcLayer(ctypes.Structure):
+    """Mirror of ctcB200FcLayer (include/ctc_b200.h)."""
+    _fields_ = [("weight", ctypes.c_void_p), ("bn_weight", ctypes.c_void_p), ("bn_bias", ctypes.c_void_p),
+                ("bn_mean", ctypes.c_void_p), ("bn_var", ctypes.c_void_p), ("bn_eps", ctypes.c_float),
+                ("bn_batch_stats", ctypes.c_int), ("batch_mean_out", ctypes.c_void_p),
+                ("batch_var_out", ctypes.c_void_p)]
 
 
 def _nvcc() -> str:
@@ -87,6 +96,10 @@ def load():
     lib.ctc_b200_compute.restype = I
     lib.ctc_b200_compute_static.argtypes = [V, V, V, V, V, I, I, I, V, P(CtcOptions)]
     lib.ctc_b200_compute_static.restype = I
+    lib.ctc_b200_fc_workspace_size.argtypes = [I, I, I, I, P(ctypes.c_size_t)]
+    lib.ctc_b200_fc_workspace_size.restype = I
+    lib.ctc_b200_fc_forward.argtypes = [V, I, I, I, I, P(FcLayer), V, V, V, V, V, ctypes.c_size_t, P(CtcOptions)]
+    lib.ctc_b200_fc_forward.restype = I
     lib.ctc_b200_create.argtypes = [P(V)]
     lib.ctc_b200_create.restype = I
     lib.ctc_b200_destroy.argtypes = [V]

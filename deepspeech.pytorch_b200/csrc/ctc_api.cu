@@ -19,6 +19,7 @@
 #include "../../include/ctc_b200.h"
 #include "ctc_kernels.cuh"
 #include "ctc_metrics.cuh"
+#include "fc_kernels.cuh"
 
 using namespace ctcb200;
 
@@ -84,10 +85,18 @@ int env_int(const char *name, int dflt) {
     return (v && *v) ? atoi(v) : dflt;
 }
 
-// CTC_B200_ENGINE=1 selects the first form of the recursion kernel (kept for A/B measurements)
+// Two forms of the recursion kernel.  The second (ctc_engine2_kernel) has the shorter dependent chain per group and
+// wins whenever an engine CTA has an SM to itself (B=64: 137 against 157 us; B=32,T=4000: 346 against 394); the first
+// issues fewer instructions per step (its warp-edge accesses are branches, not predicated instructions on all lanes)
+// and wins once several engine CTAs share an SM and the kernel is bound by issue slots instead of latency (B=256: 259
+// against 270 us, B=1024: 731 against 790).  CTC_B200_ENGINE=1 / 2 forces one form (A/B measurements); 0 = by batch.
 int engine_version() {
-    static const int v = env_int("CTC_B200_ENGINE", 2);
+    static const int v = env_int("CTC_B200_ENGINE", 0);
     return v;
+}
+inline bool engine_first_form(int B) {
+    const int v = engine_version();
+    return v == 1 || (v == 0 && 2 * B > 160);  // more engine CTAs than SMs (148): throughput-bound
 }
 
 struct Plan {
@@ -152,7 +161,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     if (pl->smem_engine > kSmemLimit || pl->smem_prep > kSmemLimit) return false;
     // more than 4 lattice warps (L > 511): split them over the two CTAs of a cluster so that each has an SMSP to
     // itself.  CTC_B200_CLUSTER=0 keeps everything in one CTA (A/B measurements).
-    pl->cluster = (nwl > 4 && engine_version() != 1 && env_int("CTC_B200_CLUSTER", 1) != 0) ? 1 : 0;
+    pl->cluster = (nwl > 4 && !engine_first_form(B) && env_int("CTC_B200_CLUSTER", 1) != 0) ? 1 : 0;
     pl->smem_engine_c = engine_smem(pl->Cp, (nwl + 1) / 2).total;
     {
         // Length-bucket slices: up to kMaxSlices, each at least kMinSliceB utterances.  CTC_B200_SLICES overrides.
@@ -342,7 +351,7 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
     return launch_sliced(
         p, pl, st, do_engine, do_grad, launches, costs_ready, loss_sum,
         [&](const CtcParams &pk, int nb, cudaStream_t s) {
-            if (engine_version() == 1)
+            if (engine_first_form(pk.B))
                 ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             else if (pl.cluster)
                 ctc_engine2c_kernel<kK, CP><<<2 * (pk.score_only ? nb : 2 * nb), ((pl.nwl + 1) / 2 + 1) * 32,
@@ -435,7 +444,7 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         rows_at(pk, nb, s);
     };
     auto eng = [&](const CtcParams &pk, int nb, cudaStream_t s) {
-        if (engine_version() == 1)
+        if (engine_first_form(pk.B))
             ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
         else if (pl.cluster)
             ctc_engine2c_kernel<kK, CP><<<2 * (pk.score_only ? nb : 2 * nb), ((pl.nwl + 1) / 2 + 1) * 32,
@@ -615,6 +624,8 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.bord = pl.nslices > 1 ? reinterpret_cast<int *>(ws + pl.o_bord) : nullptr;
     p.slice0 = 0;
     p.slice_nb = B;
+    if (o.emissions_ready && (pl.big || o.nan_to_zero || dec)) return CTC_B200_STATUS_INVALID_VALUE;
+    p.y_ready = o.emissions_ready ? 1 : 0;
     p.nan_to_zero = o.nan_to_zero ? 1 : 0;
     p.nan_count = o.nan_to_zero ? o.nan_count : nullptr;
 
@@ -670,6 +681,145 @@ extern "C" ctcB200Status ctc_b200_greedy_decode(const float *acts, long long str
     ctc_collapse_kernel<<<B, kCollapseThreads, 0, st>>>(path, act_lens_dev, T, B, o.blank, ids, offsets, out_lens);
     ++g_last_launches;
     return cudaGetLastError() == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
+}
+
+// ------------------------------------------------------------------------------------------------ fc layer (f3)
+namespace {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+// the driver's tensor-map encoder, fetched through the runtime (the library does not link libcuda)
+EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(f);
+    }();
+    return fn;
+}
+// 2-D fp32 tensor [rows][cols] (row pitch `pitch_bytes`, a multiple of 16), box [box_rows][32 columns], 128-byte
+// swizzle, out-of-range elements read as zero
+bool make_map(CUtensorMap *m, const void *base, unsigned long long rows, unsigned long long cols,
+              unsigned long long pitch_bytes, unsigned box_rows) {
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) return false;
+    const cuuint64_t gdim[2] = {cols, rows}, gstr[1] = {pitch_bytes};
+    const cuuint32_t box[2] = {(cuuint32_t)kFcBK, box_rows}, estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void *>(base), gdim, gstr, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+struct FcPlan {
+    int N;                       // classes padded to 32 / 64
+    size_t o_w2, o_bias, o_mean, o_var, o_part, total;
+    int nstat;                   // row blocks of the batch-statistics pass
+};
+bool fc_plan(int T, int B, int H, int C, FcPlan *pl) {
+    if (T < 1 || B < 1 || H < 4 || (H & 3) || C < 2 || C > 64) return false;
+    if ((long long)T * B > (1ll << 31) - kFcBM) return false;
+    pl->N = C <= 32 ? 32 : 64;
+    const long long rows = (long long)T * B;
+    pl->nstat = (int)((rows + kFcStatRows - 1) / kFcStatRows);
+    size_t o = 0;
+    pl->o_w2 = o;   o = align256(o + sizeof(float) * 2 * pl->N * (size_t)H);
+    pl->o_bias = o; o = align256(o + sizeof(float) * pl->N);
+    pl->o_mean = o; o = align256(o + sizeof(float) * H);
+    pl->o_var = o;  o = align256(o + sizeof(float) * H);
+    pl->o_part = o; o = align256(o + sizeof(double) * 2 * (size_t)pl->nstat * H);
+    pl->total = o;
+    return true;
+}
+template <int N>
+cudaError_t fc_launch(const CUtensorMap &mx, const CUtensorMap &mx32, const CUtensorMap &mw, const FcParams &fp, int grid,
+                      cudaStream_t st) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    {
+        std::lock_guard<std::mutex> lock(g_attr_mu);
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(fc_logits_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)FcCfg<N>::smem);
+            if (e != cudaSuccess) return e;
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        }
+    }
+    fc_logits_kernel<N><<<grid, kFcThreads, FcCfg<N>::smem, st>>>(mx, mx32, mw, fp);
+    return cudaGetLastError();
+}
+}  // namespace
+
+extern "C" ctcB200Status ctc_b200_fc_workspace_size(int T, int B, int H, int C, size_t *bytes) {
+    FcPlan pl;
+    if (!bytes || !fc_plan(T, B, H, C, &pl)) return CTC_B200_STATUS_INVALID_VALUE;
+    *bytes = pl.total;
+    return CTC_B200_STATUS_SUCCESS;
+}
+
+extern "C" ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H, int C, const ctcB200FcLayer *layer,
+                                             float *logits, void *ctc_workspace, const int *act_lens_dev, int *path,
+                                             void *fc_workspace, size_t fc_workspace_bytes,
+                                             const ctcB200Options *opts_in) {
+    g_last_launches = 0;
+    FcPlan pl;
+    if (!x || !layer || !layer->weight || !fc_workspace || !fc_plan(T, B, H, C, &pl))
+        return CTC_B200_STATUS_INVALID_VALUE;
+    if (fc_workspace_bytes < pl.total || ((uintptr_t)fc_workspace & 255) || ((uintptr_t)x & 15))
+        return CTC_B200_STATUS_INVALID_VALUE;
+    if (!logits && !ctc_workspace && !path) return CTC_B200_STATUS_INVALID_VALUE;
+    if (ctc_workspace && ((uintptr_t)ctc_workspace & 255)) return CTC_B200_STATUS_INVALID_VALUE;
+    cudaStream_t st = opts_in ? (cudaStream_t)opts_in->stream : nullptr;
+    unsigned char *ws = static_cast<unsigned char *>(fc_workspace);
+    float *W2 = reinterpret_cast<float *>(ws + pl.o_w2), *bias = reinterpret_cast<float *>(ws + pl.o_bias);
+    const long long rows = (long long)T * B;
+    const float *mean = layer->bn_mean, *var = layer->bn_var;
+    if (layer->bn_batch_stats) {
+        // training-mode forward of nn.BatchNorm1d: normalise with the statistics of THIS batch (biased variance)
+        float *m = reinterpret_cast<float *>(ws + pl.o_mean), *v = reinterpret_cast<float *>(ws + pl.o_var);
+        double *part = reinterpret_cast<double *>(ws + pl.o_part);
+        fc_bn_partial_kernel<<<pl.nstat, 256, 0, st>>>(x, rows, H, part);
+        fc_bn_combine_kernel<<<(H + 255) / 256, 256, 0, st>>>(part, pl.nstat, rows, H, m, v);
+        g_last_launches += 2;
+        if (layer->batch_mean_out &&
+            cudaMemcpyAsync(layer->batch_mean_out, m, sizeof(float) * H, cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+            return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (layer->batch_var_out &&
+            cudaMemcpyAsync(layer->batch_var_out, v, sizeof(float) * H, cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+            return CTC_B200_STATUS_MEMOPS_FAILED;
+        mean = m;
+        var = v;
+    }
+    fc_fold_kernel<<<pl.N, 256, 0, st>>>(layer->weight, layer->bn_weight, layer->bn_bias, mean, var, layer->bn_eps, H,
+                                         C, pl.N, W2, bias);
+    ++g_last_launches;
+    if (cudaGetLastError() != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+    CUtensorMap mx, mx32, mw;
+    if (!make_map(&mx, x, (unsigned long long)rows, (unsigned long long)H, (unsigned long long)H * 4, kFcBM) ||
+        !make_map(&mx32, x, (unsigned long long)rows, (unsigned long long)H, (unsigned long long)H * 4, 32) ||
+        !make_map(&mw, W2, (unsigned long long)(2 * pl.N), (unsigned long long)H, (unsigned long long)H * 4,
+                  (unsigned)(2 * pl.N)))
+        return CTC_B200_STATUS_EXECUTION_FAILED;
+    FcParams fp;
+    fp.rows = rows; fp.T = T; fp.B = B; fp.H = H; fp.C = C;
+    fp.bias = bias;
+    fp.logits = logits;
+    fp.y = static_cast<unsigned *>(ctc_workspace);  // the emission rows are the first array of the CTC workspace
+    fp.act_lens = act_lens_dev;
+    fp.path = path;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // equal row ranges per SM (multiples of 8 rows), at least one 32-row box each
+    long long per = (rows + sms - 1) / sms;
+    per = (per + 7) & ~7ll;
+    if (per < 32) per = 32;
+    const int grid = (int)((rows + per - 1) / per);
+    fp.rows_per_cta = (int)per;
+    cudaError_t e = pl.N == 32 ? fc_launch<32>(mx, mx32, mw, fp, grid, st) : fc_launch<64>(mx, mx32, mw, fp, grid, st);
+    ++g_last_launches;
+    return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }
 
 // ------------------------------------------------------------------------------------------------ no-allocation entry

@@ -75,6 +75,7 @@ struct CtcParams {
     int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
     int nan_to_zero;    // 1: a NaN logit is read as 0 (the reference's train.py:595-598 guard, folded into the softmax pass)
     int *nan_count;     // optional: += number of NaN logits seen in valid frames (nan_to_zero only)
+    int y_ready;        // 1: the emission rows y were written by fc_logits_kernel; the row blocks only zero padding grads
 #ifdef CTC_PROFILE
     long long *dbg;     // [ctas][16 warps][8] clock counters (tools/ubench/engine_bench.cu only)
 #endif
@@ -316,6 +317,17 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     float *xs = reinterpret_cast<float *>(smem);
     const long long row0 = (long long)((int)blockIdx.x - nextra) * kPrepRows;
     const int nrows = (int)min((long long)kPrepRows, nrows_total - row0);
+    if (p.y_ready) {
+        // the emission rows came with the logits (fc_logits_kernel's epilogue): the logits are not read at all; what
+        // is left of this block's work is the zero gradient of its padding frames
+        if (p.grads)
+            for (int i = tid; i < nrows * C; i += kPrepRows) {
+                const long long row = row0 + i / C;
+                const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
+                if (t >= min(max(p.act_lens[b], 0), p.T)) p.grads[row0 * C + i] = 0.f;
+            }
+        return;
+    }
     const float *src = p.acts + row0 * C;
     const int n = nrows * C;
     if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {

@@ -83,7 +83,8 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
                          out_grads: Optional[torch.Tensor] = None, decode: bool = False,
                          costs_ready: Optional[torch.cuda.Event] = None, nan_to_zero: bool = False,
                          nan_count: Optional[torch.Tensor] = None, loss_sum: Optional[torch.Tensor] = None,
-                         comm=None, loss_sum_all: Optional[torch.Tensor] = None):
+                         comm=None, loss_sum_all: Optional[torch.Tensor] = None,
+                         workspace: Optional[torch.Tensor] = None, emissions_ready: bool = False):
     """One call of ctc_b200_compute on the current CUDA stream.  Returns (costs[B] fp32 cuda, grads[T,B,C] | None).
 
     nan_to_zero: NaN logits are read as 0 (the guard at train.py:595-598 of the reference, folded into the softmax
@@ -104,6 +105,10 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
     decode=True calls ctc_b200_compute_decode instead and returns (costs, grads, best) where best is the dict
     {"path": int32 [B,T], "ids": int32 [B,T], "offsets": int32 [B,T], "lens": int32 [B]} (all CUDA): the greedy
     decoding of the same logits (decoder.py:165-197 of the reference), a by-product of the softmax pass.
+
+    workspace: a uint8 CUDA tensor to use as scratch instead of the cached one (fc.ctc_workspace_for).
+    emissions_ready=True: that workspace's emission rows were already written by fc.fc_forward(ctc_workspace=...) for
+    these logits; the softmax pass is skipped and `acts` is only used for its shape (C <= 64).
 
     No host synchronisation happens here when labels/lengths are CUDA tensors (then `max_label_len` is required);
     with CPU labels/lengths (the reference's calling convention) they are staged to the device inside the call.
@@ -164,7 +169,12 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
         nbytes = ctypes.c_size_t(0)
         _lib.check(lib.ctc_b200_workspace_size(T, B, C, lmax, ctypes.byref(opts), ctypes.byref(nbytes)),
                    "ctc_b200_workspace_size")
-        ws = _workspace(dev, nbytes.value)
+        if emissions_ready and workspace is None:
+            raise ValueError("emissions_ready needs the workspace the fc kernel wrote its emission rows into")
+        opts.emissions_ready = int(bool(emissions_ready))
+        ws = workspace if workspace is not None else _workspace(dev, nbytes.value)
+        if not (ws.is_cuda and ws.dtype == torch.uint8 and ws.numel() >= nbytes.value + 255):
+            raise ValueError("workspace must be a CUDA uint8 tensor of at least ctc_b200_workspace_size + 255 bytes")
         ws_ptr = (ws.data_ptr() + 255) & ~255
         ws_len = ws.numel() - (ws_ptr - ws.data_ptr())
         costs = torch.empty(B, dtype=torch.float32, device=dev)

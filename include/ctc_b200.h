@@ -86,6 +86,8 @@ typedef struct {
                               loss_sum_all; every rank of the communicator must make the same sequence of calls. */
     float *loss_sum_all;   /* DEVICE float or NULL; sum of loss_sum over the ranks of `comm` (without a communicator:
                               the same value as loss_sum) -- what reduce_tensor (data/utils.py:40-44) all-reduces */
+    int emissions_ready;   /* 1: the emission rows of `workspace` were already written by ctc_b200_fc_forward for these
+                              logits (same T, B, C): the softmax pass is skipped and `acts` is not read (C <= 64) */
 } ctcB200Options;
 
 /* replaces get_warpctc_version() */
@@ -217,6 +219,39 @@ ctcB200Status ctc_b200_scale_grads(float *grads, size_t count, const float *scal
 ctcB200Status ctc_b200_error_counts(const int *hyp_ids, int hyp_pitch, const int *hyp_lens, const int *ref_labels,
                                     const int *ref_lens, int B, int max_hyp_len, int max_ref_len, int space_index,
                                     int *counts, const ctcB200Options *opts);
+
+/*
+ * The logits producer -- SURVEY.md 8(f) rank 3.  Replaces, in the forward direction, the reference's final layer
+ *     fully_connected = nn.Sequential(nn.BatchNorm1d(H), nn.Linear(H, C, bias=False)); SequenceWise(fully_connected)
+ * (/root/reference/model.py:335-341, applied to x [T,B,H] at model.py:373) and, optionally, the softmax the CTC path
+ * applies to its output (the criterion's own pass over the logits; model.py:377): one TMA + tcgen05 (tf32, split for
+ * fp32-level accuracy) kernel reads x [T*B, H] once and writes
+ *   logits        DEVICE fp32 [T,B,C] (nullable), what model.py:373 returns before the transposes at :375 / train.py:593;
+ *   ctc_workspace (nullable) the emission rows of a CTC workspace sized by ctc_b200_workspace_size for the SAME T, B, C:
+ *                 a following ctc_b200_compute with opts->emissions_ready = 1 then skips its own softmax pass and never
+ *                 reads the logits (rows t >= act_lens_dev[b] are skipped when act_lens_dev is given);
+ *   path          (nullable) DEVICE int32 [B][T], argmax class per frame: the input of ctc_b200 greedy collapse.
+ * BatchNorm is folded into the weights per call: with bn_batch_stats = 0 it uses bn_mean / bn_var (module.eval(), the
+ * reference's validation path train.py:329-431); with 1 it first computes this batch's mean and biased variance
+ * (training-mode forward; written to batch_mean_out / batch_var_out if given, so the caller can update running stats).
+ * Any of bn_weight / bn_bias / bn_mean / bn_var may be NULL (1 / 0 / 0 / 1).  Forward only: gradients of the layer stay
+ * with the caller's autograd.  Limits: C <= 64, H a multiple of 4, x 16-byte aligned.
+ */
+typedef struct {
+    const float *weight;     /* DEVICE fp32 [C,H]: nn.Linear(H, C, bias=False).weight */
+    const float *bn_weight;  /* DEVICE fp32 [H] or NULL: BatchNorm1d.weight (gamma) */
+    const float *bn_bias;    /* DEVICE fp32 [H] or NULL: BatchNorm1d.bias (beta) */
+    const float *bn_mean;    /* DEVICE fp32 [H] or NULL: running_mean (bn_batch_stats = 0) */
+    const float *bn_var;     /* DEVICE fp32 [H] or NULL: running_var  (bn_batch_stats = 0) */
+    float bn_eps;            /* BatchNorm1d.eps (1e-5) */
+    int bn_batch_stats;      /* 1: normalise with the statistics of x itself (module.train()) */
+    float *batch_mean_out;   /* DEVICE fp32 [H] or NULL: receives the batch mean (bn_batch_stats = 1) */
+    float *batch_var_out;    /* DEVICE fp32 [H] or NULL: receives the biased batch variance */
+} ctcB200FcLayer;
+ctcB200Status ctc_b200_fc_workspace_size(int T, int B, int H, int C, size_t *bytes);
+ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H, int C, const ctcB200FcLayer *layer,
+                                  float *logits, void *ctc_workspace, const int *act_lens_dev, int *path,
+                                  void *fc_workspace, size_t fc_workspace_bytes, const ctcB200Options *opts);
 
 /*
  * ctc_b200_compute without any allocation.  NO COUNTERPART IN THE REFERENCE: added

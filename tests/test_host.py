@@ -29,7 +29,7 @@ def test_options_struct_layout_and_defaults(b200):
     o = b200.pkg._lib.CtcOptions()
     lib.ctc_b200_default_options(ctypes.byref(o))
     assert (o.blank, o.zero_infinity, o.grad_scale, o.lengths_on_device) == (0, 1, 1.0, 0)
-    assert ctypes.sizeof(o) == 80  # 8 + 7 * 4 (+4 pad) + 5 pointers
+    assert ctypes.sizeof(o) == 88  # 8 + 7 * 4 (+4 pad) + 5 pointers + emissions_ready (+4 pad)
 
 
 def test_workspace_query_is_shape_only(b200):

@@ -501,6 +501,15 @@ def run_b200(args, w):
             others[name] = entry
             bn.unload()
 
+    fc_layer = None
+    if not args.quick and world == 1 and w.name == b200ctc.workloads.HEADLINE:
+        # the next row of the scope table: the logits producer feeding this loss, same frame count
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_fc
+            fc_layer = bench_fc.run()
+        except Exception as exc:  # never lose the headline line to the extra block
+            fc_layer = {"error": repr(exc)}
     if rank == 0:
         peak, peak_kind = load_peaks()
         cpu = None
@@ -530,6 +539,8 @@ def run_b200(args, w):
             line["weak_scaling_control"] = control
         if others:
             line["workloads"] = others
+        if fc_layer:
+            line["fc_layer"] = fc_layer
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

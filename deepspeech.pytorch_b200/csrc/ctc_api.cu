@@ -803,6 +803,7 @@ extern "C" ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H
                   (unsigned)(2 * pl.N)))
         return CTC_B200_STATUS_EXECUTION_FAILED;
     FcParams fp;
+    fp.x = x;
     fp.rows = rows; fp.T = T; fp.B = B; fp.H = H; fp.C = C;
     fp.bias = bias;
     fp.logits = logits;

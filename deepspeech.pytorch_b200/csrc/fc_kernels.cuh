@@ -25,7 +25,13 @@
 
 namespace ctcb200 {
 
-constexpr int kFcBM = 128;      // rows (frames) per tile = UMMA M
+// 1: whole rows of the NEXT tile are bulk-prefetched into L2 by the producer lane (see the producer).  Measured on
+// B200 and rejected: 0.126 ms against 0.106 ms without (T=1500, B=64, H=800) -- kept as a switch for re-measurement.
+#ifndef CTC_FC_L2_PREFETCH
+#define CTC_FC_L2_PREFETCH 0
+#endif
+constexpr int kFcBM = 256;      // rows (frames) per tile: two UMMA M = 128 halves that share one W' tile
+constexpr int kFcHM = 128;      // UMMA M
 constexpr int kFcBK = 32;       // fp32 columns per k-block = one 128-byte swizzle row
 constexpr int kFcUmmaK = 8;     // tf32 elements per tcgen05.mma
 constexpr int kFcThreads = 320; // warp 0: TMA producer, warp 1: TMEM owner + MMA issuer, 2-5: converters, 6-9: epilogue
@@ -33,17 +39,21 @@ constexpr int kFcThreads = 320; // warp 0: TMA producer, warp 1: TMEM owner + MM
 template <int N>
 struct FcCfg {
     static_assert(N == 32 || N == 64, "classes are padded to 32 or 64");
-    static constexpr int stages = N == 32 ? 7 : 5;          // TMA ring: x tile + W' tiles of one k-block per stage
+    static constexpr int stages = N == 32 ? 4 : 3;          // TMA ring: x tile + W' tiles of one k-block per stage
     static constexpr int lo_bufs = 2;                       // x_lo tiles (converter -> MMA), outside the TMA ring
-    static constexpr int nacc = N == 32 ? 4 : 2;            // accumulators per tile, k-blocks dealt round-robin (below)
-    static constexpr int a_bytes = kFcBM * kFcBK * 4;       // 16 KB: x tile (also the size of an x_lo tile)
+    static constexpr int nacc = N == 32 ? 2 : 1;            // accumulators per half tile, k-blocks dealt round-robin
+    static constexpr int a_bytes = kFcBM * kFcBK * 4;       // 32 KB: x tile (also the size of an x_lo tile)
+    static constexpr int h_bytes = kFcHM * kFcBK * 4;       // one M = 128 half of it
     static constexpr int w_bytes = 2 * N * kFcBK * 4;       // [W_hi rows ; W_lo rows] of this k-block
     static constexpr int stage_bytes = a_bytes + w_bytes;
     static constexpr int acc_cols = 2 * N;                  // one accumulator: cols [0,N) main + x_lo term, [N,2N) W_lo term
-    static constexpr int tmem_cols = 2 * nacc * acc_cols;   // two tile buffers: 512 columns for both N
+    static constexpr int tmem_cols = 2 * 2 * nacc * acc_cols;  // two tile buffers x two halves: 512 columns for both N
     static constexpr size_t smem = 1024 /*alignment slack*/ + (size_t)stages * stage_bytes +
                                    (size_t)lo_bufs * a_bytes + 256 /*barriers*/;
 };
+// Why 256-row tiles: the W' tiles are re-fetched from L2 for every x tile, and with 128-row tiles that was 8 KB of W'
+// per 16 KB of x -- 460 MB through the L2-to-SM fabric for 307 MB of x, which is what bounded the first version
+// (0.106 ms whether x came from HBM or sat in L2; ablations with conversion and MMAs switched off: 0.094 ms).
 // Why several accumulators: the tensor core adds into its fp32 accumulator with truncation, so one accumulator
 // taking all 2 * H/8 additions of a row drifts by ~1e-5 at H = 800, |logit| ~ 3 (measured against the reference in
 // fp64).  Dealing the k-blocks round-robin to nacc accumulators and adding those once, rounded, in the epilogue
@@ -133,6 +143,10 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m
         ::"r"(smem_u32(smem_dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
         : "memory");
 }
+// hint: bring `bytes` (multiple of 16) contiguous bytes at the 16-byte-aligned `gptr` into L2
+__device__ __forceinline__ void l2_prefetch_bulk(const void *gptr, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -198,6 +212,7 @@ __host__ __device__ constexpr uint32_t fc_idesc(int M, int N) {
 }
 
 struct FcParams {
+    const float *x;        // [rows][H] (also behind map_x): whole rows are prefetched into L2 one tile ahead
     long long rows;        // T * B
     int rows_per_cta;      // CTA c owns rows [c * rows_per_cta, (c+1) * rows_per_cta): equal HBM bytes per SM
     int T, B, H, C;
@@ -210,7 +225,7 @@ struct FcParams {
 
 // ---------------------------------------------------------------- the logits kernel
 // Persistent: one CTA per SM; CTA c owns the rows [c * rows_per_cta, (c + 1) * rows_per_cta) and walks them in tiles
-// of 128.  Its last tile is usually partial: it is loaded with 32-row boxes (a second tensor map), so every SM moves
+// of 256 (two UMMA M = 128 halves).  Its last tile is usually partial: it is loaded with 32-row boxes (a second tensor map), so every SM moves
 // the same number of bytes (whole 128-row tiles dealt round-robin left 10 of 148 SMs with a 6th tile: +18 %).  The
 // UMMA still runs on 128 rows; rows that were not loaded hold stale data and are never written out.
 // Pipelines (all mbarriers, no CTA-wide barrier after set-up):
@@ -228,8 +243,9 @@ __global__ void __launch_bounds__(kFcThreads, 1)
     constexpr int S = Cfg::stages, LB = Cfg::lo_bufs, NA = Cfg::nacc;
     extern __shared__ unsigned char fc_smem_raw[];
     // 128-byte swizzle: tile bases must be 1024-byte aligned
-    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(fc_smem_raw) + 1023) &
-                                                            ~(uintptr_t)1023);
+    // (as an offset from the shared array, so that the compiler keeps the shared address space: through a uintptr_t
+    // round trip every access below became a generic LD / ST)
+    unsigned char *smem = fc_smem_raw + ((1024u - (smem_u32(fc_smem_raw) & 1023u)) & 1023u);
     unsigned char *lo_base = smem + (size_t)S * Cfg::stage_bytes;
     uint64_t *bars = reinterpret_cast<uint64_t *>(lo_base + (size_t)LB * Cfg::a_bytes);
     uint64_t *full = bars, *empty = bars + S, *conv = bars + 2 * S, *lofree = conv + LB, *tfull = lofree + LB,
@@ -267,16 +283,34 @@ __global__ void __launch_bounds__(kFcThreads, 1)
     if (warp == 0) {
         // ============================================================ TMA producer (one lane)
         if (lane == 0) {
+            // A TMA box takes 128 bytes of each of 128 rows that lie 4*H bytes apart, and the next 128 bytes of a row
+            // follow a whole k-block later: left alone, HBM sees scattered 128-byte reads (measured: 39 % of its
+            // peak).  So whole ROWS of the next tile (4*H contiguous bytes each) are prefetched into L2 while the
+            // current tile is consumed -- DRAM reads become sequential and the boxes hit L2.  The prefetches are
+            // spread over the k-blocks of the current tile, so at most one tile per SM (~60 MB in all) waits in L2.
+            const uint32_t row_bytes = (uint32_t)p.H * 4u;
+            const bool pf = (row_bytes & 15u) == 0 && CTC_FC_L2_PREFETCH;
+            if (pf)
+                for (long long r = r0; r < min(r1, r0 + kFcBM); ++r) l2_prefetch_bulk(p.x + r * p.H, row_bytes);
             int s = 0, ph = 0;
+            const int koff = (int)((blockIdx.x * 7u) % (unsigned)nkb);
             for (long long row = r0; row < r1; row += kFcBM) {
                 const int nrows = (int)min((long long)kFcBM, r1 - row);
                 const int nbox = (nrows + 31) >> 5;  // 32-row boxes of a partial tile
-                for (int kb = 0; kb < nkb; ++kb) {
+                const int nnext = (int)max(0ll, min((long long)kFcBM, r1 - (row + kFcBM)));  // rows of the next tile
+                for (int kbi = 0; kbi < nkb; ++kbi) {
+                    // every CTA walks the k-blocks from its own starting point (the sum over k does not care): all
+                    // 148 CTAs fetching the SAME W' tile from the same L2 lines at the same moment was the limiter of
+                    // the first version (ablation: 94 us with conversion and MMAs switched off)
+                    const int kb = (kbi + koff) % nkb;
+                    if (pf)
+                        for (int i = kbi * nnext / nkb; i < (kbi + 1) * nnext / nkb; ++i)
+                            l2_prefetch_bulk(p.x + (row + kFcBM + i) * p.H, row_bytes);
                     mbar_wait(&empty[s], ph ^ 1);  // passes at once the first time round the ring
                     unsigned char *st = smem + (size_t)s * Cfg::stage_bytes;
                     if (nrows == kFcBM) {
                         mbar_arrive_expect_tx(&full[s], Cfg::a_bytes + Cfg::w_bytes);
-                        tma_load_2d(st, &map_x, kb * kFcBK, (int)row, &full[s]);  // x tile [128][32]
+                        tma_load_2d(st, &map_x, kb * kFcBK, (int)row, &full[s]);  // x tile [256][32]
                     } else {
                         mbar_arrive_expect_tx(&full[s], nbox * 32 * kFcBK * 4 + Cfg::w_bytes);
                         for (int j = 0; j < nbox; ++j)  // 32 rows = 4 swizzle atoms of 1024 bytes
@@ -290,7 +324,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
     } else if (warp == 1) {
         // ============================================================ MMA issuer (one lane)
         if (lane == 0) {
-            constexpr uint32_t idesc2 = fc_idesc(kFcBM, 2 * N), idesc1 = fc_idesc(kFcBM, N);
+            constexpr uint32_t idesc2 = fc_idesc(kFcHM, 2 * N), idesc1 = fc_idesc(kFcHM, N);
             int s = 0, ph = 0, it = 0;
             unsigned g = 0;  // k-blocks issued so far (x_lo buffer = g % LB)
             for (long long row = r0; row < r1; row += kFcBM, ++it) {
@@ -302,16 +336,20 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                     mbar_wait(&full[s], ph);
                     mbar_wait(&conv[j], (g / LB) & 1);
                     tc_fence_after();
-                    const uint32_t d = tmem_base + (uint32_t)((buf * NA + kb % NA) * Cfg::acc_cols);
                     const uint32_t sa = smem_u32(smem + (size_t)s * Cfg::stage_bytes);
-                    const uint64_t da = fc_smem_desc(sa), dw = fc_smem_desc(sa + Cfg::a_bytes),
-                                   dl = fc_smem_desc(smem_u32(lo_base + (size_t)j * Cfg::a_bytes));
+                    const uint32_t sl = smem_u32(lo_base + (size_t)j * Cfg::a_bytes);
+                    const uint64_t dw = fc_smem_desc(sa + Cfg::a_bytes);
 #pragma unroll
-                    for (int k = 0; k < kFcBK / kFcUmmaK; ++k) {
-                        const uint64_t o = (uint64_t)((k * kFcUmmaK * 4) >> 4);
-                        // the first k-block of each accumulator overwrites, everything else accumulates
-                        tc_mma_tf32(d, da + o, dw + o, idesc2, (kb >= NA || k > 0) ? 1u : 0u);  // x [W_hi | W_lo]^T
-                        tc_mma_tf32(d, dl + o, dw + o, idesc1, 1u);                              // x_lo W_hi^T
+                    for (int h = 0; h < 2; ++h) {  // the two M = 128 halves of the tile share the W' tile
+                        const uint32_t d = tmem_base + (uint32_t)(((buf * 2 + h) * NA + kb % NA) * Cfg::acc_cols);
+                        const uint64_t da = fc_smem_desc(sa + h * Cfg::h_bytes), dl = fc_smem_desc(sl + h * Cfg::h_bytes);
+#pragma unroll
+                        for (int k = 0; k < kFcBK / kFcUmmaK; ++k) {
+                            const uint64_t o = (uint64_t)((k * kFcUmmaK * 4) >> 4);
+                            // the first k-block of each accumulator overwrites, everything else accumulates
+                            tc_mma_tf32(d, da + o, dw + o, idesc2, (kb >= NA || k > 0) ? 1u : 0u);  // x [W_hi | W_lo]^T
+                            tc_mma_tf32(d, dl + o, dw + o, idesc1, 1u);                              // x_lo W_hi^T
+                        }
                     }
                     tc_commit(&empty[s]);    // ring stage s may be refilled once these MMAs have read it
                     tc_commit(&lofree[j]);   // ... and x_lo buffer j rewritten
@@ -333,14 +371,20 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                 const float4 *a = reinterpret_cast<const float4 *>(smem + (size_t)s * Cfg::stage_bytes);
                 float4 *lo = reinterpret_cast<float4 *>(lo_base + (size_t)j * Cfg::a_bytes);
                 // elementwise, so the swizzled placement of the tile is irrelevant: same position in both tiles
+                // all loads first (the two tiles may alias as far as the compiler knows: written naively, every load
+                // waited for the previous store -- 8 dependent shared-memory round trips per k-block, which made this
+                // loop the critical chain of the whole kernel: ncu, profiles/r02_fc_ncu_summary.md)
+                constexpr int NV = Cfg::a_bytes / 16 / 128;
+                float4 v[NV];
 #pragma unroll
-                for (int i = 0; i < Cfg::a_bytes / 16 / 128; ++i) {
-                    const float4 v = a[ct + 128 * i];
+                for (int i = 0; i < NV; ++i) v[i] = a[ct + 128 * i];
+#pragma unroll
+                for (int i = 0; i < NV; ++i) {
                     float4 l;
-                    l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
-                    l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
-                    l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
-                    l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+                    l.x = v[i].x - __uint_as_float(__float_as_uint(v[i].x) & 0xffffe000u);
+                    l.y = v[i].y - __uint_as_float(__float_as_uint(v[i].y) & 0xffffe000u);
+                    l.z = v[i].z - __uint_as_float(__float_as_uint(v[i].z) & 0xffffe000u);
+                    l.w = v[i].w - __uint_as_float(__float_as_uint(v[i].w) & 0xffffe000u);
                     lo[ct + 128 * i] = l;
                 }
                 fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
@@ -357,7 +401,9 @@ __global__ void __launch_bounds__(kFcThreads, 1)
             const int buf = it & 1;
             mbar_wait(&tfull[buf], (it >> 1) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NA * Cfg::acc_cols);
+          for (int h = 0; h < 2; ++h) {
+            __syncwarp();  // lanes leave the previous half's body at different points; tcgen05.ld is warp-aligned
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((buf * 2 + h) * NA * Cfg::acc_cols);
             float v[N];
 #pragma unroll
             for (int c0 = 0; c0 < N; c0 += 32) {
@@ -374,9 +420,11 @@ __global__ void __launch_bounds__(kFcThreads, 1)
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[c0 + i] = acc[i] + __ldg(p.bias + c0 + i);
             }
-            tc_fence_before();
-            mbar_arrive(&tempty[buf]);  // accumulators are in registers: the MMA warp may reuse the buffer
-            const long long r = row + q * 32 + lane;
+            if (h == 1) {
+                tc_fence_before();
+                mbar_arrive(&tempty[buf]);  // accumulators are in registers: the MMA warp may reuse the buffer
+            }
+            const long long r = row + h * kFcHM + q * 32 + lane;
             if (r >= r1) continue;  // not this CTA's row (or past the end): never written
             if (p.logits) {
                 float *dst = p.logits + r * p.C;
@@ -406,15 +454,16 @@ __global__ void __launch_bounds__(kFcThreads, 1)
             uint4 *yd = reinterpret_cast<uint4 *>(p.y + ((size_t)b * p.T + t) * 2 * N);
 #pragma unroll
             for (int c = 0; c < N; c += 4) {
-                uint4 h, l;
-                float e = fmaxf(v[c] * inv, 1.17549435e-38f);     h.x = y_hi_word(e); l.x = y_lo_word(e);
-                e = fmaxf(v[c + 1] * inv, 1.17549435e-38f);       h.y = y_hi_word(e); l.y = y_lo_word(e);
-                e = fmaxf(v[c + 2] * inv, 1.17549435e-38f);       h.z = y_hi_word(e); l.z = y_lo_word(e);
-                e = fmaxf(v[c + 3] * inv, 1.17549435e-38f);       h.w = y_hi_word(e); l.w = y_lo_word(e);
-                if (bad) { h = make_uint4(0x7ff80000u, 0x7ff80000u, 0x7ff80000u, 0x7ff80000u); l = make_uint4(0, 0, 0, 0); }
-                yd[c / 4] = h;
+                uint4 hw, l;
+                float e = fmaxf(v[c] * inv, 1.17549435e-38f);     hw.x = y_hi_word(e); l.x = y_lo_word(e);
+                e = fmaxf(v[c + 1] * inv, 1.17549435e-38f);       hw.y = y_hi_word(e); l.y = y_lo_word(e);
+                e = fmaxf(v[c + 2] * inv, 1.17549435e-38f);       hw.z = y_hi_word(e); l.z = y_lo_word(e);
+                e = fmaxf(v[c + 3] * inv, 1.17549435e-38f);       hw.w = y_hi_word(e); l.w = y_lo_word(e);
+                if (bad) { hw = make_uint4(0x7ff80000u, 0x7ff80000u, 0x7ff80000u, 0x7ff80000u); l = make_uint4(0, 0, 0, 0); }
+                yd[c / 4] = hw;
                 yd[N / 4 + c / 4] = l;
             }
+          }
         }
     }
     // ---- teardown: everybody is done with TMEM before its owner frees it

@@ -16,10 +16,17 @@ sys.path.insert(0, ROOT)
 import b200ctc  # noqa: E402
 
 
-def main():
+def run():
+    """-> dict (one JSON-able record); importable from bench.py"""
     w = b200ctc.workloads.CONFIGS["headline_b64_t1500"]
     d = b200ctc.workloads.make(w, C=30, acts=False)
     T, B, H, C = w.T, w.B, 800, 30
+    if os.environ.get("FC_T"):  # experiment: another frame count (and FC_NOFLUSH=1: inputs stay in L2 between calls)
+        T = int(os.environ["FC_T"])
+        d["act_lens"].clamp_(max=T)
+        d["label_lens"].clamp_(max=max(1, T // 4))
+        d["labels"] = d["labels"][: int(d["label_lens"].sum())]
+    noflush = os.environ.get("FC_NOFLUSH") == "1"
     g = torch.Generator().manual_seed(5)
     x = torch.randn(T, B, H, generator=g).cuda()
     weight = ((torch.rand(C, H, generator=g) * 2 - 1) / H ** 0.5).cuda()
@@ -36,7 +43,7 @@ def main():
             fn()
         evs = []
         for _ in range(n):
-            for _ in range(6):
+            for _ in range(0 if noflush else 6):
                 flush.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(); fn(); e1.record()
@@ -76,7 +83,7 @@ def main():
     frames = T * B
     alg = frames * (4 * H + 4 * C)  # read x once, write the fp32 logits once
     alg_all = alg + int(al.sum().item()) * 8 * 32 + frames * 4
-    print(json.dumps({
+    return ({
         "kernel": "fc_logits_kernel<32>", "config": {"T": T, "B": B, "H": H, "C": C},
         "ms_logits_only": ms_logits, "ms_logits_emissions_path": ms_all, "ms_training_mode_batch_stats": ms_stats,
         "roofline": {"bound": "hbm", "alg_bytes": alg, "achieved": alg / (ms_logits * 1e-3) / 1e9, "peak": peak,
@@ -84,8 +91,8 @@ def main():
                      "frac_with_emissions": alg_all / (ms_all * 1e-3) / 1e9 / peak},
         "frames_per_s": frames / (ms_logits * 1e-3),
         "comparators": {"torch_batch_norm_plus_linear_fp32_ms": ms_torch, "torch_same_with_allow_tf32_ms": ms_torch_tf32},
-        "chain_layer_then_ctc_ms": {"logits_reread_by_criterion": ms_plain, "emission_rows_handed_over": ms_fused}}))
+        "chain_layer_then_ctc_ms": {"logits_reread_by_criterion": ms_plain, "emission_rows_handed_over": ms_fused}})
 
 
 if __name__ == "__main__":
-    main()
+    print(json.dumps(run()))

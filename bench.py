@@ -153,6 +153,37 @@ def run_reference(args, w):
     print(json.dumps(line))
 
 
+def bind_to_gpu_numa_node(torch, local_rank):
+    """Run this process (and first-touch its pinned buffers) on the CPU cores of the NUMA node the GPU hangs off,
+    as a production launcher would: with every rank on node 0 the host copies of the far-socket GPUs cross the
+    inter-socket link.  Best effort -- returns a note for the bench line."""
+    try:
+        bdf = torch.cuda.get_device_properties(local_rank).pci_bus_id if hasattr(
+            torch.cuda.get_device_properties(local_rank), "pci_bus_id") else None
+        if bdf is None:
+            import ctypes
+            buf = ctypes.create_string_buffer(32)
+            torch.cuda.cudart().cudaDeviceGetPCIBusId(buf, 32, local_rank)
+            bdf = buf.value.decode()
+        bdf = str(bdf).lower()
+        if len(bdf.split(":")[0]) == 8:
+            bdf = bdf[4:]
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return "gpu numa node unknown (single node?)"
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed:
+            return f"gpu on numa node {node}, none of its cores in this process's cpuset"
+        os.sched_setaffinity(0, allowed)
+        return f"bound to numa node {node} ({len(allowed)} cores)"
+    except Exception as exc:
+        return f"not bound ({type(exc).__name__})"
+
+
 class Bench:
     """One workload on this rank's GPU: the device-resident step, the per-kernel legs, the host-buffer (e2e) leg,
     the module leg and the torch comparator.  All timing: CUDA events on the launching stream, L2 flushed (256 MB
@@ -379,6 +410,7 @@ def run_b200(args, w):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa_note = bind_to_gpu_numa_node(torch, local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -525,7 +557,9 @@ def run_b200(args, w):
                 "notes": {"l2": "flushed (256 MB memset) between timed steps",
                           "lengths": "device-resident (no host sync in the step)",
                           "launch": "length-bucket slices on side streams (CTC_B200_SLICES)",
-                          "loss_exchange": exchange},
+                          "loss_exchange": exchange, "host_numa": numa_note,
+                          "batch_order": "longest first, as the reference's collate function emits batches "
+                                         "(data_loader_aug.py:527)"},
                 "roofline": roofline_block(w, d, ms_per_step, prep_ms, eng_ms, grad_ms, peak, peak_kind),
                 "cpu_baseline": cpu,
                 "e2e": {"value": e2e_fps, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},

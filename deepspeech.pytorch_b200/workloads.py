@@ -36,8 +36,13 @@ HEADLINE = "headline_b64_t1500"
 
 
 def make(w: Workload, seed: int = 1234, sigma: float = 1.0, B: Optional[int] = None, C: Optional[int] = None,
-         no_repeats: bool = False, acts: bool = True):
-    """-> dict(acts fp32 [T,B,C] | None, labels int32 [sum L], act_lens int32 [B], label_lens int32 [B])."""
+         no_repeats: bool = False, acts: bool = True, sort_by_length: bool = True):
+    """-> dict(acts fp32 [T,B,C] | None, labels int32 [sum L], act_lens int32 [B], label_lens int32 [B]).
+
+    sort_by_length (default): utterances are ordered longest first, which is the order every batch of the reference
+    has -- its collate function sorts by spectrogram length (data/data_loader_aug.py:527
+    `batch = sorted(batch, key=lambda sample: sample[0].size(1), reverse=True)`).  The draw itself is unchanged (the
+    same utterances as with sort_by_length=False, permuted; the logits are i.i.d., so they need no permutation)."""
     g = torch.Generator().manual_seed(seed)
     B = w.B if B is None else B
     C = w.C if C is None else C
@@ -57,6 +62,11 @@ def make(w: Workload, seed: int = 1234, sigma: float = 1.0, B: Optional[int] = N
                 if labels[i] == labels[i - 1]:
                     labels[i] = 1 + (int(labels[i]) % (C - 1))  # next class, wraps within 1..C-1
             off += n
+    if sort_by_length:
+        order = torch.argsort(act_lens, descending=True, stable=True)
+        offs = torch.cumsum(label_lens, 0) - label_lens
+        labels = torch.cat([labels[int(offs[b]):int(offs[b]) + int(label_lens[b])] for b in order.tolist()])
+        act_lens, label_lens = act_lens[order].contiguous(), label_lens[order].contiguous()
     a = torch.randn(T, B, C, generator=g) * sigma if acts else None
     return {"acts": a, "labels": labels, "act_lens": act_lens, "label_lens": label_lens, "T": T, "B": B, "C": C}
 

@@ -158,16 +158,8 @@ def bind_to_gpu_numa_node(torch, local_rank):
     as a production launcher would: with every rank on node 0 the host copies of the far-socket GPUs cross the
     inter-socket link.  Best effort -- returns a note for the bench line."""
     try:
-        bdf = torch.cuda.get_device_properties(local_rank).pci_bus_id if hasattr(
-            torch.cuda.get_device_properties(local_rank), "pci_bus_id") else None
-        if bdf is None:
-            import ctypes
-            buf = ctypes.create_string_buffer(32)
-            torch.cuda.cudart().cudaDeviceGetPCIBusId(buf, 32, local_rank)
-            bdf = buf.value.decode()
-        bdf = str(bdf).lower()
-        if len(bdf.split(":")[0]) == 8:
-            bdf = bdf[4:]
+        pr = torch.cuda.get_device_properties(local_rank)
+        bdf = "%04x:%02x:%02x.0" % (int(pr.pci_domain_id), int(pr.pci_bus_id), int(pr.pci_device_id))
         node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
         if node < 0:
             return "gpu numa node unknown (single node?)"

@@ -117,7 +117,8 @@ struct Plan {
     size_t smem_engine_req;  // dynamic shared memory REQUESTED for an engine CTA (>= smem_engine, see make_plan)
     int numax;   // reduction units per utterance (small alphabets)
     size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_tlab, o_coff, o_labels, o_llen, o_alen;
-    size_t o_Pm2, o_Pe2;
+    size_t o_Pm2, o_Pe2, o_est;
+    int two_part;          // 1: recursions run in two launches with the early gradient blocks in between
     int cluster;           // 1: engines run as 2-CTA clusters (more than 4 lattice warps, see ctc_engine2c_kernel)
     size_t smem_engine_c;  // dynamic shared memory of one CTA of such a cluster
     size_t total;
@@ -163,6 +164,14 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     // itself.  CTC_B200_CLUSTER=0 keeps everything in one CTA (A/B measurements).
     pl->cluster = (nwl > 4 && !engine_first_form(B) && env_int("CTC_B200_CLUSTER", 1) != 0) ? 1 : 0;
     pl->smem_engine_c = engine_smem(pl->Cp, (nwl + 1) / 2).total;
+    // Two-part recursion (engine_phase_range; second engine form, one CTA per utterance and direction): OFF by default.
+    // CTC_B200_TWO_PART=2 runs the two parts back to back (bit-identical results: test_two_part_recursion_...).
+    // Measured on the headline: the split costs 8.7 us of the recursion (pipeline drain + refill + launch: 132.2 ->
+    // 140.9 us), and a work-conserving model of the slices on this batch says that starting the gradient of the middle
+    // time blocks at 3/4 of each recursion can bring the end of the step forward by at most ~10 us (185 -> 175 us
+    // modelled, before the part-2 engine CTAs have to queue behind resident gradient CTAs for registers) -- so the
+    // mid-point P kernel, the gradient kernel's block filter and the second set of streams were not built.
+    pl->two_part = (!engine_first_form(B) && !pl->cluster && pl->nblk >= 16) ? env_int("CTC_B200_TWO_PART", 0) : 0;
     {
         // Length-bucket slices: up to kMaxSlices, each at least kMinSliceB utterances.  CTC_B200_SLICES overrides.
         int ns = B / kMinSliceB;
@@ -185,6 +194,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->o_ckB = o;    o = align256(o + ck);
     pl->o_ckAE = o;   o = align256(o + ckE);
     pl->o_ckBE = o;   o = align256(o + ckE);
+    pl->o_est = o;    o = align256(o + sizeof(double) * (size_t)B * 2 * kEngStateFields * NT);
     pl->o_Pm2 = o;    o = align256(o + sizeof(double) * 2 * B);
     pl->o_Pe2 = o;    o = align256(o + sizeof(int) * 2 * B);
     pl->o_Pm = o;     o = align256(o + sizeof(double) * B);
@@ -356,7 +366,14 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
             else if (pl.cluster)
                 ctc_engine2c_kernel<kK, CP><<<2 * (pk.score_only ? nb : 2 * nb), ((pl.nwl + 1) / 2 + 1) * 32,
                                               pl.smem_engine_c, s>>>(pk);
-            else
+            else if (pl.two_part && !pk.score_only) {
+                CtcParams p1 = pk, p2 = pk;
+                p1.phase = 1;
+                p2.phase = 2;
+                ctc_engine2_kernel<kK, CP><<<2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(p1);
+                ctc_engine2_kernel<kK, CP><<<2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(p2);
+                ++*launches;
+            } else
                 ctc_engine2_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
         },
@@ -449,7 +466,14 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         else if (pl.cluster)
             ctc_engine2c_kernel<kK, CP><<<2 * (pk.score_only ? nb : 2 * nb), ((pl.nwl + 1) / 2 + 1) * 32,
                                           pl.smem_engine_c, s>>>(pk);
-        else
+        else if (pl.two_part && !pk.score_only) {
+            CtcParams p1 = pk, p2 = pk;
+            p1.phase = 1;
+            p2.phase = 2;
+            ctc_engine2_kernel<kK, CP><<<2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(p1);
+            ctc_engine2_kernel<kK, CP><<<2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(p2);
+            ++*launches;
+        } else
             ctc_engine2_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
         ++*launches;
     };
@@ -598,6 +622,7 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.ckB = reinterpret_cast<int *>(ws + pl.o_ckB);
     p.ckAE = reinterpret_cast<int *>(ws + pl.o_ckAE);
     p.ckBE = reinterpret_cast<int *>(ws + pl.o_ckBE);
+    p.est = reinterpret_cast<double *>(ws + pl.o_est);
     p.Pm2 = reinterpret_cast<double *>(ws + pl.o_Pm2);
     p.Pe2 = reinterpret_cast<int *>(ws + pl.o_Pe2);
     p.Pm = reinterpret_cast<double *>(ws + pl.o_Pm);

@@ -75,6 +75,8 @@ struct CtcParams {
     int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
     int nan_to_zero;    // 1: a NaN logit is read as 0 (the reference's train.py:595-598 guard, folded into the softmax pass)
     int *nan_count;     // optional: += number of NaN logits seen in valid frames (nan_to_zero only)
+    int phase;          // second engine form: 0 = whole recursion; 1 / 2 = its first / second part (engine_phase_range)
+    double *est;        // [B][2 directions][12][NT]: per-thread state handed from part 1 to part 2
     int y_ready;        // 1: the emission rows y were written by fc_logits_kernel; the row blocks only zero padding grads
 #ifdef CTC_PROFILE
     long long *dbg;     // [ctas][16 warps][8] clock counters (tools/ubench/engine_bench.cu only)
@@ -1022,12 +1024,28 @@ __device__ __forceinline__ void beta_steps(Cells<K> &c, double &pr0, double &pr1
     }
 }
 
+// Two-part recursion.  A time block's gradient needs the alpha checkpoint at its start and the beta checkpoint at its
+// end; both exist once each direction has passed the block, i.e. at max(x, 1 - x) of the recursion for a block at
+// relative position x.  So the engines can be run in two launches -- groups [0, cut) of each direction's processing
+// order, then [cut, n) -- and the gradient kernel launched in between for the blocks that are already complete (the
+// middle half for cut = 3/4 n) runs under the second part instead of queueing up behind the whole recursion.  The
+// systolic schedule restarts cleanly: every warp re-enters at its own super-step and all a thread carries across is
+// its 8 mantissas, exponent, inflow scale and inflow values (kept in full fp64, so the two-part recursion is
+// bit-identical to the one-part one).  Utterances with fewer than 8 groups do everything in part 1.
+__host__ __device__ inline int engine_phase_cut(int ngroups) { return ngroups >= 8 ? (3 * ngroups + 3) / 4 : ngroups; }
+__host__ __device__ inline void engine_phase_range(int phase, int ngroups, int &jb, int &je) {
+    const int cut = engine_phase_cut(ngroups);
+    jb = phase == 2 ? cut : 0;
+    je = phase == 1 ? cut : ngroups;
+}
+constexpr int kEngStateFields = 12;  // a[8], pr0, pr1, f, E
+
 // the lattice warps of one direction.  CL: the utterance's lattice warps are split over the two CTAs of a cluster
 // (`warp` is then the CTA-local index, lk.gw0 + warp the global one); nwa = lattice warps the utterance needs in all.
 template <int K, int CP, bool FWD, bool CL>
 __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int warp, int lane, int nwa, int Tb, int S,
                                                unsigned *ytile, int NS, SlotRing *rings, double *pm, int *pe,
-                                               const EngLink &lk) {
+                                               const EngLink &lk, int jb = 0, int je = -1) {
     constexpr int Cp = CP;
     const int NT = p.nwl * 32;
     const int gw = CL ? lk.gw0 + warp : warp;      // global lattice warp
@@ -1035,7 +1053,8 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
     const int nbar = (nwa_l + 1) * 32;
     const int thread = gw * 32 + lane;  // lattice thread index; owns states [thread*K, thread*K+K)
     const int ngroups = (Tb + kGroup - 1) / kGroup;
-    const int nsuper = ngroups + nwa_l - 1;
+    if (je < 0) je = ngroups;  // groups [jb, je) of this direction's processing order
+    const int nsuper = (je - jb) + nwa_l - 1;
     int idx[K / 2], lab_i[K / 2];
     double skipA[K / 2], skipB[K / 2];
     decode_tlab<K>(p.tlab[(size_t)b * NT + thread], idx, skipA, skipB, lab_i, false, 0);
@@ -1081,6 +1100,16 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
             pr1 = 0.0;
         }
     }
+    double *est = nullptr;
+    if (!CL && p.est) est = p.est + ((size_t)b * 2 + (FWD ? 0 : 1)) * kEngStateFields * NT + thread;
+    if (!CL && jb > 0) {  // second part: continue from the state part 1 left
+#pragma unroll
+        for (int k = 0; k < K; ++k) c.a[k] = est[(size_t)k * NT];
+        pr0 = est[(size_t)8 * NT];
+        pr1 = est[(size_t)9 * NT];
+        f = est[(size_t)10 * NT];
+        c.E = (int)est[(size_t)11 * NT];
+    }
     named_bar_sync(1, nbar);
     for (int i = 0; i < q; ++i) named_bar_sync(1, nbar);
 
@@ -1090,7 +1119,7 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
     // checkpoints: alpha after row t0+7 -> block G+1 ; beta_{t0} -> block G-1 (see ctc_engine_kernel)
     int *ck = (FWD ? p.ckA : p.ckB) + (size_t)b * p.nblk * NT * K;
     int *ckE = (FWD ? p.ckAE : p.ckBE) + (size_t)b * p.nblk * NT;
-    const int cb0 = FWD ? 1 : ngroups - 2;
+    const int cb0 = FWD ? 1 + jb : ngroups - 2 - jb;
     int4 *ckp = reinterpret_cast<int4 *>(ck + ((ptrdiff_t)cb0 * NT + gw * 32) * K) + lane;
     int *ckEp = ckE + (ptrdiff_t)cb0 * NT + thread;
     const ptrdiff_t ckstep = (FWD ? 1 : -1) * (ptrdiff_t)NT * (K / 4), ckEstep = (FWD ? 1 : -1) * (ptrdiff_t)NT;
@@ -1099,10 +1128,11 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
     // emission values of the first row this direction visits
     YRow<K> y;
     {
-        const int nr0 = FWD ? (ngroups == 1 ? ntail : kGroup) : ntail;  // rows of the first group processed
+        const int G0 = FWD ? jb : ngroups - 1 - jb;                 // first group processed here
+        const int nr0 = (G0 == ngroups - 1) ? ntail : kGroup;       // its rows
         load_y<K, CP>(y, yt, FWD ? 0 : nr0 - 1, blank, idx);
     }
-    for (int j = 0; j < ngroups; ++j) {
+    for (int j = jb; j < je; ++j) {
         const bool tail = FWD ? (j == ngroups - 1) : (j == 0);
         const int nr = tail ? ntail : kGroup;
         // slots of this group's rows: the j-th group this direction processes uses half (j & 1) of a ring; the
@@ -1170,7 +1200,7 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
             yt += kGroup * 2 * Cp;
             if (++st == NS) { st = 0; yt = ytile; }
 #ifndef CTC_V2_NOPREFETCH
-            load_y<K, CP>(y, yt, FWD ? 0 : kGroup - 1, blank, idx);
+            if (j + 1 < je) load_y<K, CP>(y, yt, FWD ? 0 : kGroup - 1, blank, idx);  // (the next part loads its own)
 #endif
         } else if (FWD) {
             // ---- P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2): the owning threads publish (mantissa, exponent)
@@ -1187,10 +1217,18 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
         }
         named_bar_sync(1, nbar);
 #ifdef CTC_V2_NOPREFETCH
-        if (j < ngroups - 1) load_y<K, CP>(y, yt, FWD ? 0 : kGroup - 1, blank, idx);
+        if (j + 1 < je) load_y<K, CP>(y, yt, FWD ? 0 : kGroup - 1, blank, idx);
 #endif
     }
-    for (int i = q + ngroups; i < nsuper; ++i) named_bar_sync(1, nbar);
+    for (int i = q + (je - jb); i < nsuper; ++i) named_bar_sync(1, nbar);
+    if (!CL && je < ngroups) {  // first part: hand the state to the second
+#pragma unroll
+        for (int k = 0; k < K; ++k) est[(size_t)k * NT] = c.a[k];
+        est[(size_t)8 * NT] = pr0;
+        est[(size_t)9 * NT] = pr1;
+        est[(size_t)10 * NT] = f;
+        est[(size_t)11 * NT] = (double)c.E;
+    }
 }
 
 // cost and p(l|x) of one utterance from the published (mantissa, exponent) pairs of alpha_{T-1}(S-1), alpha_{T-1}(S-2)
@@ -1230,9 +1268,11 @@ __device__ __forceinline__ void engine_finish(const CtcParams &p, int b, int S, 
 template <int CP, bool CL>
 __device__ __forceinline__ void engine_producer(const CtcParams &p, int b, bool fwd, int lane, int nwa_l, int Tb,
                                                 unsigned *ytile, uint64_t *y_full, int NS, const EngLink &lk,
-                                                bool xrecv, bool xsend) {
+                                                bool xrecv, bool xsend, int jb = 0, int je = -1) {
     constexpr int Cp = CP;
-    const int ngroups = (Tb + kGroup - 1) / kGroup;
+    const int ngroups_all = (Tb + kGroup - 1) / kGroup;
+    if (je < 0) je = ngroups_all;
+    const int ngroups = je - jb;  // tiles of this launch: tile j is group jb + j of the direction's processing order
     const int nsuper = ngroups + nwa_l - 1;
     const int nbar = (nwa_l + 1) * 32;
     const uint32_t full_l = CL ? lk.xbars : 0u, empty_l = CL ? lk.xbars + 8 * kXSlots : 0u;
@@ -1265,7 +1305,7 @@ __device__ __forceinline__ void engine_producer(const CtcParams &p, int b, bool 
         const int st = ist;
         ist = (ist + 1 == NS) ? 0 : ist + 1;
         if (j < ngroups && lane == 0) {
-            const int G = fwd ? j : (ngroups - 1 - j);
+            const int G = fwd ? (jb + j) : (ngroups_all - 1 - (jb + j));
             const int t0 = G * kGroup;
             const int nr = min(kGroup, Tb - t0);
             mbar_arrive_expect_tx(&y_full[st], rowbytes * nr);
@@ -1319,7 +1359,7 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine2_kerne
     const int nwa = min(nwl, (S + 32 * K - 1) / (32 * K));  // lattice warps this utterance needs
 
     if (Tb == 0) {  // nothing to recurse over
-        if (fwd && tid == 0) {
+        if (fwd && tid == 0 && p.phase != 2) {
             const bool ok = (L == 0);
             p.feas[b] = ok;
             p.Pm[b] = 1.0;
@@ -1329,17 +1369,21 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine2_kerne
         return;
     }
     if (warp >= nwa && warp != nwl) return;  // lattice warps beyond this utterance's S
+    const int ngroups = (Tb + kGroup - 1) / kGroup;
+    int jb, je;
+    engine_phase_range(p.phase, ngroups, jb, je);
+    if (jb >= je) return;  // second part of an utterance that did everything in the first
     if (warp == nwl) {
         const EngLink nolink = {0, 0, nwa, 0u, 0u, nullptr, nullptr};
-        engine_producer<CP, false>(p, b, fwd, lane, nwa, Tb, ytile, y_full, NS, nolink, false, false);
+        engine_producer<CP, false>(p, b, fwd, lane, nwa, Tb, ytile, y_full, NS, nolink, false, false, jb, je);
         return;
     }
     const EngLink nolink = {0, 0, nwa, 0u, 0u, nullptr, nullptr};
     if (fwd)
-        engine_lattice<K, CP, true, false>(p, b, warp, lane, nwa, Tb, S, ytile, NS, rings, pm, pe, nolink);
+        engine_lattice<K, CP, true, false>(p, b, warp, lane, nwa, Tb, S, ytile, NS, rings, pm, pe, nolink, jb, je);
     else
-        engine_lattice<K, CP, false, false>(p, b, warp, lane, nwa, Tb, S, ytile, NS, rings, pm, pe, nolink);
-    if (fwd && tid == 0) engine_finish(p, b, S, pm[0], pe[0], pm[1], pe[1]);
+        engine_lattice<K, CP, false, false>(p, b, warp, lane, nwa, Tb, S, ytile, NS, rings, pm, pe, nolink, jb, je);
+    if (fwd && tid == 0 && je == ngroups) engine_finish(p, b, S, pm[0], pe[0], pm[1], pe[1]);
 }
 
 // Long label sequences (more than 4 lattice warps, L > 511): the lattice warps of one (utterance, direction) are split

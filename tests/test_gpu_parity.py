@@ -850,3 +850,22 @@ def test_cluster_engine_matches_single_cta_engine(oracle, b200, monkeypatch):
     assert np.array_equal(c0, c1) and np.array_equal(g0, g1)
     ce, _ = _run(b200, d, want_grads=False)  # score-only launch: alpha clusters only
     assert np.array_equal(ce, c1)
+
+
+def test_two_part_recursion_is_bit_identical(oracle, b200, monkeypatch):
+    # the recursion kernels can run in two launches (3/4 + 1/4 of each direction's groups, per-thread state handed over
+    # in full fp64; an off-by-default switch, see make_plan): costs and gradients must not change by a bit
+    for name, kw in (("headline_b64_t1500", {}), ("cpu_b16_t500", {"B": 40, "seed": 3})):
+        d = _wl(b200, name, **kw)
+        d["act_lens"][-1] = 57   # fewer than 8 groups: everything in part 1
+        d["act_lens"][-2] = 64   # exactly 8 groups
+        d["act_lens"][-3] = 129  # ragged last group
+        d["label_lens"][-3:] = torch.tensor([20, 9, 7], dtype=torch.int32)
+        d["labels"] = d["labels"][: int(d["label_lens"].sum())]
+        monkeypatch.setenv("CTC_B200_TWO_PART", "0")
+        c0, g0 = _run(b200, d)
+        monkeypatch.setenv("CTC_B200_TWO_PART", "2")
+        c2, g2 = _run(b200, d)
+        assert np.array_equal(c0, c2) and np.array_equal(g0, g2), name
+        monkeypatch.delenv("CTC_B200_TWO_PART")
+        _check(oracle, b200, d)

@@ -130,13 +130,13 @@ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     if (T < 0 || B < 1 || C < 2 || Lmax < 0) return false;
     pl->big = C > kMaxSmallC;
-    if (pl->big && Lmax > 255) return false;  // position-indexed emission rows: 1 + L <= 256 (this build)
+    if (pl->big && Lmax > 511) return false;  // position-indexed emission rows: 1 + L <= 512 (this build)
     const int S = 2 * Lmax + 1;
     const int nwl = (S + 32 * kK - 1) / (32 * kK);
     if (nwl > kMaxLatticeWarps) return false;  // label length > 1023
     pl->nwl = nwl;
     pl->Lmax = Lmax;
-    pl->Cp = pl->big ? 256 : (C <= 32 ? 32 : (C <= 64 ? 64 : 128));
+    pl->Cp = pl->big ? (Lmax <= 255 ? 256 : 512) : (C <= 32 ? 32 : (C <= 64 ? 64 : 128));
     const int NT = nwl * 32;
     // one checkpoint per group of 8 time steps: the grad kernel then never renormalises or re-settles exponents
     const int R = kGroup;
@@ -392,9 +392,9 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
 // full occupancy (6 CTAs/SM: 0.357 ms, 5: 0.41, 4: 0.46), so either the lattice kernels wait for free slots until the
 // row kernel drains, or (with priorities) they take the slots and the rows slow down by more than the recursion hides;
 // the gradient kernel's scattered reductions also disturb the streaming.
+template <int CP>
 cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
                        cudaEvent_t costs_ready, const LossOut &loss_sum) {
-    constexpr int CP = 256;
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -461,7 +461,7 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
         rows_at(pk, nb, s);
     };
     auto eng = [&](const CtcParams &pk, int nb, cudaStream_t s) {
-        if (engine_first_form(pk.B))
+        if (CP < 512 && engine_first_form(pk.B))  // (the first form's producer keeps the fixed tile look-ahead)
             ctc_engine_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
         else if (pl.cluster)
             ctc_engine2c_kernel<kK, CP><<<2 * (pk.score_only ? nb : 2 * nb), ((pl.nwl + 1) / 2 + 1) * 32,
@@ -489,7 +489,9 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
 
 cudaError_t launch_all(const CtcParams &p, const Plan &pl, cudaStream_t st, int phase_mask, int *launches,
                        cudaEvent_t costs_ready, const LossOut &loss_sum) {
-    if (pl.big) return launch_big(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
+    if (pl.big)
+        return pl.Cp == 256 ? launch_big<256>(p, pl, st, phase_mask, launches, costs_ready, loss_sum)
+                            : launch_big<512>(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
     switch (pl.Cp) {
         case 32: return launch_all_cp<32>(p, pl, st, phase_mask, launches, costs_ready, loss_sum);
         case 64: return launch_all_cp<64>(p, pl, st, phase_mask, launches, costs_ready, loss_sum);

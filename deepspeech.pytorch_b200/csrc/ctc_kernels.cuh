@@ -425,11 +425,22 @@ __device__ __forceinline__ void decode_tlab(const uint4 tl, int (&idx)[K / 2], d
     }
 }
 
+// Large alphabets index their emission rows by label POSITION (0: blank, 1 + i: label i); the table's 8-bit field
+// cannot hold positions beyond 255, and the position follows from the lattice thread index anyway (thread e owns
+// labels 4e .. 4e+3), so it is recomputed here.
+template <int K>
+__device__ __forceinline__ void position_idx(const uint4 tl, int e, int (&idx)[K / 2]) {
+#pragma unroll
+    for (int h = 0; h < K / 2; ++h) idx[h] = ((tl.y >> (8 + h)) & 1) ? 1 + 4 * e + h : 0;
+}
+
 // ================================================================================================ engine
 #ifndef CTC_LOOKAHEAD
 #define CTC_LOOKAHEAD 4
 #endif
 constexpr int kLookAhead = CTC_LOOKAHEAD;  // emission tiles in flight ahead of the first lattice warp
+// ... except at pitch 512 (large alphabets with 255 < L <= 511): a tile is 32 KB there, so one tile ahead
+__host__ __device__ constexpr int look_ahead(int Cp) { return Cp >= 512 ? 1 : kLookAhead; }
 
 struct EngineSmem {
     size_t ytile, bars, slots, misc, xlink, total;
@@ -437,7 +448,7 @@ struct EngineSmem {
 };
 __host__ __device__ inline EngineSmem engine_smem(int Cp, int nwl) {
     EngineSmem s;
-    s.nstage = nwl + kLookAhead + 1;
+    s.nstage = nwl + look_ahead(Cp) + 1;
     size_t o = 0;
     s.ytile = o; o = align16(o + sizeof(unsigned) * s.nstage * kGroup * 2 * Cp);
     s.bars = o;  o = align16(o + sizeof(uint64_t) * s.nstage);
@@ -661,6 +672,7 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
     double skipA[K / 2], skipB[K / 2];
     decode_tlab<K>(p.tlab[(size_t)b * NT + (K == 8 ? thread : (thread >> 1))], idx, skipA, skipB, lab_i, false,
                    thread & 1);
+    if (K == 8 && p.big) position_idx<K>(p.tlab[(size_t)b * NT + thread], thread, idx);
     (void)lab_i;
     (void)C;
 
@@ -1057,7 +1069,11 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
     const int nsuper = (je - jb) + nwa_l - 1;
     int idx[K / 2], lab_i[K / 2];
     double skipA[K / 2], skipB[K / 2];
-    decode_tlab<K>(p.tlab[(size_t)b * NT + thread], idx, skipA, skipB, lab_i, false, 0);
+    {
+        const uint4 tl = p.tlab[(size_t)b * NT + thread];
+        decode_tlab<K>(tl, idx, skipA, skipB, lab_i, false, 0);
+        if (p.big) position_idx<K>(tl, thread, idx);
+    }
     (void)lab_i;
     const int blank = p.bpos;
 
@@ -1321,14 +1337,15 @@ __device__ __forceinline__ void engine_producer(const CtcParams &p, int b, bool 
             ++nwaited;
         }
     };
-    for (int j = 0; j <= kLookAhead; ++j) issue(j);
+    constexpr int LA = look_ahead(CP);
+    for (int j = 0; j <= LA; ++j) issue(j);
     wait_tile();  // tile 0
     wait_tile();  // tile 1: its first row is read during super-step 0
     link_before(0);
     named_bar_sync(1, nbar);
     for (int i = 0; i < nsuper; ++i) {
         fence_proxy_async();
-        issue(i + kLookAhead + 1);
+        issue(i + LA + 1);
         wait_tile();  // tile i + 2
         link_before(i + 1);
         named_bar_sync(1, nbar);
@@ -1650,6 +1667,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
         uint4 tl = make_uint4(0x01010101u * (unsigned)p.bpos, 0u, 0u, 0u);
         if (valid_e) tl = p.tlab[(size_t)b * NT + e];
         decode_tlab<K>(tl, idx, skipA, skipB, lpos, core);
+        if (BIG && valid_e) position_idx<K>(tl, e, idx);
     }
     const double invP = 1.0 / p.Pm[b];
     const int eP = p.Pe[b];

@@ -869,3 +869,23 @@ def test_two_part_recursion_is_bit_identical(oracle, b200, monkeypatch):
         assert np.array_equal(c0, c2) and np.array_equal(g0, g2), name
         monkeypatch.delenv("CTC_B200_TWO_PART")
         _check(oracle, b200, d)
+
+
+@pytest.mark.parametrize("C,Lmax", [(700, 300), (5000, 400), (1000, 511)])
+def test_large_alphabet_long_labels(oracle, b200, C, Lmax):
+    # C > 128 with label sequences beyond 255 symbols (a BPE target at T = 1000 easily is): emission rows indexed by
+    # label position at pitch 512, positions derived from the lattice thread index.  Ragged batch: one utterance at the
+    # limit, short ones that stay below 256, repeats, an infeasible one.
+    T, B = 1100, 6
+    g = torch.Generator().manual_seed(C + Lmax)
+    acts = torch.randn(T, B, C, generator=g) * 1.5
+    ll = torch.tensor([Lmax, 256, 255, 12, Lmax - 37, 600 if Lmax > 500 else 300], dtype=torch.int32).clamp(max=Lmax)
+    act_lens = torch.tensor([T, T - 3, 900, 40, 2 * (Lmax - 37) + 5, int(ll[5]) - 1], dtype=torch.int32)  # last: L > T
+    labels = torch.randint(1, C, (int(ll.sum()),), generator=g, dtype=torch.int32)
+    labels[5:9] = labels[4]  # a run of repeats inside the long utterance
+    d = {"acts": acts, "labels": labels, "act_lens": act_lens, "label_lens": ll}
+    costs, grads = _check(oracle, b200, d)
+    assert costs[5] == 0.0 and np.all(grads[:, 5] == 0)
+    _check(oracle, b200, d, device_lens=True, grad_scale=0.5)
+    ce, _ = _run(b200, d, want_grads=False)
+    assert np.array_equal(ce, costs)

@@ -40,7 +40,8 @@ def test_workspace_query_is_shape_only(b200):
     assert lib.ctc_b200_workspace_size(1500, 128, 29, 450, None, ctypes.byref(n)) == 0 and n.value > small
     assert lib.ctc_b200_workspace_size(4000, 32, 29, 600, None, ctypes.byref(n)) == 0    # long targets
     assert lib.ctc_b200_workspace_size(1000, 64, 5000, 200, None, ctypes.byref(n)) == 0   # large alphabet
-    assert lib.ctc_b200_workspace_size(1000, 64, 5000, 300, None, ctypes.byref(n)) == 2   # ... needs L <= 255
+    assert lib.ctc_b200_workspace_size(1000, 64, 5000, 300, None, ctypes.byref(n)) == 0   # pitch-512 emission rows
+    assert lib.ctc_b200_workspace_size(1000, 64, 5000, 512, None, ctypes.byref(n)) == 2   # ... needs L <= 511
     assert lib.ctc_b200_workspace_size(10, 0, 29, 5, None, ctypes.byref(n)) == 2          # B < 1
     assert lib.ctc_b200_workspace_size(10, 1, 1, 5, None, ctypes.byref(n)) == 2           # C < 2
     assert lib.ctc_b200_workspace_size(10, 1, 29, 5, None, None) == 2

@@ -350,8 +350,11 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
     cudaError_t e = cudaSuccess;
     if (!(phase_mask & 4) && p.T > 0) {
         const long long rows = (long long)p.T * p.B;
-        const int nrb = (int)((rows + kPrepRows - 1) / kPrepRows);
-        ctc_prep_kernel<<<nrb + p.B + (pl.nslices > 1 ? 1 : 0), kPrepRows, pl.smem_prep, st>>>(p);
+        const int nrb = (int)((rows + kPrepRowsCta - 1) / kPrepRowsCta);
+        static const int prep_dbg = env_int("CTC_B200_PREP_DBG", 0);  // timing experiment: 1 = table blocks only,
+        CtcParams pp = p;                                             // 2 = softmax row blocks only
+        pp.prep_dbg = prep_dbg;
+        ctc_prep_kernel<<<nrb + p.B + (pl.nslices > 1 ? 1 : 0), kPrepRows, pl.smem_prep, st>>>(pp);
         ++*launches;
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;

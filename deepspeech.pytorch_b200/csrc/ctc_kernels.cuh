@@ -77,6 +77,7 @@ struct CtcParams {
     int *nan_count;     // optional: += number of NaN logits seen in valid frames (nan_to_zero only)
     int phase;          // second engine form: 0 = whole recursion; 1 / 2 = its first / second part (engine_phase_range)
     double *est;        // [B][2 directions][12][NT]: per-thread state handed from part 1 to part 2
+    int prep_dbg;       // timing experiments (CTC_B200_PREP_DBG): 1 = row blocks return at once, 2 = table blocks do
     int y_ready;        // 1: the emission rows y were written by fc_logits_kernel; the row blocks only zero padding grads
 #ifdef CTC_PROFILE
     long long *dbg;     // [ctas][16 warps][8] clock counters (tools/ubench/engine_bench.cu only)
@@ -120,10 +121,11 @@ __host__ __device__ inline int grad_max_units(int C, int Lmax, int nqmax) {
 }
 
 // ================================================================================================ prep
-constexpr int kPrepRows = 128;
+constexpr int kPrepRows = 128;    // THREADS of a prep CTA (the name dates from the round-1 one-thread-per-row softmax)
+constexpr int kPrepRowsCta = 32;  // softmax rows per row block: 4x the warps in flight of 128-row blocks
 
 __host__ __device__ inline size_t prep_smem(int C, int Lmax) {
-    const size_t rows = align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows;
+    const size_t rows = 0;  // (the row blocks no longer stage anything in shared memory)
     const size_t utt = 2 * sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1);  // sorted positions + staged labels
     return (rows > utt ? rows : utt) + sizeof(int) * (C + 2) + 64;  // >= 4 * B bytes (sort block): see make_plan
 }
@@ -299,14 +301,15 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int C = p.C, Cp = p.Cp;
     const long long nrows_total = (long long)p.T * p.B;
-    const int nrb = (int)((nrows_total + kPrepRows - 1) / kPrepRows);
-    const size_t rows_bytes = align16(sizeof(float) * kPrepRows * C) + sizeof(float) * 2 * kPrepRows;
+    const int nrb = (int)((nrows_total + kPrepRowsCta - 1) / kPrepRowsCta);
+    const size_t rows_bytes = 0;
     const size_t utt_bytes = 2 * sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
     int *cnt = reinterpret_cast<int *>(smem + (rows_bytes > utt_bytes ? rows_bytes : utt_bytes));
 
     // The utterance / sort blocks are long dependent chains of small loads: they take the LOWEST block indices so that
     // they are scheduled first and run under the softmax blocks instead of forming the tail of the launch.
     const int nextra = (int)gridDim.x - nrb;  // B utterance blocks (+1 sort block when the launch is sliced)
+    if (p.prep_dbg && ((int)blockIdx.x < nextra) == (p.prep_dbg == 2)) return;
     if ((int)blockIdx.x < nextra) {
         if ((int)blockIdx.x == p.B)
             sort_by_length(p, reinterpret_cast<int *>(smem));
@@ -317,8 +320,8 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
     }
     // ---------------------------------------------------- row block: softmax of 128 consecutive (t,b) rows
     float *xs = reinterpret_cast<float *>(smem);
-    const long long row0 = (long long)((int)blockIdx.x - nextra) * kPrepRows;
-    const int nrows = (int)min((long long)kPrepRows, nrows_total - row0);
+    const long long row0 = (long long)((int)blockIdx.x - nextra) * kPrepRowsCta;
+    const int nrows = (int)min((long long)kPrepRowsCta, nrows_total - row0);
     if (p.y_ready) {
         // the emission rows came with the logits (fc_logits_kernel's epilogue): the logits are not read at all; what
         // is left of this block's work is the zero gradient of its padding frames
@@ -330,80 +333,90 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
             }
         return;
     }
-    const float *src = p.acts + row0 * C;
-    const int n = nrows * C;
-    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
-        const float4 *s4 = reinterpret_cast<const float4 *>(src);
-        float4 *d4 = reinterpret_cast<float4 *>(xs);
-        const int n4 = n >> 2;
-        for (int i = tid; i < n4; i += kPrepRows) d4[i] = __ldg(s4 + i);
-        for (int i = (n4 << 2) + tid; i < n; i += kPrepRows) xs[i] = __ldg(src + i);
-    } else {
-        for (int i = tid; i < n; i += kPrepRows) xs[i] = __ldg(src + i);
-    }
-    __syncthreads();
-    // Cp / 4 lanes per row (8 for C <= 32), 4 adjacent classes per lane: max and sum by shuffles inside the lane group,
-    // every exp evaluated once, the emission row written as two 16-byte stores per lane.
+    // Rows straight from global memory, no shared-memory stage (round 1 staged the 128 rows, synchronised the CTA and
+    // then made 8 dependent passes per warp: 18.6 us for 11 MB in / 25 MB out on the headline, and this kernel is on
+    // the critical path of every step).  Cp / 4 lanes per row (8 for C <= 32), 4 adjacent classes per lane; the loads
+    // of TWO passes are issued before the first is consumed; max and sum by shuffles inside the lane group, every exp
+    // evaluated once, the emission row written as two 16-byte stores per lane.
+    (void)xs;
     const int lpr = Cp >> 2, rpw = 32 / lpr;  // lanes per row, rows per warp pass
     const int j = lane & (lpr - 1);
-    for (int r0 = warp * rpw; r0 < nrows; r0 += (kPrepRows / 32) * rpw) {
-        const int r = r0 + lane / lpr;
-        const bool valid = r < nrows;
-        const long long row = row0 + (valid ? r : 0);
-        const int t = (int)(row / p.B), b = (int)(row - (long long)t * p.B);
-        const bool active = valid && t < min(max(p.act_lens[b], 0), p.T);
-        float x[4];
+    constexpr int U = 2;
+    const int stride = (kPrepRows / 32) * rpw;
+    for (int r0 = warp * rpw; r0 < nrows; r0 += U * stride) {
+        float xv[U][4];
+        int tt[U], bb[U], al[U];
+        bool vv[U];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) x[i] = (valid && 4 * j + i < C) ? xs[r * C + 4 * j + i] : -INFINITY;
-        if (p.nan_to_zero) {
-            int nn = 0;
+        for (int u = 0; u < U; ++u) {
+            const int r = r0 + u * stride + lane / lpr;
+            vv[u] = r < nrows && (r0 + u * stride) < nrows;
+            const long long row = row0 + (vv[u] ? r : 0);
+            tt[u] = (int)(row / p.B);
+            bb[u] = (int)(row - (long long)tt[u] * p.B);
+            al[u] = vv[u] ? __ldg(p.act_lens + bb[u]) : 0;
+            const float *src = p.acts + row * C + 4 * j;
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (x[i] != x[i]) { x[i] = 0.f; ++nn; }
-            if (nn && active && p.nan_count) atomicAdd(p.nan_count, nn);
+            for (int i = 0; i < 4; ++i) xv[u][i] = (vv[u] && 4 * j + i < C) ? __ldg(src + i) : -INFINITY;
         }
-        float m = fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3]));
-        for (int d = 1; d < lpr; d <<= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
-        if (!valid) m = 0.f;
-        if (p.path != nullptr) {
-            // best path: first class attaining the row maximum, from the values already in
-            // registers -- the decoder needs no second read of the logits
-            int cand = 0x7fffffff;
 #pragma unroll
-            for (int i = 3; i >= 0; --i)
-                if (x[i] == m) cand = 4 * j + i;
-            for (int d = 1; d < lpr; d <<= 1) cand = min(cand, __shfl_xor_sync(kFull, cand, d));
-            if (active && j == 0) p.path[(size_t)b * p.T + t] = cand;
-        }
-        float e[4];
+        for (int u = 0; u < U; ++u) {
+            if ((r0 + u * stride) >= nrows) break;  // warp-uniform
+            const bool valid = vv[u];
+            const int t = tt[u], b = bb[u];
+            const long long row = (long long)t * p.B + b;
+            const bool active = valid && t < min(max(al[u], 0), p.T);
+            float x[4] = {xv[u][0], xv[u][1], xv[u][2], xv[u][3]};
+            if (p.nan_to_zero) {
+                int nn = 0;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) e[i] = (4 * j + i < C) ? expf(x[i] - m) : 0.f;
-        float sum = (e[0] + e[1]) + (e[2] + e[3]);
-        for (int d = 1; d < lpr; d <<= 1) sum += __shfl_xor_sync(kFull, sum, d);
-        const float inv = 1.0f / sum;
-        if (active) {
-            // y clamped to >= 2^-126: a feasible alignment never gets probability exactly 0 from fp32 underflow
-            unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * Cp;  // utterance-major: a tile of rows is one bulk copy
-            uint4 hi, lo;
-            float v = fmaxf(e[0] * inv, 1.17549435e-38f); hi.x = y_hi_word(v); lo.x = y_lo_word(v);
-            v = fmaxf(e[1] * inv, 1.17549435e-38f); hi.y = y_hi_word(v); lo.y = y_lo_word(v);
-            v = fmaxf(e[2] * inv, 1.17549435e-38f); hi.z = y_hi_word(v); lo.z = y_lo_word(v);
-            v = fmaxf(e[3] * inv, 1.17549435e-38f); hi.w = y_hi_word(v); lo.w = y_lo_word(v);
-            if (sum != sum) {
-                // a NaN or +Inf logit (not scrubbed by nan_to_zero) makes the row sum NaN: the whole row becomes NaN
-                // and propagates through the recursions into cost and gradient of this utterance, as it would in
-                // the reference's criterion (whose caller then reports it, train.py:604-611) -- never a finite
-                // wrong value (fmaxf would have returned the clamp)
-                hi = make_uint4(kNanHi, kNanHi, kNanHi, kNanHi);
-                lo = make_uint4(0u, 0u, 0u, 0u);
+                for (int i = 0; i < 4; ++i)
+                    if (x[i] != x[i]) { x[i] = 0.f; ++nn; }
+                if (nn && active && p.nan_count) atomicAdd(p.nan_count, nn);
             }
-            *reinterpret_cast<uint4 *>(ydst + 4 * j) = hi;
-            *reinterpret_cast<uint4 *>(ydst + Cp + 4 * j) = lo;
-        } else if (valid && p.grads) {
-            // padding frame (t >= act_lens[b]): never read by the lattice kernels; its gradient row is zero
+            float m = fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3]));
+            for (int d = 1; d < lpr; d <<= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
+            if (!valid) m = 0.f;
+            if (p.path != nullptr) {
+                // best path: first class attaining the row maximum, from the values already in
+                // registers -- the decoder needs no second read of the logits
+                int cand = 0x7fffffff;
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (4 * j + i < C) p.grads[row * C + 4 * j + i] = 0.f;
+                for (int i = 3; i >= 0; --i)
+                    if (x[i] == m) cand = 4 * j + i;
+                for (int d = 1; d < lpr; d <<= 1) cand = min(cand, __shfl_xor_sync(kFull, cand, d));
+                if (active && j == 0) p.path[(size_t)b * p.T + t] = cand;
+            }
+            float e[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) e[i] = (4 * j + i < C) ? expf(x[i] - m) : 0.f;
+            float sum = (e[0] + e[1]) + (e[2] + e[3]);
+            for (int d = 1; d < lpr; d <<= 1) sum += __shfl_xor_sync(kFull, sum, d);
+            const float inv = 1.0f / sum;
+            if (active) {
+                // y clamped to >= 2^-126: a feasible alignment never gets probability exactly 0 from fp32 underflow
+                unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * Cp;  // utterance-major: a tile of rows is one bulk copy
+                uint4 hi, lo;
+                float v = fmaxf(e[0] * inv, 1.17549435e-38f); hi.x = y_hi_word(v); lo.x = y_lo_word(v);
+                v = fmaxf(e[1] * inv, 1.17549435e-38f); hi.y = y_hi_word(v); lo.y = y_lo_word(v);
+                v = fmaxf(e[2] * inv, 1.17549435e-38f); hi.z = y_hi_word(v); lo.z = y_lo_word(v);
+                v = fmaxf(e[3] * inv, 1.17549435e-38f); hi.w = y_hi_word(v); lo.w = y_lo_word(v);
+                if (sum != sum) {
+                    // a NaN or +Inf logit (not scrubbed by nan_to_zero) makes the row sum NaN: the whole row becomes NaN
+                    // and propagates through the recursions into cost and gradient of this utterance, as it would in
+                    // the reference's criterion (whose caller then reports it, train.py:604-611) -- never a finite
+                    // wrong value (fmaxf would have returned the clamp)
+                    hi = make_uint4(kNanHi, kNanHi, kNanHi, kNanHi);
+                    lo = make_uint4(0u, 0u, 0u, 0u);
+                }
+                *reinterpret_cast<uint4 *>(ydst + 4 * j) = hi;
+                *reinterpret_cast<uint4 *>(ydst + Cp + 4 * j) = lo;
+            } else if (valid && p.grads) {
+                // padding frame (t >= act_lens[b]): never read by the lattice kernels; its gradient row is zero
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (4 * j + i < C) p.grads[row * C + 4 * j + i] = 0.f;
+            }
         }
     }
 }

@@ -67,7 +67,7 @@ int main(int argc, char **argv) {
     printf("B=%d T=%d C=%d Lmax=%d nwl=%d R=%d smem prep %zu engine %zu grad %zu\n", B, T, C, Lmax, p.nwl, R, s_prep, s_eng, s_grad);
     cudaEvent_t e[4];
     for (auto &x : e) cudaEventCreate(&x);
-    const int nrb = (int)(((long long)T * B + kPrepRows - 1) / kPrepRows);
+    const int nrb = (int)(((long long)T * B + kPrepRowsCta - 1) / kPrepRowsCta);
     float best[3] = {1e9, 1e9, 1e9};
     for (int it = 0; it < 6; ++it) {
         cudaEventRecord(e[0]);

@@ -88,15 +88,17 @@ int env_int(const char *name, int dflt) {
 // Two forms of the recursion kernel.  The second (ctc_engine2_kernel) has the shorter dependent chain per group and
 // wins whenever an engine CTA has an SM to itself (B=64: 137 against 157 us; B=32,T=4000: 346 against 394); the first
 // issues fewer instructions per step (its warp-edge accesses are branches, not predicated instructions on all lanes)
-// and wins once several engine CTAs share an SM and the kernel is bound by issue slots instead of latency (B=256: 259
-// against 270 us, B=1024: 731 against 790).  CTC_B200_ENGINE=1 / 2 forces one form (A/B measurements); 0 = by batch.
+// and wins once three or more engine CTAs share an SM and the kernel is bound by issue slots instead of latency (B=256:
+// 259 against 270 us, B=1024: 731 against 790).  CTC_B200_ENGINE=1 / 2 forces one form (A/B measurements); 0 = by batch.
 int engine_version() {
     static const int v = env_int("CTC_B200_ENGINE", 0);
     return v;
 }
 inline bool engine_first_form(int B) {
     const int v = engine_version();
-    return v == 1 || (v == 0 && 2 * B > 160);  // more engine CTAs than SMs (148): throughput-bound
+    // measured crossover (T=1500, C=29, us, first / second form): B=96 192 / 154, B=128 192 / 164, B=160 188 / 168,
+    // B=192 236 / 207, B=256 259 / 270, B=1024 731 / 790
+    return v == 1 || (v == 0 && B > 224);
 }
 
 struct Plan {

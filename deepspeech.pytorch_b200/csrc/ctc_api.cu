@@ -836,6 +836,14 @@ extern "C" ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H
         return CTC_B200_STATUS_EXECUTION_FAILED;
     FcParams fp;
     fp.x = x;
+    fp.trace = nullptr;
+    static const bool fc_trace = env_int("CTC_FC_TRACE", 0) != 0;  // diagnostic: synchronises and prints
+    static long long *trace_dev = nullptr;
+    if (fc_trace) {
+        if (!trace_dev) cudaMalloc((void **)&trace_dev, sizeof(long long) * kFcTraceK * 8);
+        cudaMemsetAsync(trace_dev, 0, sizeof(long long) * kFcTraceK * 8, st);
+        fp.trace = trace_dev;
+    }
     fp.rows = rows; fp.T = T; fp.B = B; fp.H = H; fp.C = C;
     fp.bias = bias;
     fp.logits = logits;
@@ -852,6 +860,17 @@ extern "C" ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H
     fp.rows_per_cta = (int)per;
     cudaError_t e = pl.N == 32 ? fc_launch<32>(mx, mx32, mw, fp, grid, st) : fc_launch<64>(mx, mx32, mw, fp, grid, st);
     ++g_last_launches;
+    if (fc_trace && e == cudaSuccess) {
+        static long long h[kFcTraceK * 8];
+        cudaStreamSynchronize(st);
+        cudaMemcpy(h, trace_dev, sizeof(h), cudaMemcpyDeviceToHost);
+        const long long t0 = h[0];
+        fprintf(stderr, "[fc trace] k-block: producer-issue | conv: lo-free tile-landed done | mma: tile-landed lo-ready committed  (clk after first issue)\n");
+        for (int g = 0; g < kFcTraceK && h[g * 8]; ++g)
+            fprintf(stderr, "[fc trace] %3d: %7lld | %7lld %7lld %7lld | %7lld %7lld %7lld\n", g, h[g * 8] - t0,
+                    h[g * 8 + 1] - t0, h[g * 8 + 2] - t0, h[g * 8 + 3] - t0, h[g * 8 + 4] - t0, h[g * 8 + 5] - t0,
+                    h[g * 8 + 6] - t0);
+    }
     return e == cudaSuccess ? CTC_B200_STATUS_SUCCESS : CTC_B200_STATUS_EXECUTION_FAILED;
 }
 

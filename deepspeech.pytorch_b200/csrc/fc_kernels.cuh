@@ -34,13 +34,15 @@ constexpr int kFcBM = 256;      // rows (frames) per tile: two UMMA M = 128 halv
 constexpr int kFcHM = 128;      // UMMA M
 constexpr int kFcBK = 32;       // fp32 columns per k-block = one 128-byte swizzle row
 constexpr int kFcUmmaK = 8;     // tf32 elements per tcgen05.mma
-constexpr int kFcThreads = 320; // warp 0: TMA producer, warp 1: TMEM owner + MMA issuer, 2-5: converters, 6-9: epilogue
+constexpr int kFcThreads = 352; // warp 0: TMA producer, warp 1: TMEM owner + MMA issuer of tile half 0, 2-5: converters,
+                                // 6-9: epilogue, warp 10: MMA issuer of tile half 1
 
 template <int N>
 struct FcCfg {
     static_assert(N == 32 || N == 64, "classes are padded to 32 or 64");
     static constexpr int stages = N == 32 ? 4 : 3;          // TMA ring: x tile + W' tiles of one k-block per stage
-    static constexpr int lo_bufs = 2;                       // x_lo tiles (converter -> MMA), outside the TMA ring
+    static constexpr int lo_bufs = 2;                       // x_lo tiles (converter -> MMA), outside the TMA ring (3 buffers
+                                                            // + 3 ring stages measured: the ring runs dry, 0.101 vs 0.098 ms)
     static constexpr int nacc = N == 32 ? 2 : 1;            // accumulators per half tile, k-blocks dealt round-robin
     static constexpr int a_bytes = kFcBM * kFcBK * 4;       // 32 KB: x tile (also the size of an x_lo tile)
     static constexpr int h_bytes = kFcHM * kFcBK * 4;       // one M = 128 half of it
@@ -221,7 +223,28 @@ struct FcParams {
     unsigned *y;           // CTC emission rows [B][T][2*N] (planar fp64 words, see ctc_prep_kernel) or nullptr
     const int *act_lens;   // with y: rows t >= act_lens[b] are skipped (nullptr: every row is written)
     int *path;             // optional [B][T]: argmax class of every frame (greedy best path by-product)
+    long long *trace;      // diagnostic (CTC_FC_TRACE): CTA 0 records clock64 per role and k-block, [kFcTraceK][8]
 };
+constexpr int kFcTraceK = 96;
+__device__ __forceinline__ long long fc_clk() { long long c; asm volatile("mov.u64 %0, %%clock64;" : "=l"(c)); return c; }
+#define FC_TRACE(slot, g) do { if (p.trace && blockIdx.x == 0 && (g) < (unsigned)kFcTraceK) p.trace[(g) * 8 + (slot)] = fc_clk(); } while (0)
+
+// 32 x 32 transpose across a warp: on entry lane r holds v[c] = M[r][c], on exit lane c holds v[r] = M[r][c].
+// Five butterfly stages of 16 shuffles, register indices static.
+__device__ __forceinline__ void warp_transpose32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+        const bool up = (lane & s) != 0;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            if ((i & s) == 0) {
+                const float give = up ? v[i] : v[i + s];
+                const float got = __shfl_xor_sync(kFull, give, s);
+                if (up) v[i] = got; else v[i + s] = got;
+            }
+        }
+    }
+}
 
 // ---------------------------------------------------------------- the logits kernel
 // Persistent: one CTA per SM; CTA c owns the rows [c * rows_per_cta, (c + 1) * rows_per_cta) and walks them in tiles
@@ -230,10 +253,10 @@ struct FcParams {
 // UMMA still runs on 128 rows; rows that were not loaded hold stale data and are never written out.
 // Pipelines (all mbarriers, no CTA-wide barrier after set-up):
 //   full[s]   TMA -> converters + MMA : ring stage s holds the x tile and the W' tiles of a k-block     (1 arrival + tx)
-//   empty[s]  MMA -> TMA              : the MMAs reading stage s have completed (tcgen05.commit)              (1)
+//   empty[s]  MMA -> TMA              : the MMAs reading stage s have completed (tcgen05.commit x 2 issuers)  (2)
 //   conv[j]   converters -> MMA       : x_lo buffer j is written (and fenced to the async proxy)              (128)
-//   lofree[j] MMA -> converters       : the MMAs reading x_lo buffer j have completed (tcgen05.commit)        (1)
-//   tfull[b]  MMA -> epilogue         : tile buffer b holds a finished tile (tcgen05.commit)                  (1)
+//   lofree[j] MMA -> converters       : the MMAs reading x_lo buffer j have completed (tcgen05.commit x 2)    (2)
+//   tfull[b]  MMA -> epilogue         : tile buffer b holds a finished tile (tcgen05.commit x 2)              (2)
 //   tempty[b] epilogue -> MMA         : tile buffer b has been read out                                       (128)
 template <int N>
 __global__ void __launch_bounds__(kFcThreads, 1)
@@ -259,14 +282,14 @@ __global__ void __launch_bounds__(kFcThreads, 1)
     if (tid == 0) {
         for (int s = 0; s < S; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], 1);
+            mbar_init(&empty[s], 2);   // one tcgen05.commit from each of the two MMA issuers
         }
         for (int j = 0; j < LB; ++j) {
             mbar_init(&conv[j], 128);
-            mbar_init(&lofree[j], 1);
+            mbar_init(&lofree[j], 2);
         }
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&tfull[b], 1);
+            mbar_init(&tfull[b], 2);
             mbar_init(&tempty[b], 128);
         }
         fence_mbar_init();
@@ -293,6 +316,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
             if (pf)
                 for (long long r = r0; r < min(r1, r0 + kFcBM); ++r) l2_prefetch_bulk(p.x + r * p.H, row_bytes);
             int s = 0, ph = 0;
+            unsigned gp = 0;
             const int koff = (int)((blockIdx.x * 7u) % (unsigned)nkb);
             for (long long row = r0; row < r1; row += kFcBM) {
                 const int nrows = (int)min((long long)kFcBM, r1 - row);
@@ -307,6 +331,8 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                         for (int i = kbi * nnext / nkb; i < (kbi + 1) * nnext / nkb; ++i)
                             l2_prefetch_bulk(p.x + (row + kFcBM + i) * p.H, row_bytes);
                     mbar_wait(&empty[s], ph ^ 1);  // passes at once the first time round the ring
+                    FC_TRACE(0, gp);  // producer: slot free, about to issue
+                    ++gp;
                     unsigned char *st = smem + (size_t)s * Cfg::stage_bytes;
                     if (nrows == kFcBM) {
                         mbar_arrive_expect_tx(&full[s], Cfg::a_bytes + Cfg::w_bytes);
@@ -321,8 +347,12 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                 }
             }
         }
-    } else if (warp == 1) {
-        // ============================================================ MMA issuer (one lane)
+    } else if (warp == 1 || warp == 10) {
+        // ============================================================ MMA issuers (one lane each): warp 1 issues the
+        // MMAs of the tile's first M = 128 half, warp 10 those of the second.  One thread issuing all 16 MMAs of a
+        // k-block was the bottleneck of the kernel (clock64 trace, CTC_FC_TRACE: ~70 clk per issue, 1165 clk per
+        // k-block against 670 for the converters); the halves have their own accumulators, so they need no ordering.
+        const int h = warp == 1 ? 0 : 1;
         if (lane == 0) {
             constexpr uint32_t idesc2 = fc_idesc(kFcHM, 2 * N), idesc1 = fc_idesc(kFcHM, N);
             int s = 0, ph = 0, it = 0;
@@ -334,13 +364,14 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                 for (int kb = 0; kb < nkb; ++kb, ++g) {
                     const int j = (int)(g % LB);
                     mbar_wait(&full[s], ph);
+                    if (h == 0) FC_TRACE(4, g);  // MMA: tile landed
                     mbar_wait(&conv[j], (g / LB) & 1);
+                    if (h == 0) FC_TRACE(5, g);  // MMA: x_lo ready
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + (size_t)s * Cfg::stage_bytes);
                     const uint32_t sl = smem_u32(lo_base + (size_t)j * Cfg::a_bytes);
                     const uint64_t dw = fc_smem_desc(sa + Cfg::a_bytes);
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {  // the two M = 128 halves of the tile share the W' tile
+                    {  // this issuer's M = 128 half of the tile (the halves share the W' tile)
                         const uint32_t d = tmem_base + (uint32_t)(((buf * 2 + h) * NA + kb % NA) * Cfg::acc_cols);
                         const uint64_t da = fc_smem_desc(sa + h * Cfg::h_bytes), dl = fc_smem_desc(sl + h * Cfg::h_bytes);
 #pragma unroll
@@ -353,6 +384,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                     }
                     tc_commit(&empty[s]);    // ring stage s may be refilled once these MMAs have read it
                     tc_commit(&lofree[j]);   // ... and x_lo buffer j rewritten
+                    if (h == 0) FC_TRACE(6, g);  // MMA: issued + committed
                     if (++s == S) { s = 0; ph ^= 1; }
                 }
                 tc_commit(&tfull[buf]);
@@ -367,7 +399,9 @@ __global__ void __launch_bounds__(kFcThreads, 1)
             for (int kb = 0; kb < nkb; ++kb, ++g) {
                 const int j = (int)(g % LB);
                 mbar_wait(&lofree[j], ((g / LB) & 1) ^ 1);  // passes at once for the first LB k-blocks
+                if (ct == 0) FC_TRACE(1, g);  // converter: x_lo buffer free
                 mbar_wait(&full[s], ph);
+                if (ct == 0) FC_TRACE(2, g);  // converter: tile landed
                 const float4 *a = reinterpret_cast<const float4 *>(smem + (size_t)s * Cfg::stage_bytes);
                 float4 *lo = reinterpret_cast<float4 *>(lo_base + (size_t)j * Cfg::a_bytes);
                 // elementwise, so the swizzled placement of the tile is irrelevant: same position in both tiles
@@ -389,6 +423,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                 }
                 fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
                 mbar_arrive(&conv[j]);
+                if (ct == 0) FC_TRACE(3, g);  // converter: done
                 if (++s == S) { s = 0; ph ^= 1; }
             }
         }
@@ -424,14 +459,26 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                 tc_fence_before();
                 mbar_arrive(&tempty[buf]);  // accumulators are in registers: the MMA warp may reuse the buffer
             }
-            const long long r = row + h * kFcHM + q * 32 + lane;
-            if (r >= r1) continue;  // not this CTA's row (or past the end): never written
+            const long long rw = row + h * kFcHM + q * 32;  // first row of this warp's 32
+            const long long r = rw + lane;
             if (p.logits) {
-                float *dst = p.logits + r * p.C;
+                // The warp's 32 rows x C logits are one contiguous block of memory.  One thread storing its row as C
+                // scalars makes every store instruction touch 32 different lines (7680 L1 wavefronts per tile on the
+                // load/store pipe the converters share: a 7 us stall at every tile boundary in the clock64 trace);
+                // transposed through shuffles, lane c holds column c and every store instruction writes ONE row.
 #pragma unroll
-                for (int c = 0; c < N; ++c)
-                    if (c < p.C) dst[c] = v[c];
+                for (int c0 = 0; c0 < N; c0 += 32) {
+                    float w[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) w[i] = v[c0 + i];
+                    warp_transpose32(w, lane);
+                    const int c = c0 + lane;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c < p.C && rw + i < r1) p.logits[(rw + i) * p.C + c] = w[i];
+                }
             }
+            if (r >= r1) continue;  // not this CTA's row (or past the end): never written
             if (p.y == nullptr && p.path == nullptr) continue;
             const int t = (int)(r / p.B), b = (int)(r - (long long)t * p.B);
             if (p.act_lens && t >= min(max(p.act_lens[b], 0), p.T)) continue;  // padding frame: never read

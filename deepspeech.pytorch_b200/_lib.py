@@ -44,7 +44,7 @@ class FcLayer(ctypes.Structure):
     _fields_ = [("weight", ctypes.c_void_p), ("bn_weight", ctypes.c_void_p), ("bn_bias", ctypes.c_void_p),
                 ("bn_mean", ctypes.c_void_p), ("bn_var", ctypes.c_void_p), ("bn_eps", ctypes.c_float),
                 ("bn_batch_stats", ctypes.c_int), ("batch_mean_out", ctypes.c_void_p),
-                ("batch_var_out", ctypes.c_void_p)]
+                ("batch_var_out", ctypes.c_void_p), ("reuse_folded", ctypes.c_int)]
 
 
 def _nvcc() -> str:

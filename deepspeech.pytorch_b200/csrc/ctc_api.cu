@@ -824,9 +824,11 @@ extern "C" ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H
         mean = m;
         var = v;
     }
-    fc_fold_kernel<<<pl.N, 256, 0, st>>>(layer->weight, layer->bn_weight, layer->bn_bias, mean, var, layer->bn_eps, H,
-                                         C, pl.N, W2, bias);
-    ++g_last_launches;
+    if (!(layer->reuse_folded && !layer->bn_batch_stats)) {
+        fc_fold_kernel<<<pl.N, 256, 0, st>>>(layer->weight, layer->bn_weight, layer->bn_bias, mean, var, layer->bn_eps,
+                                             H, C, pl.N, W2, bias);
+        ++g_last_launches;
+    }
     if (cudaGetLastError() != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
     CUtensorMap mx, mx32, mw;
     if (!make_map(&mx, x, (unsigned long long)rows, (unsigned long long)H, (unsigned long long)H * 4, kFcBM) ||
@@ -840,8 +842,8 @@ extern "C" ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H
     static const bool fc_trace = env_int("CTC_FC_TRACE", 0) != 0;  // diagnostic: synchronises and prints
     static long long *trace_dev = nullptr;
     if (fc_trace) {
-        if (!trace_dev) cudaMalloc((void **)&trace_dev, sizeof(long long) * kFcTraceK * 8);
-        cudaMemsetAsync(trace_dev, 0, sizeof(long long) * kFcTraceK * 8, st);
+        if (!trace_dev) cudaMalloc((void **)&trace_dev, sizeof(long long) * (kFcTraceK * 8 + 2 * 256));
+        cudaMemsetAsync(trace_dev, 0, sizeof(long long) * (kFcTraceK * 8 + 2 * 256), st);
         fp.trace = trace_dev;
     }
     fp.rows = rows; fp.T = T; fp.B = B; fp.H = H; fp.C = C;
@@ -858,14 +860,48 @@ extern "C" ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H
     if (per < 32) per = 32;
     const int grid = (int)((rows + per - 1) / per);
     fp.rows_per_cta = (int)per;
-    cudaError_t e = pl.N == 32 ? fc_launch<32>(mx, mx32, mw, fp, grid, st) : fc_launch<64>(mx, mx32, mw, fp, grid, st);
+    // CTC_FC_TS=1 (C <= 32): the TS form -- A operands written to TMEM by the converters (tcgen05.st) and read from
+    // there by the tensor core, half the shared-memory traffic.  Measured equal to the SS form (0.083 against 0.082 ms)
+    // with one accumulator per tile half instead of two (error 1.3e-5 against 7e-6), so the SS form is the default.
+    static const bool use_ts = env_int("CTC_FC_TS", 0) != 0;
+    cudaError_t e;
+    if (pl.N == 32 && use_ts) {
+        static bool ts_attr[64] = {false};
+        {
+            std::lock_guard<std::mutex> lock(g_attr_mu);
+            if (dev < 0 || dev >= 64 || !ts_attr[dev]) {
+                if (cudaFuncSetAttribute(fc_logits_ts_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)FcTsCfg<32>::smem) != cudaSuccess)
+                    return CTC_B200_STATUS_EXECUTION_FAILED;
+                if (dev >= 0 && dev < 64) ts_attr[dev] = true;
+            }
+        }
+        fc_logits_ts_kernel<32><<<grid, kFcThreads, FcTsCfg<32>::smem, st>>>(mx, mx32, mw, fp);
+        e = cudaGetLastError();
+    } else {
+        e = pl.N == 32 ? fc_launch<32>(mx, mx32, mw, fp, grid, st) : fc_launch<64>(mx, mx32, mw, fp, grid, st);
+    }
     ++g_last_launches;
     if (fc_trace && e == cudaSuccess) {
-        static long long h[kFcTraceK * 8];
+        static long long h[kFcTraceK * 8 + 2 * 256];
         cudaStreamSynchronize(st);
         cudaMemcpy(h, trace_dev, sizeof(h), cudaMemcpyDeviceToHost);
         const long long t0 = h[0];
         fprintf(stderr, "[fc trace] k-block: producer-issue | conv: lo-free tile-landed done | mma: tile-landed lo-ready committed  (clk after first issue)\n");
+        {
+            long long b0 = h[kFcTraceK * 8], e0 = 0, emin = 1ll << 62;
+            for (int c = 0; c < grid && c < 256; ++c) {
+                b0 = h[kFcTraceK * 8 + 2 * c] < b0 ? h[kFcTraceK * 8 + 2 * c] : b0;
+                e0 = h[kFcTraceK * 8 + 2 * c + 1] > e0 ? h[kFcTraceK * 8 + 2 * c + 1] : e0;
+                emin = h[kFcTraceK * 8 + 2 * c + 1] < emin ? h[kFcTraceK * 8 + 2 * c + 1] : emin;
+            }
+            fprintf(stderr, "[fc trace] CTAs: first start 0, first end %.1f us, last end %.1f us; per CTA (start,end us):",
+                    (emin - b0) * 1e-3, (e0 - b0) * 1e-3);
+            for (int c = 0; c < grid && c < 256; c += 9)
+                fprintf(stderr, " %d:(%.1f,%.1f)", c, (h[kFcTraceK * 8 + 2 * c] - b0) * 1e-3,
+                        (h[kFcTraceK * 8 + 2 * c + 1] - b0) * 1e-3);
+            fprintf(stderr, "\n");
+        }
         for (int g = 0; g < kFcTraceK && h[g * 8]; ++g)
             fprintf(stderr, "[fc trace] %3d: %7lld | %7lld %7lld %7lld | %7lld %7lld %7lld\n", g, h[g * 8] - t0,
                     h[g * 8 + 1] - t0, h[g * 8 + 2] - t0, h[g * 8 + 3] - t0, h[g * 8 + 4] - t0, h[g * 8 + 5] - t0,

@@ -302,6 +302,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (p.trace && tid == 0) p.trace[kFcTraceK * 8 + 2 * blockIdx.x] = (long long)global_ns();
 
     if (warp == 0) {
         // ============================================================ TMA producer (one lane)
@@ -516,10 +517,326 @@ __global__ void __launch_bounds__(kFcThreads, 1)
     // ---- teardown: everybody is done with TMEM before its owner frees it
     tc_fence_before();
     __syncthreads();
+    if (p.trace && tid == 0) p.trace[kFcTraceK * 8 + 2 * blockIdx.x + 1] = (long long)global_ns();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, Cfg::tmem_cols);
     }
 }
+
+
+// ---------------------------------------------------------------- TS form: A operands from TMEM
+// D[tmem] (+)= A[tmem] * B[smem]^T : A is M x 8 tf32 on lanes 0..M-1, 8 consecutive columns from `tmem_a`
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// 32 lanes x 32 consecutive 32-bit columns: thread `lane` of the warp writes its lane's 32 values
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+        "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+        "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+// TMEM (512 columns): [0, 256) accumulators -- tile buffer b, half h at (b*2 + h) * 2N (2N <= 64 ... 128: see smem
+// and column budget below); [256, 512) A operands -- k-block buffer j: x of half 0 / 1 at +0 / +32, x_lo at +64 / +96.
+template <int N>
+struct FcTsCfg {
+    static_assert(N == 32, "the TS form is built for classes padded to 32 (2 * 2 * 2N accumulator columns + 256)");
+    static constexpr int stages = 5;                        // TMA ring: x tile (32 KB) + W' tiles (8 KB) per stage
+    static constexpr int a_bytes = kFcBM * kFcBK * 4;
+    static constexpr int h_bytes = kFcHM * kFcBK * 4;
+    static constexpr int w_bytes = 2 * N * kFcBK * 4;
+    static constexpr int stage_bytes = a_bytes + w_bytes;
+    static constexpr int acc_cols = 2 * N;
+    static constexpr int tmem_cols = 512;
+    __host__ __device__ static constexpr int a_col(int j, int h) { return 256 + j * 128 + h * 32; }
+    static constexpr size_t smem = 1024 + (size_t)stages * stage_bytes + 256;
+};
+
+// The same kernel with the A operands in TMEM (see the converter role).  One accumulator per tile half (the TMEM
+// columns the second one used now hold the A operands).
+template <int N>
+__global__ void __launch_bounds__(kFcThreads, 1)
+    fc_logits_ts_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_x32,
+                     const __grid_constant__ CUtensorMap map_w, const FcParams p) {
+    using Cfg = FcTsCfg<N>;
+    constexpr int S = Cfg::stages, LB = 2, NA = 1;
+    extern __shared__ unsigned char fc_smem_raw[];
+    // 128-byte swizzle: tile bases must be 1024-byte aligned
+    // (as an offset from the shared array, so that the compiler keeps the shared address space: through a uintptr_t
+    // round trip every access below became a generic LD / ST)
+    unsigned char *smem = fc_smem_raw + ((1024u - (smem_u32(fc_smem_raw) & 1023u)) & 1023u);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)S * Cfg::stage_bytes);
+    uint64_t *full = bars, *empty = bars + S, *conv = bars + 2 * S, *lofree = conv + LB, *tfull = lofree + LB,
+             *tempty = tfull + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nkb = (p.H + kFcBK - 1) / kFcBK;
+    const long long r0 = (long long)blockIdx.x * p.rows_per_cta;
+    const long long r1 = min(p.rows, r0 + p.rows_per_cta);
+
+    if (tid == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 130);  // 128 converter threads have read the x tile + the two issuers' MMAs the W' tile
+        }
+        for (int j = 0; j < LB; ++j) {
+            mbar_init(&conv[j], 128);
+            mbar_init(&lofree[j], 2);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&tfull[b], 2);
+            mbar_init(&tempty[b], 128);
+        }
+        fence_mbar_init();
+        tma_prefetch_desc(&map_x);
+        tma_prefetch_desc(&map_x32);
+        tma_prefetch_desc(&map_w);
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, Cfg::tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (p.trace && tid == 0) p.trace[kFcTraceK * 8 + 2 * blockIdx.x] = (long long)global_ns();
+
+    if (warp == 0) {
+        // ============================================================ TMA producer (one lane)
+        if (lane == 0) {
+            // A TMA box takes 128 bytes of each of 128 rows that lie 4*H bytes apart, and the next 128 bytes of a row
+            // follow a whole k-block later: left alone, HBM sees scattered 128-byte reads (measured: 39 % of its
+            // peak).  So whole ROWS of the next tile (4*H contiguous bytes each) are prefetched into L2 while the
+            // current tile is consumed -- DRAM reads become sequential and the boxes hit L2.  The prefetches are
+            // spread over the k-blocks of the current tile, so at most one tile per SM (~60 MB in all) waits in L2.
+            const uint32_t row_bytes = (uint32_t)p.H * 4u;
+            const bool pf = (row_bytes & 15u) == 0 && CTC_FC_L2_PREFETCH;
+            if (pf)
+                for (long long r = r0; r < min(r1, r0 + kFcBM); ++r) l2_prefetch_bulk(p.x + r * p.H, row_bytes);
+            int s = 0, ph = 0;
+            unsigned gp = 0;
+            const int koff = (int)((blockIdx.x * 7u) % (unsigned)nkb);
+            for (long long row = r0; row < r1; row += kFcBM) {
+                const int nrows = (int)min((long long)kFcBM, r1 - row);
+                const int nbox = (nrows + 31) >> 5;  // 32-row boxes of a partial tile
+                const int nnext = (int)max(0ll, min((long long)kFcBM, r1 - (row + kFcBM)));  // rows of the next tile
+                for (int kbi = 0; kbi < nkb; ++kbi) {
+                    // every CTA walks the k-blocks from its own starting point (the sum over k does not care): all
+                    // 148 CTAs fetching the SAME W' tile from the same L2 lines at the same moment was the limiter of
+                    // the first version (ablation: 94 us with conversion and MMAs switched off)
+                    const int kb = (kbi + koff) % nkb;
+                    if (pf)
+                        for (int i = kbi * nnext / nkb; i < (kbi + 1) * nnext / nkb; ++i)
+                            l2_prefetch_bulk(p.x + (row + kFcBM + i) * p.H, row_bytes);
+                    mbar_wait(&empty[s], ph ^ 1);  // passes at once the first time round the ring
+                    FC_TRACE(0, gp);  // producer: slot free, about to issue
+                    ++gp;
+                    unsigned char *st = smem + (size_t)s * Cfg::stage_bytes;
+                    if (nrows == kFcBM) {
+                        mbar_arrive_expect_tx(&full[s], Cfg::a_bytes + Cfg::w_bytes);
+                        tma_load_2d(st, &map_x, kb * kFcBK, (int)row, &full[s]);  // x tile [256][32]
+                    } else {
+                        mbar_arrive_expect_tx(&full[s], nbox * 32 * kFcBK * 4 + Cfg::w_bytes);
+                        for (int j = 0; j < nbox; ++j)  // 32 rows = 4 swizzle atoms of 1024 bytes
+                            tma_load_2d(st + j * 32 * kFcBK * 4, &map_x32, kb * kFcBK, (int)row + 32 * j, &full[s]);
+                    }
+                    tma_load_2d(st + Cfg::a_bytes, &map_w, kb * kFcBK, 0, &full[s]);  // W' tile [2N][32]
+                    if (++s == S) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1 || warp == 10) {
+        // ============================================================ MMA issuers (one lane each): warp 1 issues the
+        // MMAs of the tile's first M = 128 half, warp 10 those of the second.  One thread issuing all 16 MMAs of a
+        // k-block was the bottleneck of the kernel (clock64 trace, CTC_FC_TRACE: ~70 clk per issue, 1165 clk per
+        // k-block against 670 for the converters); the halves have their own accumulators, so they need no ordering.
+        const int h = warp == 1 ? 0 : 1;
+        if (lane == 0) {
+            constexpr uint32_t idesc2 = fc_idesc(kFcHM, 2 * N), idesc1 = fc_idesc(kFcHM, N);
+            int s = 0, ph = 0, it = 0;
+            unsigned g = 0;  // k-blocks issued so far (x_lo buffer = g % LB)
+            for (long long row = r0; row < r1; row += kFcBM, ++it) {
+                const int buf = it & 1;
+                mbar_wait(&tempty[buf], ((it >> 1) & 1) ^ 1);  // the epilogue has drained this tile buffer
+                tc_fence_after();
+                for (int kb = 0; kb < nkb; ++kb, ++g) {
+                    const int j = (int)(g % LB);
+                    mbar_wait(&full[s], ph);
+                    if (h == 0) FC_TRACE(4, g);  // MMA: tile landed
+                    mbar_wait(&conv[j], (g / LB) & 1);
+                    if (h == 0) FC_TRACE(5, g);  // MMA: x_lo ready
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + (size_t)s * Cfg::stage_bytes);
+                    const uint64_t dw = fc_smem_desc(sa + Cfg::a_bytes);
+                    // A operands in TMEM: x of this half at Cfg::a_col(j, h), x_lo 64 columns further
+                    const uint32_t ax = tmem_base + (uint32_t)Cfg::a_col(j, h);
+                    {  // this issuer's M = 128 half of the tile (the halves share the W' tile)
+                        const uint32_t d = tmem_base + (uint32_t)(((buf * 2 + h) * NA + kb % NA) * Cfg::acc_cols);
+#pragma unroll
+                        for (int k = 0; k < kFcBK / kFcUmmaK; ++k) {
+                            const uint64_t o = (uint64_t)((k * kFcUmmaK * 4) >> 4);
+                            // the first k-block of each accumulator overwrites, everything else accumulates
+                            tc_mma_tf32_ts(d, ax + 8 * k, dw + o, idesc2, (kb >= NA || k > 0) ? 1u : 0u);  // x [W_hi | W_lo]^T
+                            tc_mma_tf32_ts(d, ax + 64 + 8 * k, dw + o, idesc1, 1u);                       // x_lo W_hi^T
+                        }
+                    }
+                    tc_commit(&empty[s]);    // ring stage s may be refilled once these MMAs have read it
+                    tc_commit(&lofree[j]);   // ... and x_lo buffer j rewritten
+                    if (h == 0) FC_TRACE(6, g);  // MMA: issued + committed
+                    if (++s == S) { s = 0; ph ^= 1; }
+                }
+                tc_commit(&tfull[buf]);
+            }
+        }
+    } else if (warp < 6) {
+        // ============================================================ converters: one tile row per thread and half.  The
+        // thread reads its row's 32 fp32 of the k-block from the swizzled tile (16-byte chunk c of row r sits at chunk
+        // position c ^ (r & 7)) and writes x and x_lo = x - (x with 13 low bits cleared) into TMEM with tcgen05.st --
+        // a warp may only touch TMEM lanes [32 * (warp % 4), +32), and A operands put tile row m on lane m, so warp
+        // quarter q handles rows q*32 + lane of BOTH halves.  The tensor core then reads A from TMEM: no x_lo tile in
+        // shared memory, no A-operand reads from shared memory (half the shared-memory traffic of the SS form).
+        const int qc = warp & 3;
+        const int rt = qc * 32 + lane;  // row inside a half
+        int s = 0, ph = 0;
+        unsigned g = 0;
+        for (long long row = r0; row < r1; row += kFcBM) {
+            for (int kb = 0; kb < nkb; ++kb, ++g) {
+                const int j = (int)(g % LB);
+                mbar_wait(&lofree[j], ((g / LB) & 1) ^ 1);  // passes at once for the first LB k-blocks
+                if (tid == 64) FC_TRACE(1, g);  // converter: TMEM A buffer free
+                mbar_wait(&full[s], ph);
+                if (tid == 64) FC_TRACE(2, g);  // converter: tile landed
+                tc_fence_after();
+                const unsigned char *tile = smem + (size_t)s * Cfg::stage_bytes;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int r = h * kFcHM + rt;
+                    const unsigned char *rp = tile + (size_t)r * 128;
+                    uint32_t xv[32], lv[32];
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        const uint4 w = *reinterpret_cast<const uint4 *>(rp + ((c ^ (r & 7)) << 4));
+                        xv[4 * c + 0] = w.x; xv[4 * c + 1] = w.y; xv[4 * c + 2] = w.z; xv[4 * c + 3] = w.w;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        lv[i] = __float_as_uint(__uint_as_float(xv[i]) - __uint_as_float(xv[i] & 0xffffe000u));
+                    const uint32_t ta = tmem_base + ((uint32_t)(qc * 32) << 16) + (uint32_t)Cfg::a_col(j, h);
+                    tmem_st_32x32(ta, xv);
+                    tmem_st_32x32(ta + 64, lv);
+                }
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                tc_fence_before();
+                mbar_arrive(&conv[j]);   // A operands of this k-block are in TMEM
+                mbar_arrive(&empty[s]);  // ... and this thread is done with the x tile of ring stage s
+                if (tid == 64) FC_TRACE(3, g);  // converter: done
+                if (++s == S) { s = 0; ph ^= 1; }
+            }
+        }
+    } else {
+        // ============================================================ epilogue: one logits row per thread
+        const int q = warp & 3;  // a warp may only touch TMEM lanes [32 * (warp % 4), +32)
+        const int na = min(NA, nkb);  // accumulators that received at least one k-block
+        int it = 0;
+        for (long long row = r0; row < r1; row += kFcBM, ++it) {
+            const int buf = it & 1;
+            mbar_wait(&tfull[buf], (it >> 1) & 1);
+            tc_fence_after();
+          for (int h = 0; h < 2; ++h) {
+            __syncwarp();  // lanes leave the previous half's body at different points; tcgen05.ld is warp-aligned
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((buf * 2 + h) * NA * Cfg::acc_cols);
+            float v[N];
+#pragma unroll
+            for (int c0 = 0; c0 < N; c0 += 32) {
+                float acc[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+                for (int a = 0; a < na; ++a) {
+                    float hi[32], lo[32];
+                    tmem_ld_32x32(taddr + a * Cfg::acc_cols + c0, hi);
+                    tmem_ld_32x32(taddr + a * Cfg::acc_cols + N + c0, lo);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) acc[i] += hi[i] + lo[i];
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[c0 + i] = acc[i] + __ldg(p.bias + c0 + i);
+            }
+            if (h == 1) {
+                tc_fence_before();
+                mbar_arrive(&tempty[buf]);  // accumulators are in registers: the MMA warp may reuse the buffer
+            }
+            const long long rw = row + h * kFcHM + q * 32;  // first row of this warp's 32
+            const long long r = rw + lane;
+            if (p.logits) {
+                // The warp's 32 rows x C logits are one contiguous block of memory.  One thread storing its row as C
+                // scalars makes every store instruction touch 32 different lines (7680 L1 wavefronts per tile on the
+                // load/store pipe the converters share: a 7 us stall at every tile boundary in the clock64 trace);
+                // transposed through shuffles, lane c holds column c and every store instruction writes ONE row.
+#pragma unroll
+                for (int c0 = 0; c0 < N; c0 += 32) {
+                    float w[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) w[i] = v[c0 + i];
+                    warp_transpose32(w, lane);
+                    const int c = c0 + lane;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c < p.C && rw + i < r1) p.logits[(rw + i) * p.C + c] = w[i];
+                }
+            }
+            if (r >= r1) continue;  // not this CTA's row (or past the end): never written
+            if (p.y == nullptr && p.path == nullptr) continue;
+            const int t = (int)(r / p.B), b = (int)(r - (long long)t * p.B);
+            if (p.act_lens && t >= min(max(p.act_lens[b], 0), p.T)) continue;  // padding frame: never read
+            float m = -INFINITY;
+            int arg = 0;
+#pragma unroll
+            for (int c = 0; c < N; ++c)
+                if (c < p.C && v[c] > m) { m = v[c]; arg = c; }  // strict >: the first maximum wins (torch.max)
+            if (p.path) p.path[(size_t)b * p.T + t] = arg;
+            if (p.y == nullptr) continue;
+            // the softmax row exactly as ctc_prep_kernel forms it: expf, one division, clamp to >= 2^-126, planar words
+            float sum = 0.f;
+#pragma unroll
+            for (int c = 0; c < N; ++c) {
+                v[c] = (c < p.C) ? expf(v[c] - m) : 0.f;
+                sum += v[c];
+            }
+            const float inv = 1.0f / sum;
+            const bool bad = sum != sum;
+            uint4 *yd = reinterpret_cast<uint4 *>(p.y + ((size_t)b * p.T + t) * 2 * N);
+#pragma unroll
+            for (int c = 0; c < N; c += 4) {
+                uint4 hw, l;
+                float e = fmaxf(v[c] * inv, 1.17549435e-38f);     hw.x = y_hi_word(e); l.x = y_lo_word(e);
+                e = fmaxf(v[c + 1] * inv, 1.17549435e-38f);       hw.y = y_hi_word(e); l.y = y_lo_word(e);
+                e = fmaxf(v[c + 2] * inv, 1.17549435e-38f);       hw.z = y_hi_word(e); l.z = y_lo_word(e);
+                e = fmaxf(v[c + 3] * inv, 1.17549435e-38f);       hw.w = y_hi_word(e); l.w = y_lo_word(e);
+                if (bad) { hw = make_uint4(0x7ff80000u, 0x7ff80000u, 0x7ff80000u, 0x7ff80000u); l = make_uint4(0, 0, 0, 0); }
+                yd[c / 4] = hw;
+                yd[N / 4 + c / 4] = l;
+            }
+          }
+        }
+    }
+    // ---- teardown: everybody is done with TMEM before its owner frees it
+    tc_fence_before();
+    __syncthreads();
+    if (p.trace && tid == 0) p.trace[kFcTraceK * 8 + 2 * blockIdx.x + 1] = (long long)global_ns();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::tmem_cols);
+    }
+}
+
 
 }  // namespace ctcb200

@@ -247,6 +247,9 @@ typedef struct {
     int bn_batch_stats;      /* 1: normalise with the statistics of x itself (module.train()) */
     float *batch_mean_out;   /* DEVICE fp32 [H] or NULL: receives the batch mean (bn_batch_stats = 1) */
     float *batch_var_out;    /* DEVICE fp32 [H] or NULL: receives the biased batch variance */
+    int reuse_folded;        /* 1: fc_workspace still holds the folded weights of an earlier call with the SAME layer
+                                (weights and statistics unchanged, bn_batch_stats = 0): the fold kernel is skipped --
+                                what an evaluation loop wants after its first batch */
 } ctcB200FcLayer;
 ctcB200Status ctc_b200_fc_workspace_size(int T, int B, int H, int C, size_t *bytes);
 ctcB200Status ctc_b200_fc_forward(const float *x, int T, int B, int H, int C, const ctcB200FcLayer *layer,

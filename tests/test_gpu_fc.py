@@ -124,3 +124,19 @@ def test_fc_rejects_unsupported_shapes(b200):
     x = torch.randn(4, 2, 32, device="cuda")
     with pytest.raises(RuntimeError):
         b200.fc.fc_forward(x, torch.randn(65, 32, device="cuda"))  # C > 64
+
+
+def test_fc_ts_form_matches_goldens():
+    # the alternative form of the kernel (A operands through TMEM: tcgen05.st by the converters, TS-form tcgen05.mma),
+    # selected per process by CTC_FC_TS=1: same goldens; one accumulator per tile half, so its error is ~2x the default's
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, CTC_FC_TS="1")
+    res = subprocess.run([sys.executable, os.path.join(root, "tools", "fc_check.py")], capture_output=True, text=True,
+                         env=env, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    errs = [float(line.split("max abs err")[1].split()[0]) for line in res.stdout.splitlines() if "max abs err" in line]
+    assert len(errs) == len(GOLD) and max(errs) <= LOGITS_ATOL, res.stdout
+    assert "BAD" not in res.stdout

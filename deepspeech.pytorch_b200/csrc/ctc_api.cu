@@ -57,8 +57,8 @@ constexpr int kDefaultSlices = 8;
 constexpr int kMinSliceB = 8;  // utterances per slice below which slicing stops paying
 struct SidePool {
     bool ok = false;
-    cudaStream_t side[kMaxSlices], aux;
-    cudaEvent_t fork, join[kMaxSlices], eng_done[kMaxSlices], aux_done;
+    cudaStream_t side[kMaxSlices], side2[kMaxSlices], aux;  // side2: the small warp class of a slice's gradient work
+    cudaEvent_t fork, join[kMaxSlices], join2[kMaxSlices], eng_done[kMaxSlices], eng_done2[kMaxSlices], aux_done;
 };
 SidePool g_pool[64];
 std::mutex g_pool_mu;  // held while a sliced launch is being enqueued: the pool's events are shared by all callers
@@ -73,7 +73,10 @@ SidePool *side_pool(int dev) {
     if (cudaStreamCreateWithFlags(&sp.aux, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     for (int k = 0; k < kMaxSlices; ++k) {
         if (cudaStreamCreateWithFlags(&sp.side[k], cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        if (cudaStreamCreateWithFlags(&sp.side2[k], cudaStreamNonBlocking) != cudaSuccess) return nullptr;
         if (cudaEventCreateWithFlags(&sp.join[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&sp.join2[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&sp.eng_done2[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
         if (cudaEventCreateWithFlags(&sp.eng_done[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
     }
     sp.ok = true;
@@ -111,6 +114,9 @@ struct Plan {
     size_t smem_prep, smem_engine, smem_grad;
     // workspace byte offsets
     int nqmax;   // grad kernel warps per CTA
+    int nq_small;        // > 0: utterances that need <= nq_small warps get their own launch with CTAs of that size
+    int nsplit_small;    // ... its CTAs per utterance
+    size_t smem_grad_small;
     int nsplit;  // grad kernel CTAs per utterance
     int big;     // large-alphabet path (C > kMaxSmallC)
     size_t o_ctab, o_units, o_cu, o_bord;
@@ -160,6 +166,28 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         if (ns > pl->nblk / 2) ns = pl->nblk / 2;  // >= 2 groups per CTA (measured 2: 0.233, 4: 0.235, 6: 0.240 ms/step)
         if (ns < 1) ns = 1;
         pl->nsplit = ns;
+        // Warp classes (small alphabets, >= 2 gradient warps): an utterance whose lattice fits half of the warps would
+        // leave the other half of a full-size CTA idle -- and this kernel's throughput follows the number of warps
+        // that have work -- so those utterances get a launch of their own with half-size CTAs (half the registers,
+        // about half the shared memory: twice as many resident).  Gradient kernel alone (tools/ubench/engine_bench):
+        // B=64 100.4 -> 88.2 us, B=1024 1305 -> 1094 us.  Every class launch covers all utterances of its slice (the
+        // host does not see device-side lengths), so the CTAs of the other class's utterances start and leave at
+        // once -- but a full-size CTA needs a full-size slot even for that: on the headline (B=64, 8 slices) the nearly
+        // empty full-size launches of the short slices queue behind resident work and hold the step's join back
+        // (0.190 -> 0.208 ms), while at B=1024 the step gains (1.900 -> 1.821 ms).  Hence by batch size;
+        // CTC_B200_GRAD_CLASSES=0 / 1 forces one launch for all / the two classes.
+        const int cls = env_int("CTC_B200_GRAD_CLASSES", -1);
+        pl->nq_small = (!pl->big && pl->nqmax >= 2 && (cls < 0 ? B >= 256 : cls != 0)) ? pl->nqmax / 2 : 0;
+        pl->smem_grad_small = 0;
+        pl->nsplit_small = ns;
+        if (pl->nq_small) {
+            pl->smem_grad_small =
+                grad_smem(C, pl->Cp, grad_class_lmax(pl->nq_small, Lmax), pl->nq_small, kK, false).total;
+            const int res = (int)(kSmemLimit / pl->smem_grad_small) > 0 ? (int)(kSmemLimit / pl->smem_grad_small) : 1;
+            int n2 = (7 * 148 * (res > 8 ? 8 : res) + B - 1) / B;
+            if (n2 > pl->nblk / 2) n2 = pl->nblk / 2;
+            pl->nsplit_small = n2 < 1 ? 1 : n2;
+        }
     }
     if (pl->smem_engine > kSmemLimit || pl->smem_prep > kSmemLimit) return false;
     // more than 4 lattice warps (L > 511): split them over the two CTAs of a cluster so that each has an SMSP to
@@ -248,7 +276,7 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
             ++*launches;
         }
         if (costs_ready && cudaEventRecord(costs_ready, st) != cudaSuccess) return cudaErrorUnknown;
-        if (do_grad) grd(p, p.B, st);
+        if (do_grad) grd(p, p.B, st, st);
         launch_collapse(p, st, launches);
         return cudaGetLastError();
     }
@@ -277,7 +305,18 @@ cudaError_t launch_sliced(const CtcParams &p, const Plan &pl, cudaStream_t st, b
             CtcParams pk = p;
             pk.slice0 = slice_begin(pl, p.B, k);
             const int nb = slice_begin(pl, p.B, k + 1) - pk.slice0;
-            if (pass == 0) eng(pk, nb, sp->side[k]); else grd(pk, nb, sp->side[k]);
+            if (pass == 0) {
+                eng(pk, nb, sp->side[k]);
+            } else if (pl.nq_small) {
+                // the slice's small warp class runs beside its full-size one, on a stream of its own
+                if ((e = cudaEventRecord(sp->eng_done2[k], sp->side[k])) != cudaSuccess) return e;
+                if ((e = cudaStreamWaitEvent(sp->side2[k], sp->eng_done2[k], 0)) != cudaSuccess) return e;
+                grd(pk, nb, sp->side[k], sp->side2[k]);
+                if ((e = cudaEventRecord(sp->join2[k], sp->side2[k])) != cudaSuccess) return e;
+                if ((e = cudaStreamWaitEvent(st, sp->join2[k], 0)) != cudaSuccess) return e;
+            } else {
+                grd(pk, nb, sp->side[k], sp->side[k]);
+            }
             if (trace) cudaEventRecord(tr[k][pass], sp->side[k]);
         }
         if (pass == 0) {
@@ -382,8 +421,18 @@ cudaError_t launch_all_cp(const CtcParams &p, const Plan &pl, cudaStream_t st, i
                 ctc_engine2_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
             ++*launches;
         },
-        [&](const CtcParams &pk, int nb, cudaStream_t s) {
-            ctc_grad_kernel<kK, CP, false><<<dim3(pk.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pk);
+        [&](const CtcParams &pk, int nb, cudaStream_t s, cudaStream_t s_small) {
+            CtcParams pf = pk;
+            if (pl.nq_small) {
+                CtcParams ps = pk;  // utterances with 1 .. nq_small lattice warps
+                ps.nqmax = pl.nq_small;
+                ps.gLmax = grad_class_lmax(pl.nq_small, pl.Lmax);
+                ps.nsplit = pl.nsplit_small;
+                ctc_grad_kernel<kK, CP, false><<<dim3(ps.nsplit, nb), pl.nq_small * 32, pl.smem_grad_small, s_small>>>(ps);
+                ++*launches;
+                pf.gq_lo = pl.nq_small + 1;
+            }
+            ctc_grad_kernel<kK, CP, false><<<dim3(pf.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pf);
             ++*launches;
         });
 }
@@ -482,7 +531,7 @@ cudaError_t launch_big(const CtcParams &p, const Plan &pl, cudaStream_t st, int 
             ctc_engine2_kernel<kK, CP><<<pk.score_only ? nb : 2 * nb, (pl.nwl + 1) * 32, pl.smem_engine_req, s>>>(pk);
         ++*launches;
     };
-    auto grd = [&](const CtcParams &pk, int nb, cudaStream_t s) {
+    auto grd = [&](const CtcParams &pk, int nb, cudaStream_t s, cudaStream_t) {
         ctc_grad_kernel<kK, CP, true><<<dim3(pk.nsplit, nb), pl.nqmax * 32, pl.smem_grad, s>>>(pk);
         ++*launches;
     };
@@ -642,6 +691,8 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.ctab = reinterpret_cast<int2 *>(ws + pl.o_ctab);
     p.nsplit = pl.nsplit;
     p.nqmax = pl.nqmax;
+    p.gq_lo = 1;
+    p.gLmax = pl.Lmax;
     p.coff = reinterpret_cast<int *>(ws + pl.o_coff);
     p.units = reinterpret_cast<unsigned *>(ws + pl.o_units);
     p.cu = reinterpret_cast<int *>(ws + pl.o_cu);

@@ -72,7 +72,10 @@ struct CtcParams {
     int slice0;         // engine / grad kernels: this launch covers bord[slice0 .. slice0 + gridDim) (bord == 0: b itself)
     int slice_nb;       // utterances of this launch (large-alphabet row kernel: grid = T * slice_nb)
     int nsplit;         // grad kernel: time blocks are dealt round-robin to this many CTAs per utterance
-    int nqmax;          // grad kernel: warps per CTA = ceil((2*Lmax+1) / 224)
+    int nqmax;          // grad kernel: warps per CTA of THIS launch (= its shared-memory layout)
+    int gq_lo;          // grad kernel: this launch takes the utterances that need gq_lo .. nqmax lattice warps (the
+                        // host launches one grid per warp class, so that every resident warp has work)
+    int gLmax;          // grad kernel: longest label sequence of this launch's class (shared-memory layout)
     int nan_to_zero;    // 1: a NaN logit is read as 0 (the reference's train.py:595-598 guard, folded into the softmax pass)
     int *nan_count;     // optional: += number of NaN logits seen in valid frames (nan_to_zero only)
     int phase;          // second engine form: 0 = whole recursion; 1 / 2 = its first / second part (engine_phase_range)
@@ -115,6 +118,16 @@ __host__ __device__ inline int grad_row_pitch(int Lmax, int nqmax) {
     return n | 1;  // any ODD pitch puts the 8 rows of a group in 8 different residues mod 8, hence (with units 8 banks
                    // apart) the reduction's (unit, row) lanes in 32 different banks; the smallest one saves up to 31
                    // floats per row -- at B=64,T=1000,C=5000 (Lmax 183) exactly what lets a 4th CTA fit on the SM
+}
+// Longest label sequence nq gradient warps can hold, and where the blank block of an utterance's posterior row starts:
+// behind the longest label sequence of the utterance's own warp class (the same in every launch that can take it).
+__host__ __device__ inline int grad_class_lmax(int nq, int Lmax) {
+    const int l = 4 * kCoreThreads * nq - 1;
+    return l < Lmax ? l : Lmax;
+}
+__host__ __device__ inline int grad_blank_off(int L, int Lmax) {
+    const int l = grad_class_lmax(grad_nq(L), Lmax);
+    return l > 0 ? l : 1;
 }
 __host__ __device__ inline int grad_max_units(int C, int Lmax, int nqmax) {
     return ((Lmax > 0 ? Lmax : 1) + kUnit - 1) / kUnit + C + nqmax * (32 / kUnit);
@@ -219,7 +232,7 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
         // One lane per class, warp prefix sum over the unit counts.  cnt[c] now holds the END of class c's segment.
         unsigned *un = p.units + (size_t)b * p.numax;
         int *cu = p.cu + (size_t)b * (C + 1);
-        const int Lb = p.Lmax > 0 ? p.Lmax : 1;
+        const int Lb = grad_blank_off(L, p.Lmax);
         const int nq = grad_nq(L);
         int base = 0;
         for (int c0 = 0; c0 < C; c0 += 32) {
@@ -1625,6 +1638,10 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
     const int Tb = min(max(p.act_lens[b], 0), p.T);
     const int nblk_b = (Tb + R - 1) / R;
     if (z >= nblk_b) return;  // padding frames were zero-filled by the prep kernel
+    const int L = min(max(p.label_lens[b], 0), p.Lmax);
+    const int S = 2 * L + 1;
+    const int nq = (S + K * kCoreThreads - 1) / (K * kCoreThreads);  // lattice warps of this utterance
+    if (nq < p.gq_lo || nq > p.nqmax) return;  // another warp class's launch takes it
     const size_t rowstride = (size_t)p.B * C;
     if (!p.feas[b]) {  // infeasible utterance: zero gradient
         for (int blk = z; blk < nblk_b; blk += p.nsplit)
@@ -1632,10 +1649,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
                 for (int c = lane; c < C; c += 32) p.grads[((size_t)(blk * R + r) * p.B + b) * C + c] = 0.f;
         return;
     }
-    const int L = min(max(p.label_lens[b], 0), p.Lmax);
-    const int S = 2 * L + 1;
-    const int nq = (S + K * kCoreThreads - 1) / (K * kCoreThreads);  // <= p.nqmax == blockDim.x / 32
-    const GradSmem lay = grad_smem(C, Cp, p.Lmax, p.nqmax, K, BIG);
+    const GradSmem lay = grad_smem(C, Cp, p.gLmax, p.nqmax, K, BIG);
     unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
     uint64_t *ybar = reinterpret_cast<uint64_t *>(smem + lay.bar);
     unsigned *units = reinterpret_cast<unsigned *>(smem + lay.units);
@@ -1643,7 +1657,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
     float *psort = reinterpret_cast<float *>(smem + lay.psort);
     int *arow = reinterpret_cast<int *>(smem + lay.arow) + (size_t)q * R * 32 * K;
     const int Lp = lay.pitch;                    // pitch of a posterior row
-    const int Lb = p.Lmax > 0 ? p.Lmax : 1;      // where the blank partial sums start inside a row
+    const int Lb = grad_blank_off(L, p.Lmax);    // where the blank partial sums start inside a row
     float *bpart = psort + Lb;                   // [row * Lp + warp * 32 + lane]
     const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
     const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;

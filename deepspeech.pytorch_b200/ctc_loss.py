@@ -357,12 +357,16 @@ class _CTCFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, acts, labels, act_lens, label_lens, blank, zero_infinity, scale, max_label_len, want,
-                nan_to_zero=False, comm_handle=0):
+                nan_to_zero=False, comm_handle=0, go_pred=1.0, observer=None):
+        # go_pred: the factor the caller's backward() is expected to bring (CTCLoss._predicted_grad_output); it is
+        # folded into the kernels' gradient scale, backward() then multiplies by grad_output / go_pred
         costs, grads, nans, loss, loss_all = _ctc_loss_op(acts, labels, act_lens, label_lens, blank, zero_infinity,
-                                                          scale, want,
+                                                          scale * go_pred, want,
                                                           -1 if max_label_len is None else int(max_label_len),
                                                           nan_to_zero, int(comm_handle))
         ctx.has_grads = want
+        ctx.go_pred = float(go_pred)
+        ctx.observer = observer
         if want:
             ctx.save_for_backward(grads)
         loss = loss * scale if scale != 1.0 else loss
@@ -372,18 +376,22 @@ class _CTCFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_output, *unused):
         if not ctx.has_grads:
-            return (None,) * 11
+            return (None,) * 13
         (grads,) = ctx.saved_tensors
         if getattr(ctx, "consumed", False):
             # a second backward through the same graph (retain_graph=True): the cached gradients already carry the
             # first call's factor, so undo it out of place
-            return (grads * (grad_output.reshape(1, 1, 1).to(grads.device) / ctx.applied),) + (None,) * 10
+            return (grads * (grad_output.reshape(1, 1, 1).to(grads.device) / ctx.applied),) + (None,) * 12
         # The reference binding's contract (cached grads * grad_output) without its extra [T,B,C] tensor: the cached
-        # gradients are scaled IN PLACE by the device scalar (no host sync), and not touched at all when it is 1.
-        ctx.applied = grad_output.detach().reshape(1, 1, 1).to(grads.device).clone()
+        # gradients are scaled IN PLACE by the device scalar grad_output / go_pred (no host sync), and not touched at
+        # all when that is 1 -- i.e. when grad_output is 1 or is what the criterion predicted from earlier steps.
+        go = grad_output.detach().reshape(1).to(device=grads.device, dtype=torch.float32)
+        ctx.applied = go.reshape(1, 1, 1).clone()
         ctx.consumed = True
-        scale_grads_(grads, grad_output)
-        return (grads,) + (None,) * 10
+        if ctx.observer is not None:
+            ctx.observer._observe_grad_output(go)
+        scale_grads_(grads, go / ctx.go_pred if ctx.go_pred != 1.0 else go)
+        return (grads,) + (None,) * 12
 
 
 class CTCLoss(torch.nn.Module):
@@ -404,11 +412,23 @@ class CTCLoss(torch.nn.Module):
     (data/utils.py:40-44, train.py:356,461,606) -- exchanged by the library's cost-summing kernel over NVLink peer
     memory while the gradient kernels run, with no collective launch.  The returned loss itself stays rank-local,
     as in the reference.
+    predict_grad_output=True (default): the reference divides the returned loss by the batch size and calls
+    backward() (train.py:600-602,619-620), so autograd hands back grad_output = 1/B and the cached gradients need a
+    multiply -- a read+write pass over [T,B,C] (0.4 ms at C = 5000).  The criterion remembers the grad_output of the
+    previous backward() (copied to pinned host memory without a sync, read at the next forward) and folds it into
+    the kernels' gradient scale; backward() multiplies by grad_output / predicted on the device, which touches
+    nothing when the prediction was right and corrects the gradients when it was not, so the result is always
+    gradients * grad_output.
     """
 
     def __init__(self, blank: int = 0, size_average: bool = False, length_average: bool = False,
-                 zero_infinity: bool = True, loss_on_cpu: bool = False, nan_to_zero: bool = False, comm=None):
+                 zero_infinity: bool = True, loss_on_cpu: bool = False, nan_to_zero: bool = False, comm=None,
+                 predict_grad_output: bool = True):
         super().__init__()
+        self.predict_grad_output = predict_grad_output
+        self._go_pred = 1.0
+        self._go_host = None   # pinned fp32 [1]: grad_output of the last backward()
+        self._go_event = None
         self.comm = comm
         self.loss_all_ranks = None
         self.blank = blank
@@ -429,11 +449,31 @@ class CTCLoss(torch.nn.Module):
             scale = 1.0 / float(acts.shape[1])
         # grad mode is off inside autograd.Function.forward, so decide here whether gradients are wanted
         want = bool(acts.requires_grad and torch.is_grad_enabled())
+        observe = want and self.predict_grad_output and not torch.cuda.is_current_stream_capturing()
         loss, nans, loss_all = _CTCFunction.apply(acts, labels, act_lens, label_lens, self.blank, self.zero_infinity,
                                                   scale, max_label_len, want, self.nan_to_zero,
-                                                  self.comm.handle if self.comm is not None else 0)
+                                                  self.comm.handle if self.comm is not None else 0,
+                                                  self._predicted_grad_output() if observe else 1.0,
+                                                  self if observe else None)
         if self.nan_to_zero:
             self.nan_count = nans
         if self.comm is not None:
             self.loss_all_ranks = loss_all * scale if scale != 1.0 else loss_all
         return loss.cpu() if self.loss_on_cpu else loss
+
+    def _predicted_grad_output(self) -> float:
+        # the last observation, if its copy has landed (never waits)
+        if self._go_event is not None and self._go_event.query():
+            v = float(self._go_host[0])
+            if v == v and v not in (0.0, float("inf"), float("-inf")):
+                self._go_pred = v
+        return self._go_pred
+
+    def _observe_grad_output(self, go: torch.Tensor) -> None:
+        if self._go_host is None:
+            self._go_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+            self._go_event = torch.cuda.Event()
+        elif not self._go_event.query():
+            return  # the previous observation is still in flight: do not overwrite what it is writing
+        self._go_host.copy_(go, non_blocking=True)
+        self._go_event.record()

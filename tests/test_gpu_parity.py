@@ -795,6 +795,29 @@ def test_module_backward_scales_in_place(oracle, b200):
     assert torch.equal(g[1:], ref[1:] * 0.25) and g[0] == ref[0]
 
 
+@pytest.mark.parametrize("C", [30, 200])
+def test_module_predicts_grad_output_across_steps(oracle, b200, C):
+    # the criterion folds the grad_output it saw at the previous backward() (train.py:602: loss / B, every step) into the
+    # kernels' gradient scale; backward() then multiplies by grad_output / predicted on the device: exact whether the
+    # prediction holds (steps 2, 3: nothing is touched), is absent (step 1) or is wrong (step 4: another divisor)
+    w = b200.workloads.Workload("m", 6, 120, C, 25, 0.05, 0.2)
+    crit = b200.CTCLoss()
+    for step, div in enumerate((6.0, 6.0, 6.0, 4.0, 4.0)):
+        d = b200.workloads.make(w, seed=60 + step)
+        oc, og = oracle.compute(d["acts"].numpy(), d["labels"].numpy(), d["act_lens"].numpy(), d["label_lens"].numpy())
+        x = d["acts"].cuda().requires_grad_(True)
+        loss = crit(x, d["labels"], d["act_lens"], d["label_lens"])
+        (loss / div).backward()
+        torch.cuda.synchronize()
+        assert abs(loss.item() - oc.sum()) <= LOSS_RTOL * oc.sum()  # the returned loss never carries the prediction
+        assert np.abs(x.grad.cpu().numpy().astype(np.float64) * div - og).max() <= GRAD_ATOL, (step, div)
+    assert crit._go_pred == 0.25  # learnt from the observations, without a host sync in the step itself
+    plain = b200.CTCLoss(predict_grad_output=False)
+    x = d["acts"].cuda().requires_grad_(True)
+    (plain(x, d["labels"], d["act_lens"], d["label_lens"]) / 4.0).backward()
+    assert plain._go_pred == 1.0 and np.abs(x.grad.cpu().numpy().astype(np.float64) * 4.0 - og).max() <= GRAD_ATOL
+
+
 def test_zero_frames_with_a_sliceable_batch(b200):
     # T == 0 skips the prep launch (which writes the length ranking of a sliced launch): the engines must then run
     # unsliced.  Straight through the C ABI, since an empty torch tensor has no data pointer.

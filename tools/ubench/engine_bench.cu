@@ -52,6 +52,7 @@ int main(int argc, char **argv) {
     CK(cudaMalloc(&p.dbg, 8 * 2 * B * 16 * 8 + 8192)); CK(cudaMemset(p.dbg, 0, 8 * 2 * B * 16 * 8 + 8192));
 #endif
     p.nqmax = (2 * Lmax + 1 + 223) / 224;
+    p.gq_lo = 1; p.gLmax = Lmax;
     size_t s_prep = prep_smem(C, Lmax), s_eng = engine_smem(p.Cp, p.nwl).total, s_grad = grad_smem(C, p.Cp, Lmax, p.nqmax, kK, false).total;
     { int resident = (int)(227 * 1024 / s_grad); if (resident < 1) resident = 1; p.nsplit = (2 * 148 * resident + B - 1) / B; if (p.nsplit > p.nblk) p.nsplit = p.nblk; if (argc > 5) p.nsplit = atoi(argv[5]); }
     CK(cudaFuncSetAttribute(ctc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -78,6 +79,20 @@ int main(int argc, char **argv) {
         cudaEventRecord(e[2]);
         if (getenv("SCORE_ONLY")) { CtcParams q = p; q.score_only = 1; cudaEventRecord(e[1]); ctc_engine_kernel<kK, 32><<<B, (p.nwl + 1) * 32, s_eng>>>(q); cudaEventRecord(e[2]); }
 #if KK == 8
+        if (getenv("CLASSES") && p.nqmax >= 2) {  // small warp class on its own stream, full class on the default one
+            static cudaStream_t s2 = nullptr; static cudaEvent_t ev, ev2;
+            if (!s2) { cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking); cudaEventCreate(&ev); cudaEventCreate(&ev2); }
+            CtcParams ps = p, pf = p;
+            ps.nqmax = p.nqmax / 2; ps.gLmax = grad_class_lmax(ps.nqmax, Lmax); pf.gq_lo = ps.nqmax + 1;
+            const size_t sm = grad_smem(C, p.Cp, ps.gLmax, ps.nqmax, kK, false).total;
+            int res = (int)(227 * 1024 / sm); if (res > 8) res = 8;
+            ps.nsplit = std::min(p.nblk / 2, (7 * 148 * res + B - 1) / B);
+            if (getenv("NSPLIT_SMALL")) ps.nsplit = atoi(getenv("NSPLIT_SMALL"));
+            cudaEventRecord(ev, 0); cudaStreamWaitEvent(s2, ev, 0);
+            ctc_grad_kernel<kK, 32, false><<<dim3(ps.nsplit, B), ps.nqmax * 32, sm, s2>>>(ps);
+            ctc_grad_kernel<kK, 32, false><<<dim3(pf.nsplit, B), pf.nqmax * 32, s_grad>>>(pf);
+            cudaEventRecord(ev2, s2); cudaStreamWaitEvent(0, ev2, 0);
+        } else
         ctc_grad_kernel<kK, 32, false><<<dim3(p.nsplit, B), p.nqmax * 32, s_grad>>>(p);
 #endif
         cudaEventRecord(e[3]);

@@ -818,6 +818,35 @@ def test_module_predicts_grad_output_across_steps(oracle, b200, C):
     assert plain._go_pred == 1.0 and np.abs(x.grad.cpu().numpy().astype(np.float64) * 4.0 - og).max() <= GRAD_ATOL
 
 
+def test_gradient_warp_classes_match_single_launch(oracle, b200, monkeypatch):
+    # the gradient kernel's two warp classes (own launch with half-size CTAs for utterances that need at most half of
+    # the warps; default for B >= 256) against one launch for all, on label lengths at the class boundaries
+    # (112 labels = 225 states = the first that need a second warp, 223 / 224 the third), incl. empty and infeasible
+    B, T, C = 12, 500, 29
+    lens = [0, 1, 111, 112, 113, 200, 223, 224, 225, 300, 335, 336]
+    g = torch.Generator().manual_seed(808)
+    acts = torch.randn(T, B, C, generator=g)
+    act_lens = torch.tensor([T - 7 * i for i in range(B)], dtype=torch.int32)
+    act_lens[9] = 200  # 300 labels in 200 frames: infeasible
+    labels = torch.cat([torch.randint(1, C, (n,), generator=g, dtype=torch.int32) for n in lens])
+    label_lens = torch.tensor(lens, dtype=torch.int32)
+    out = {}
+    for cls in ("0", "1"):
+        monkeypatch.setenv("CTC_B200_GRAD_CLASSES", cls)
+        for slices in ("1", "4"):
+            monkeypatch.setenv("CTC_B200_SLICES", slices)
+            c, gr = b200.ctc_forward_backward(acts.cuda(), labels, act_lens, label_lens)
+            torch.cuda.synchronize()
+            out[cls, slices] = (c.cpu(), gr.cpu())
+    oc, og = oracle.compute(acts.numpy(), labels.numpy(), act_lens.numpy(), label_lens.numpy())
+    for key, (c, gr) in out.items():
+        assert torch.equal(c, out["0", "1"][0]) and torch.equal(gr, out["0", "1"][1]), key  # bit-identical
+    c, gr = out["1", "4"]
+    fin = np.isfinite(oc)
+    assert (np.abs(c.numpy()[fin] - oc[fin]) / np.maximum(np.abs(oc[fin]), 1e-30)).max() <= LOSS_RTOL
+    assert np.abs(gr.numpy().astype(np.float64) - og).max() <= GRAD_ATOL
+
+
 def test_zero_frames_with_a_sliceable_batch(b200):
     # T == 0 skips the prep launch (which writes the length ranking of a sliced launch): the engines must then run
     # unsliced.  Straight through the C ABI, since an empty torch tensor has no data pointer.

@@ -119,12 +119,11 @@ struct Plan {
     size_t smem_grad_small;
     int nsplit;  // grad kernel CTAs per utterance
     int big;     // large-alphabet path (C > kMaxSmallC)
-    size_t o_ctab, o_units, o_cu, o_bord;
+    size_t o_ctab, o_bord;
     size_t smem_rows;  // large alphabets: dynamic shared memory of the row kernel
     int nslices;           // length-bucket slices the engine / grad launches are cut into (1 = unsliced)
     size_t smem_engine_req;  // dynamic shared memory REQUESTED for an engine CTA (>= smem_engine, see make_plan)
-    int numax;   // reduction units per utterance (small alphabets)
-    size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_tlab, o_coff, o_labels, o_llen, o_alen;
+    size_t o_y, o_ckA, o_ckB, o_ckAE, o_ckBE, o_Pm, o_Pe, o_feas, o_laboff, o_tlab, o_labels, o_llen, o_alen;
     size_t o_Pm2, o_Pe2, o_est;
     int two_part;          // 1: recursions run in two launches with the early gradient blocks in between
     int cluster;           // 1: engines run as 2-CTA clusters (more than 4 lattice warps, see ctc_engine2c_kernel)
@@ -170,14 +169,15 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         // leave the other half of a full-size CTA idle -- and this kernel's throughput follows the number of warps
         // that have work -- so those utterances get a launch of their own with half-size CTAs (half the registers,
         // about half the shared memory: twice as many resident).  Gradient kernel alone (tools/ubench/engine_bench):
-        // B=64 100.4 -> 88.2 us, B=1024 1305 -> 1094 us.  Every class launch covers all utterances of its slice (the
-        // host does not see device-side lengths), so the CTAs of the other class's utterances start and leave at
-        // once -- but a full-size CTA needs a full-size slot even for that: on the headline (B=64, 8 slices) the nearly
-        // empty full-size launches of the short slices queue behind resident work and hold the step's join back
-        // (0.190 -> 0.208 ms), while at B=1024 the step gains (1.900 -> 1.821 ms).  Hence by batch size;
+        // B=1024 1085 -> 944 us.  Every class launch covers all utterances of its slice (the host does not see
+        // device-side lengths), so the CTAs of the other class's utterances start and leave at once -- but a
+        // full-size CTA needs a full-size slot even for that: with few utterances per slice (B=64, 8 slices of 8) the
+        // nearly empty full-size launches of the short slices queue behind resident work and hold the step's join
+        // back.  Whole step, one launch against two classes (tools/grad_classes_sweep.py): B=64 179 / 194 us, B=128
+        // 269 / 277, B=192 380 / 369, B=256 478 / 471, B=1024 1704 / 1601.  Hence by batch size;
         // CTC_B200_GRAD_CLASSES=0 / 1 forces one launch for all / the two classes.
         const int cls = env_int("CTC_B200_GRAD_CLASSES", -1);
-        pl->nq_small = (!pl->big && pl->nqmax >= 2 && (cls < 0 ? B >= 256 : cls != 0)) ? pl->nqmax / 2 : 0;
+        pl->nq_small = (!pl->big && pl->nqmax >= 2 && (cls < 0 ? B >= 192 : cls != 0)) ? pl->nqmax / 2 : 0;
         pl->smem_grad_small = 0;
         pl->nsplit_small = ns;
         if (pl->nq_small) {
@@ -233,10 +233,6 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     pl->o_laboff = o; o = align256(o + sizeof(int) * B);
     pl->o_tlab = o;   o = align256(o + sizeof(uint4) * (size_t)B * NT);
     pl->o_ctab = o;    if (pl->big) o = align256(o + sizeof(int2) * (size_t)B * (Lmax > 0 ? Lmax : 1));
-    pl->o_coff = o;   o = align256(o + sizeof(int) * (size_t)B * (C + 1));
-    pl->numax = pl->big ? 0 : grad_max_units(C, Lmax, pl->nqmax);
-    pl->o_units = o;  o = align256(o + sizeof(unsigned) * (size_t)B * pl->numax);
-    pl->o_cu = o;     if (!pl->big) o = align256(o + sizeof(int) * (size_t)B * (C + 1));
     pl->o_bord = o;   o = align256(o + sizeof(int) * (size_t)B);
     pl->o_labels = o; o = align256(o + sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
     pl->o_llen = o;   o = align256(o + sizeof(int) * B);
@@ -693,10 +689,6 @@ static ctcB200Status compute_impl(const float *acts, float *grads, const int *la
     p.nqmax = pl.nqmax;
     p.gq_lo = 1;
     p.gLmax = pl.Lmax;
-    p.coff = reinterpret_cast<int *>(ws + pl.o_coff);
-    p.units = reinterpret_cast<unsigned *>(ws + pl.o_units);
-    p.cu = reinterpret_cast<int *>(ws + pl.o_cu);
-    p.numax = pl.numax;
     if (dec) {
         if (!dec->path || !dec->ids || !dec->out_lens) return CTC_B200_STATUS_INVALID_VALUE;
         p.path = dec->path;

@@ -4,9 +4,8 @@
 //                       loads of 128 consecutive rows into shared memory, one thread per row for max / sum, coalesced
 //                       stores of the emission rows y[b,t,:] as PLANAR fp64 words (Cp high words, Cp low words;
 //                       utterance-major, so the 8 rows of a group are ONE TMA bulk copy); padding frames get their
-//                       zero gradient rows here.  Utterance blocks: label offsets, class-sorted label order, the
-//                       per-thread label table and the gradient kernel's reduction units.  Extra block of a sliced
-//                       launch: utterances ranked by length (sort_by_length).
+//                       zero gradient rows here.  Utterance blocks: label offsets and the per-thread label table.
+//                       Extra block of a sliced launch: utterances ranked by length (sort_by_length).
 //   ctc_engine_kernel : grid 2 * nb (score-only: nb) per slice.  CTA 2i runs the alpha recursion of utterance i
 //                       forwards in time, CTA 2i+1 the beta recursion backwards, concurrently on different SMs.
 //                       Lattice warps hold K = 8 states per thread in registers and form a SYSTOLIC pipeline over
@@ -17,8 +16,9 @@
 //   ctc_grad_kernel   : grid (nsplit, nb) per slice, 4 CTAs/SM.  CTA (z, i) takes time groups z, z+nsplit, ... of
 //                       utterance i: warp q recomputes alpha over its 224 states (+16-state halos) from the
 //                       checkpoint into shared memory, sweeps beta backwards from the beta checkpoint forming
-//                       posteriors alpha*betabar/P, then the CTA reduces them per class in equal-sized units and
-//                       writes grad = scale * (softmax - occupancy) once.
+//                       posteriors alpha*betabar/P and adding them, as 2^-30 fixed point, into [row][class]
+//                       occupancy tables in shared memory (integer reductions: order-independent, deterministic);
+//                       then the CTA writes grad = scale * (softmax - occupancy) once, as coalesced rows.
 //   large alphabets (C > 128): ctc_prep_utt_kernel + ctc_prep_big_kernel (streaming softmax that also writes the dense
 //                       part of the gradient; emission rows gathered by label POSITION) -> the same engine / grad
 //                       kernels at pitch 256, the grad kernel subtracting the occupancies in place.
@@ -57,10 +57,6 @@ struct CtcParams {
     int *Pe;            // [B] exponent of p(l|x)
     int *feas;          // [B] 1 = feasible
     int *laboff;        // [B] offset of utterance b in `labels`
-    int *coff;          // [B][C+1]  class segment offsets in that order
-    unsigned *units;    // [B][numax] reduction units of the gradient kernel: start | len << 16 (see grad_units)
-    int *cu;            // [B][C+1]   first unit of class c
-    int numax;          // units per utterance (upper bound)
     uint4 *tlab;        // [B][nwl*32] per lattice thread (K = 8): packed label classes, skip/valid bits, lpos
     int bpos;           // index of the blank inside an emission row (class rows: blank; position rows: 0)
     int big;            // 1: large-alphabet path (emission rows indexed by label POSITION, see ctc_prep_big_kernel)
@@ -105,7 +101,6 @@ __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t
 // Posterior rows of the gradient kernel (one per time step of a group): [0, Lmax) label posteriors at their
 // class-sorted positions, then nq * 32 per-thread partial sums of the blank posteriors.  The pitch is odd so
 // that the 8 rows of a group start in 8 different banks.
-constexpr int kUnit = 8;         // positions per reduction unit
 constexpr int kCoreThreads = 28; // engine threads per gradient-kernel warp (224 states) + 2 halo threads each side
 __host__ __device__ inline int grad_nq(int L) { return (2 * L + 1 + 8 * kCoreThreads - 1) / (8 * kCoreThreads); }
 __host__ __device__ inline int grad_row_pitch(int Lmax, int nqmax) {
@@ -129,10 +124,6 @@ __host__ __device__ inline int grad_blank_off(int L, int Lmax) {
     const int l = grad_class_lmax(grad_nq(L), Lmax);
     return l > 0 ? l : 1;
 }
-__host__ __device__ inline int grad_max_units(int C, int Lmax, int nqmax) {
-    return ((Lmax > 0 ? Lmax : 1) + kUnit - 1) / kUnit + C + nqmax * (32 / kUnit);
-}
-
 // ================================================================================================ prep
 constexpr int kPrepRows = 128;    // THREADS of a prep CTA (the name dates from the round-1 one-thread-per-row softmax)
 constexpr int kPrepRowsCta = 32;  // softmax rows per row block: 4x the warps in flight of 128-row blocks
@@ -143,53 +134,13 @@ __host__ __device__ inline size_t prep_smem(int C, int Lmax) {
     return (rows > utt ? rows : utt) + sizeof(int) * (C + 2) + 64;  // >= 4 * B bytes (sort block): see make_plan
 }
 
-// Class-sorted positions of the labels of one utterance (one warp, labels already staged in shared memory):
-// lpos[i] = rank of label i when labels are stably sorted by class; coff[c] = first position of class c.  Lets the
-// grad kernel reduce posteriors per class over contiguous shared-memory segments, deterministically.
-__device__ __forceinline__ void sort_labels_warp(const int *lab, int L, int C, int *cnt, int *lpos_s, int *coff_g,
-                                                 int lane) {
-    for (int c = lane; c <= C; c += 32) cnt[c] = 0;
-    __syncwarp();
-    for (int i = lane; i < L; i += 32) atomicAdd(&cnt[lab[i]], 1);
-    __syncwarp();
-    // exclusive prefix over the class counts: 32 classes per pass, shuffle scan
-    int run = 0;
-    for (int c0 = 0; c0 <= C; c0 += 32) {
-        const int c = c0 + lane;
-        const int n = (c < C) ? cnt[c] : 0;
-        int incl = n;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int o = __shfl_up_sync(kFull, incl, d);
-            if (lane >= d) incl += o;
-        }
-        if (c <= C) {
-            cnt[c] = run + incl - n;
-            coff_g[c] = run + incl - n;
-        }
-        run += __shfl_sync(kFull, incl, 31);
-    }
-    __syncwarp();
-    for (int base = 0; base < L; base += 32) {
-        const int i = base + lane;
-        const bool act = i < L;
-        const int c = act ? lab[i] : (-1 - lane);
-        const unsigned m = __match_any_sync(kFull, c);
-        const int rank = __popc(m & ((1u << lane) - 1u));
-        const int start = act ? cnt[c] : 0;
-        __syncwarp();
-        if (act) lpos_s[i] = start + rank;
-        if (act && rank == 0) cnt[c] = start + __popc(m);
-        __syncwarp();
-    }
-}
-
-// Utterance block of the prep kernels (128 threads): label offset, class-sorted order, the per-lattice-thread label
-// table (K = 8: thread e owns labels 4e .. 4e+3) and the gradient kernel's reduction units.  The labels are staged in
-// shared memory first, so the block is three rounds of global latency (lengths, labels, results) rather than one
-// per label.  lps, labs: shared int [Lmax] each; cnt: shared int [C + 2].
+// Utterance block of the prep kernels (128 threads): label offset and the per-lattice-thread label table (K = 8:
+// thread e owns labels 4e .. 4e+3); large alphabets also rank the labels by class (the gradient kernel's
+// class-sorted posterior row).  The labels are staged in shared memory first, so the block is three rounds of global
+// latency (lengths, labels, results) rather than one per label.  lps, labs: shared int [Lmax] each; cnt: shared
+// int [C + 2].
 __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *lps, int *labs, int *cnt) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int C = p.C;
     int *s_off = cnt + C + 1;
     if (tid == 0) *s_off = 0;
@@ -221,42 +172,8 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
             lps[i] = less + eq_before;
             p.ctab[(size_t)b * p.Lmax + less + eq_before] = make_int2(c, eq_before == 0 ? eq : 0);
         }
-    } else if (warp == 0) {
-        sort_labels_warp(lab, L, C, cnt, lps, p.coff + (size_t)b * (C + 1), lane);
     }
     __syncthreads();
-    if (!p.big && warp == 1) {
-        // Reduction units of the gradient kernel: every class segment of the sorted posterior row is cut into pieces
-        // of <= kUnit positions (the blank's segment is the block of per-thread partial sums behind the labels), so
-        // the per-class sums are formed by equal-sized, independent tasks instead of one serial walk per class.
-        // One lane per class, warp prefix sum over the unit counts.  cnt[c] now holds the END of class c's segment.
-        unsigned *un = p.units + (size_t)b * p.numax;
-        int *cu = p.cu + (size_t)b * (C + 1);
-        const int Lb = grad_blank_off(L, p.Lmax);
-        const int nq = grad_nq(L);
-        int base = 0;
-        for (int c0 = 0; c0 < C; c0 += 32) {
-            const int c = c0 + lane;
-            int s0 = 0, s1 = 0;
-            if (c < C) {
-                s1 = cnt[c];                       // end of the segment (start + count after the ranking pass)
-                s0 = (c > 0) ? cnt[c - 1] : 0;     // == start of class c: segments are contiguous
-                if (c == p.blank) { s0 = Lb; s1 = Lb + nq * 32; }
-            }
-            const int n = (s1 - s0 + kUnit - 1) / kUnit;
-            int incl = n;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int o = __shfl_up_sync(kFull, incl, d);
-                if (lane >= d) incl += o;
-            }
-            int nu = base + incl - n;
-            if (c < C) cu[c] = nu;
-            for (; s0 < s1; s0 += kUnit) un[nu++] = (unsigned)s0 | ((unsigned)min(kUnit, s1 - s0) << 16);
-            base += __shfl_sync(kFull, incl, 31);
-        }
-        if (lane == 0) cu[C] = base;
-    }
     const int NT = p.nwl * 32;
     for (int e = tid; e < NT; e += blockDim.x) {
         unsigned cls = 0, bits = 0, lp[4] = {0, 0, 0, 0};
@@ -271,7 +188,7 @@ __device__ __forceinline__ void prep_utterance(const CtcParams &p, int b, int *l
                 bits |= 1u << (8 + h);
                 if (i == 0 || lab[i - 1] != c) bits |= 1u << h;            // skip into s
                 if (i + 1 < L && lab[i + 1] != c) bits |= 1u << (4 + h);  // skip out of s
-                lp[h] = (unsigned)lps[i];  // class-sorted slot of the label's posterior
+                if (p.big) lp[h] = (unsigned)lps[i];  // class-sorted slot of the label's posterior
             }
         }
         p.tlab[(size_t)b * NT + e] = make_uint4(cls, bits, lp[0] | (lp[1] << 16), lp[2] | (lp[3] << 16));
@@ -1510,21 +1427,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((kMaxLatticeWarps / 
 // a group every thread works with ONE alpha exponent and ONE beta exponent.  The next group's checkpoints
 // (registers) and emission tile (TMA, double buffer) are prefetched during the current one.
 constexpr int kMaxGradWarps = 10;  // ceil((2*1023+1) / 224)
+constexpr int kOccCopies = 4;  // occupancy tables per CTA (lane & 3 picks one: fewer same-address collisions)
 
 struct GradSmem {
-    size_t ytile, bar, units, cu, psort, arow, total;
-    int pitch, numax;
+    size_t ytile, bar, psort, arow, total;
+    int pitch;
 };
 __host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, int K, bool big) {
     GradSmem s;
     s.pitch = grad_row_pitch(Lmax, nq);
-    s.numax = big ? 0 : grad_max_units(C, Lmax, nq);
     size_t o = 0;
     s.ytile = o; o = align16(o + sizeof(unsigned) * 2 * kGroup * 2 * Cp);
     s.bar = o;   o = align16(o + 2 * sizeof(uint64_t));
-    s.units = o; o = align16(o + sizeof(unsigned) * s.numax);
-    s.cu = o;    o = align16(o + sizeof(int) * (big ? 0 : C + 1));
-    s.psort = o; o = align16(o + sizeof(float) * kGroup * s.pitch);
+    {
+        const size_t rows = sizeof(float) * kGroup * s.pitch, occ = sizeof(unsigned) * kOccCopies * (kGroup * Cp + 8);
+        s.psort = o; o = align16(o + (big ? rows : occ));  // small alphabets: occupancy tables instead of posterior rows
+    }
     s.arow = o;  o = align16(o + sizeof(int) * (size_t)nq * kGroup * 32 * K);
     s.total = o;
     return s;
@@ -1584,7 +1502,7 @@ __device__ __forceinline__ void grad_alpha_rows(Cells<K> &c, double pr0, double 
 
 // beta sweep over one group with posteriors: label-state posteriors -> psort (class-sorted slots), blank-state
 // posteriors summed per thread -> bpart
-template <int K, int CP, bool FULL>
+template <int K, int CP, bool FULL, bool OCC>
 __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double pr1, double f, double g,
                                                const unsigned *yt, int nrow, int blank, const int (&idx)[K / 2],
                                                const double (&skipB)[K / 2], const int (&lpos)[K / 2], bool core,
@@ -1608,13 +1526,29 @@ __device__ __forceinline__ void grad_beta_rows(Cells<K> &c, double pr0, double p
             double bb[K];
             beta_rest<K>(c.a, bb, b0, b1, s0, s1v, n1, n2, y, skipB);
             double bsum = 0.0;
+            if (OCC) {
+                // small alphabets (CTC_GRAD_OCC): occupancies accumulate as 2^-30 fixed point in [row][class] tables,
+                // integer shared-memory reductions (order-independent, hence deterministic); g carries the 2^30;
+                // round-to-nearest through the low word of (x + 2^52): one DFMA, no conversion instruction
+                unsigned *occ = reinterpret_cast<unsigned *>(psort) + r * CP + (lane % kOccCopies) * (kGroup * CP + 8);
 #pragma unroll
-            for (int h = 0; h < K / 2; ++h) {
-                bsum = fma(av[2 * h], bb[2 * h], bsum);
-                const double pl = av[2 * h + 1] * bb[2 * h + 1] * g;
-                if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
+                for (int h = 0; h < K / 2; ++h) {
+                    bsum = fma(av[2 * h], bb[2 * h], bsum);
+                    const double pl = fma(av[2 * h + 1] * bb[2 * h + 1], g, 4503599627370496.0);
+                    if (lpos[h] >= 0) atomicAdd(occ + idx[h], (unsigned)__double2loint(pl));
+                }
+                const unsigned bv =
+                    __reduce_add_sync(kFull, core ? (unsigned)__double2loint(fma(bsum, g, 4503599627370496.0)) : 0u);
+                if (lane == 0) atomicAdd(occ + blank, bv);
+            } else {
+#pragma unroll
+                for (int h = 0; h < K / 2; ++h) {
+                    bsum = fma(av[2 * h], bb[2 * h], bsum);
+                    const double pl = av[2 * h + 1] * bb[2 * h + 1] * g;
+                    if (lpos[h] >= 0) psort[r * Lp + lpos[h]] = (float)pl;
+                }
+                bpart_w[r * Lp + lane] = core ? (float)(bsum * g) : 0.f;
             }
-            bpart_w[r * Lp + lane] = core ? (float)(bsum * g) : 0.f;
             y = yn;
         }
     }
@@ -1652,8 +1586,6 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
     const GradSmem lay = grad_smem(C, Cp, p.gLmax, p.nqmax, K, BIG);
     unsigned *ytile = reinterpret_cast<unsigned *>(smem + lay.ytile);
     uint64_t *ybar = reinterpret_cast<uint64_t *>(smem + lay.bar);
-    unsigned *units = reinterpret_cast<unsigned *>(smem + lay.units);
-    int *cu = reinterpret_cast<int *>(smem + lay.cu);
     float *psort = reinterpret_cast<float *>(smem + lay.psort);
     int *arow = reinterpret_cast<int *>(smem + lay.arow) + (size_t)q * R * 32 * K;
     const int Lp = lay.pitch;                    // pitch of a posterior row
@@ -1670,15 +1602,10 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
         mbar_arrive_expect_tx(&ybar[0], rowbytes * nr0);
         tma_bulk_g2s(ytile, ybase + (size_t)(z * R) * 2 * Cp, rowbytes * nr0, &ybar[0]);
     }
-    int NU = 0;
-    if (!BIG) {
-        const int *cg = p.cu + (size_t)b * (C + 1);
-        NU = cg[C];
-        const unsigned *ug = p.units + (size_t)b * p.numax;
-        for (int c = tid; c <= C; c += blockDim.x) cu[c] = cg[c];
-        for (int u = tid; u < NU; u += blockDim.x) units[u] = ug[u];
-    }
-    __syncthreads();  // mbarrier init + unit tables visible
+    constexpr bool kOcc = !BIG;  // small alphabets: occupancies accumulate in fixed-point [row][class] tables
+    if (kOcc)
+        for (int i = tid; i < kOccCopies * (R * CP + 8); i += blockDim.x) reinterpret_cast<unsigned *>(psort)[i] = 0u;
+    __syncthreads();  // mbarrier init + cleared occupancy tables visible
     if (q >= nq) return;  // warps beyond this utterance's states
     const int nbar = nq * 32;
 
@@ -1779,7 +1706,8 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
         pb1 = __shfl_down_sync(kFull, cbeta.a[1], 1);
         if (lane == 31) { pb0 = 0.0; pb1 = 0.0; }
         // posterior(t,s) = alpha_t(s) * betabar_t(s) / P ; both exponents are constant over the group
-        const double g = pow2i(min(max(c.E, -(1 << 28)) + max(cbeta.E, -(1 << 28)) - eP, 1000)) * invP;
+        // (kOcc: times 2^30, the fixed-point scale of the occupancy tables)
+        const double g = pow2i(min(max(c.E, -(1 << 28)) + max(cbeta.E, -(1 << 28)) - eP, 960) + (kOcc ? 30 : 0)) * invP;
         float *bpart_w = bpart + q * 32;
         PROF(long long h1 = prof_clk();)
         mbar_wait(&ybar[cur], (it >> 1) & 1);
@@ -1787,19 +1715,38 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
         if (nrow == R) {
             grad_alpha_rows<K, CP, true>(c, pa, fa, yt, nrow, p.bpos, idx, skipA, lane, arow);
             PROF(h3 = prof_clk();)
-            grad_beta_rows<K, CP, true>(cbeta, pb0, pb1, fb, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
+            grad_beta_rows<K, CP, true, kOcc>(cbeta, pb0, pb1, fb, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
                                         psort, Lp, bpart_w);
         } else {
             grad_alpha_rows<K, CP, false>(c, pa, fa, yt, nrow, p.bpos, idx, skipA, lane, arow);
             PROF(h3 = prof_clk();)
-            grad_beta_rows<K, CP, false>(cbeta, pb0, pb1, fb, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
+            grad_beta_rows<K, CP, false, kOcc>(cbeta, pb0, pb1, fb, g, yt, nrow, p.bpos, idx, skipB, lpos, core, lane, arow,
                                          psort, Lp, bpart_w);
         }
         PROF(long long h4 = prof_clk();)
         named_bar_sync(1, nbar);
         PROF(float probe = *reinterpret_cast<volatile float *>(bpart + lane); long long h4b = prof_clk() + (probe > 1e30f ? 1 : 0); gb1 += h4b - h4;)
         // ---- per-class occupancy, gradient rows written once
-        if (BIG) {
+        if (kOcc) {
+            // the occupancy tables are complete: gradient rows leave as coalesced stores, the tables are cleared for
+            // the next group.  A NaN likelihood (NaN / Inf logits) makes every gradient of the utterance NaN.
+            const float scale = p.grad_scale;
+            unsigned *occ = reinterpret_cast<unsigned *>(psort);
+            const float bad = (invP == invP) ? 0.f : __int_as_float(0x7fc00000);
+            for (int i = tid; i < R * CP; i += nbar) {
+                const int r = i / CP, cc = i % CP;
+                unsigned v = 0;
+#pragma unroll
+                for (int k = 0; k < kOccCopies; ++k) {
+                    v += occ[i + k * (R * CP + 8)];
+                    occ[i + k * (R * CP + 8)] = 0u;
+                }
+                if (cc < C && r < nrow)
+                    p.grads[((size_t)(t0 + r) * p.B + b) * C + cc] =
+                        scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) -
+                                 ((float)v * (1.f / 1073741824.f) + bad));
+            }
+        } else {
             // large alphabets: the dense rows scale * softmax are already in place (ctc_prep_big_kernel); subtract the
             // occupancy of each class on the lattice.  One reduction (RED.ADD, no return value, so no DRAM round trip
             // on this thread) per (row, distinct class): a single addend per address, hence deterministic and equal
@@ -1824,47 +1771,9 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
                     }
                 }
             }
-        } else {
-            // (Measured again in round 2 and rejected: blank partials reduced by a warp per row + ONE task per
-            // (class, row) walking its whole segment, no intermediate barrier -- headline 0.110 against 0.095 ms,
-            // B = 1024 1.38 against 1.14 ms: the serial walks and their imbalance cost more than the barrier.)
-            // lane = (task slot lane>>3, row lane&7).  Phase A: one task per (unit, row) sums <= 8 adjacent posteriors
-            // (rows sit 1 bank apart, consecutive units 8 banks apart: conflict-free) and leaves the sum in the
-            // unit's first slot; phase B: one task per (class, row) adds the class's unit sums in a fixed order and
-            // writes the gradient.
-            const float scale = p.grad_scale;
-            const int r = lane & 7, slot = q * 4 + (lane >> 3);
-            float *prow = psort + r * Lp;
-            for (int u = slot; u < NU; u += 4 * nq) {
-                const unsigned un = units[u];
-                float *ps = prow + (un & 0xffffu);
-                const int len = (int)(un >> 16);
-                float v[kUnit];
-#pragma unroll
-                for (int i = 0; i < kUnit; ++i) v[i] = (i < len) ? ps[i] : 0.f;
-                ps[0] = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
-            }
-            named_bar_sync(2, nbar);
-            for (int cc = slot; cc < C; cc += 4 * nq) {
-                const int u0 = cu[cc], n = cu[cc + 1] - u0;
-                // the units of a class are consecutive pieces of its segment: unit k starts at s0 + 8k
-                const float *pu = prow + (n > 0 ? (units[u0] & 0xffffu) : 0u);
-                float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
-                int k = 0;
-                for (; k + 3 < n; k += 4) {
-                    o0 += pu[kUnit * k];
-                    o1 += pu[kUnit * (k + 1)];
-                    o2 += pu[kUnit * (k + 2)];
-                    o3 += pu[kUnit * (k + 3)];
-                }
-                for (; k < n; ++k) o0 += pu[kUnit * k];
-                if (r < nrow)
-                    p.grads[((size_t)(t0 + r) * p.B + b) * C + cc] =
-                        scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) - ((o0 + o1) + (o2 + o3)));
-            }
         }
         PROF(long long h5 = prof_clk();)
-        named_bar_sync(1, nbar);  // psort / bpart / emission buffer are reused by the next group
+        named_bar_sync(1, nbar);  // occupancy tables / posterior rows / emission buffer are reused by the next group
         PROF(long long h6 = prof_clk(); gs += h1 - h0; gw += h2 - h1; ga += h3 - h2; gb += h4 - h3; gr += h5 - h4b; gb2 += h6 - h5;)
     }
     PROF(if (lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) { long long *d = p.dbg + (32 + q) * 8; d[0] = prof_clk() - g0; d[1] = gs; d[2] = gw; d[3] = ga; d[4] = gb; d[5] = gr; d[6] = it; d[7] = gb1 * 1000000 + gb2; })

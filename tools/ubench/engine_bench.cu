@@ -45,9 +45,7 @@ int main(int argc, char **argv) {
     size_t ck = sizeof(int) * (size_t)B * p.nblk * NT * kK, ckE = sizeof(int) * (size_t)B * p.nblk * NT;
     CK(cudaMalloc(&p.ckA, ck)); CK(cudaMalloc(&p.ckB, ck)); CK(cudaMalloc(&p.ckAE, ckE)); CK(cudaMalloc(&p.ckBE, ckE));
     CK(cudaMalloc(&p.Pm, 8 * B)); CK(cudaMalloc(&p.Pe, 4 * B)); CK(cudaMalloc(&p.feas, 4 * B)); CK(cudaMalloc(&p.laboff, 4 * B));
-    CK(cudaMalloc(&p.tlab, 16 * (size_t)B * NT)); CK(cudaMalloc(&p.coff, 4 * (size_t)B * (C + 1)));
-    p.numax = grad_max_units(C, Lmax, (2 * Lmax + 1 + 223) / 224);
-    CK(cudaMalloc(&p.units, 4 * (size_t)B * p.numax)); CK(cudaMalloc(&p.cu, 4 * (size_t)B * (C + 1)));
+    CK(cudaMalloc(&p.tlab, 16 * (size_t)B * NT));
 #ifdef CTC_PROFILE
     CK(cudaMalloc(&p.dbg, 8 * 2 * B * 16 * 8 + 8192)); CK(cudaMemset(p.dbg, 0, 8 * 2 * B * 16 * 8 + 8192));
 #endif

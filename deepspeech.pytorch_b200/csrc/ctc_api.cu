@@ -160,9 +160,14 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         // deal the time groups of an utterance round-robin to enough CTAs for ~7 waves of resident CTAs: utterances
         // differ in length and lattice width, so many small CTAs balance better than a few long ones (measured on
         // the headline shape: 10 CTAs/utterance 154 us, 19: 141, 32: 139, 63: 141)
-        const int resident = (int)(kSmemLimit / pl->smem_grad) > 0 ? (int)(kSmemLimit / pl->smem_grad) : 1;
+        // resident CTAs per SM: shared memory, and 128 registers per thread (the kernel's __maxnreg__)
+        const int by_smem = (int)(kSmemLimit / pl->smem_grad) > 0 ? (int)(kSmemLimit / pl->smem_grad) : 1;
+        const int by_regs = 65536 / (128 * 32 * pl->nqmax) > 0 ? 65536 / (128 * 32 * pl->nqmax) : 1;
+        const int resident = by_smem < by_regs ? by_smem : by_regs;
         int ns = (7 * 148 * resident + B - 1) / B;
         if (ns > pl->nblk / 2) ns = pl->nblk / 2;  // >= 2 groups per CTA (measured 2: 0.233, 4: 0.235, 6: 0.240 ms/step)
+        ns = env_int("CTC_B200_NSPLIT", ns);       // tuning experiments
+        if (ns > pl->nblk) ns = pl->nblk;
         if (ns < 1) ns = 1;
         pl->nsplit = ns;
         // Warp classes (small alphabets, >= 2 gradient warps): an utterance whose lattice fits half of the warps would
@@ -183,8 +188,10 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         if (pl->nq_small) {
             pl->smem_grad_small =
                 grad_smem(C, pl->Cp, grad_class_lmax(pl->nq_small, Lmax), pl->nq_small, kK, false).total;
-            const int res = (int)(kSmemLimit / pl->smem_grad_small) > 0 ? (int)(kSmemLimit / pl->smem_grad_small) : 1;
-            int n2 = (7 * 148 * (res > 8 ? 8 : res) + B - 1) / B;
+            int res = (int)(kSmemLimit / pl->smem_grad_small) > 0 ? (int)(kSmemLimit / pl->smem_grad_small) : 1;
+            const int res_regs = 65536 / (128 * 32 * pl->nq_small);
+            if (res > res_regs) res = res_regs;
+            int n2 = (7 * 148 * res + B - 1) / B;
             if (n2 > pl->nblk / 2) n2 = pl->nblk / 2;
             pl->nsplit_small = n2 < 1 ? 1 : n2;
         }

@@ -13,6 +13,8 @@ import subprocess
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, "libctc_b200.so")
+if os.environ.get("CTC_B200_LIB"):  # A/B experiments: another in-tree build of the same sources (e.g. other -D constants)
+    LIB_PATH = os.path.abspath(os.environ["CTC_B200_LIB"])
 SOURCES = [os.path.join(_PKG, "csrc", f) for f in ("ctc_api.cu", "ctc_kernels.cuh", "ctc_device.cuh", "ctc_metrics.cuh",
                                                    "fc_kernels.cuh")] + [
     os.path.join(_ROOT, "include", "ctc_b200.h")

@@ -253,6 +253,24 @@ class Bench:
         self.torch.cuda.synchronize()
         return self.b.last_launch_count()
 
+    def graph_replay_ms(self, nsteps):
+        """the same step captured once in a CUDA graph and replayed (one launch per step instead of ~25 API calls)"""
+        torch = self.torch
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self.step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            self.step()
+        self.timed(5, fn=graph.replay)
+        ms = self.timed(nsteps, fn=graph.replay)
+        del graph
+        return sum(ms) / len(ms)
+
     def device_step_ms(self, nsteps):
         """max over ranks of the summed device time of `nsteps` steps, per step (barrier + sync on both sides)"""
         torch, dist = self.torch, self.dist
@@ -478,8 +496,12 @@ def run_b200(args, w):
     frames = bn.frames
 
     comparators, module = None, None
-    control = None
+    control, replay = None, None
     if not args.quick:
+        if world == 1:
+            rms = bn.graph_replay_ms(nk)
+            replay = {"ms_per_step": rms, "value": frames / (rms * 1e-3), "unit": UNIT,
+                      "what": "the same step captured in a CUDA graph and replayed; `value` above is the eager launch"}
         module = bn.module_ms(nk)
         tc_ms = bn.torch_cuda_ctc_ms(min(nk, 10))
         comparators = {"torch_cuda_ctc": {"ms_per_step": tc_ms, "value": frames * world / (tc_ms * 1e-3), "unit": UNIT,
@@ -561,6 +583,8 @@ def run_b200(args, w):
             line["comparators"] = comparators
         if module:
             line["module_step_ms"] = module
+        if replay:
+            line["cuda_graph_replay"] = replay
         if control:
             line["weak_scaling_control"] = control
         if others:

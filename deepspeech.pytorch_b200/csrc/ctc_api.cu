@@ -1176,6 +1176,8 @@ struct ctcB200Context {
     size_t n_acts = 0, n_grads = 0, n_costs = 0, n_ws = 0, n_meta = 0, n_hmeta = 0;
     cudaStream_t side[kHostChunks] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t done[kHostChunks] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t uploaded[kHostChunks] = {nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t up = nullptr;  // all uploads, one after the other: the first slice gets the whole link
     cudaEvent_t start = nullptr;
     bool streams_ok = false;
 };
@@ -1193,9 +1195,11 @@ static bool grow(void **ptr, size_t *have, size_t need) {
 static bool make_streams(ctcB200Context *c) {
     if (c->streams_ok) return true;
     if (cudaEventCreateWithFlags(&c->start, cudaEventDisableTiming) != cudaSuccess) return false;
+    if (cudaStreamCreateWithFlags(&c->up, cudaStreamNonBlocking) != cudaSuccess) return false;
     for (int k = 0; k < kHostChunks; ++k) {
         if (cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking) != cudaSuccess) return false;
         if (cudaEventCreateWithFlags(&c->done[k], cudaEventDisableTiming) != cudaSuccess) return false;
+        if (cudaEventCreateWithFlags(&c->uploaded[k], cudaEventDisableTiming) != cudaSuccess) return false;
     }
     c->streams_ok = true;
     return true;
@@ -1218,7 +1222,9 @@ extern "C" ctcB200Status ctc_b200_destroy(ctcB200Context *c) {
     for (int k = 0; k < kHostChunks; ++k) {
         if (c->side[k]) cudaStreamDestroy(c->side[k]);
         if (c->done[k]) cudaEventDestroy(c->done[k]);
+        if (c->uploaded[k]) cudaEventDestroy(c->uploaded[k]);
     }
+    if (c->up) cudaStreamDestroy(c->up);
     if (c->start) cudaEventDestroy(c->start);
     delete c;
     return CTC_B200_STATUS_SUCCESS;
@@ -1349,10 +1355,19 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
     // Chunks are issued in batch order.  On the reference's length-sorted batches that is longest first, i.e. the
     // critical recursion starts first.  Measured and rejected: longest first, then the others shortest first (so that
     // their downloads would not queue behind the long chunk's) -- uploads and downloads contend on the link and the
-    // call got slower (headline batch: 1.66e8 against 1.95e8 frames/s).
+    // call got slower (headline batch: 1.66e8 against 1.95e8 frames/s); with the serial upload stream below the two
+    // orders measure the same (1.99e8 / 2.01e8): the slice uploaded last then is the second longest, and the call ends
+    // with ITS recursion instead of with the queue of downloads.
+    // Uploads go through ONE stream, slice after slice: issued on the slices' own streams they share the link, and the
+    // first slice -- the longest utterances on the reference's length-sorted batches, i.e. the critical recursion --
+    // would have its logits only when nearly everything has arrived.  CTC_B200_HOST_SERIAL_UPLOAD=0: the old way.
+    static const bool serial_up = env_int("CTC_B200_HOST_SERIAL_UPLOAD", 1) != 0;
+    if (nch > 1 && serial_up && cudaStreamWaitEvent(c->up, c->start, 0) != cudaSuccess)
+        return CTC_B200_STATUS_EXECUTION_FAILED;
     for (int k = 0; k < nch; ++k) {
         const int b0 = b0s[k], nb = b0s[k + 1] - b0;
         cudaStream_t st = nch > 1 ? c->side[k] : user;
+        cudaStream_t sup = (nch > 1 && serial_up) ? c->up : st;
         if (nch > 1 && cudaStreamWaitEvent(st, c->start, 0) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
         // compact device copies [T][nb][C] of this slice (rows of the host tensor are B*C floats apart)
         float *da = c->d_acts + (size_t)T * b0 * C;
@@ -1360,8 +1375,12 @@ extern "C" ctcB200Status ctc_b200_compute_host(ctcB200Context *c, const float *a
         const size_t width = (size_t)nb * C * sizeof(float);
         const int Tk = Ts[k];
         if (Tk > 0 && cudaMemcpy2DAsync(da, width, acts_host + (size_t)b0 * C, host_pitch, width, (size_t)Tk,
-                                        cudaMemcpyHostToDevice, st) != cudaSuccess)
+                                        cudaMemcpyHostToDevice, sup) != cudaSuccess)
             return CTC_B200_STATUS_MEMOPS_FAILED;
+        if (sup != st) {
+            if (cudaEventRecord(c->uploaded[k], sup) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+            if (cudaStreamWaitEvent(st, c->uploaded[k], 0) != cudaSuccess) return CTC_B200_STATUS_EXECUTION_FAILED;
+        }
         h2d += (unsigned long long)width * Tk;
         d2h += (dg ? (unsigned long long)width * Tk : 0ull) + sizeof(float) * (size_t)nb;
         if (trace) cudaEventRecord(tr[k][0], st);

@@ -138,7 +138,9 @@ def ctc_forward_backward(acts: torch.Tensor, labels, act_lens, label_lens, blank
         if on_dev:
             if max_label_len is None:
                 raise ValueError("max_label_len is required when lengths live on the device (avoids a sync)")
-            lmax = int(max_label_len)
+            # an upper BOUND on the label lengths; the ABI reads 0 as "not given", so a batch of empty transcripts
+            # (bound 0) is passed as 1
+            lmax = max(int(max_label_len), 1)
         else:
             lmax = int(label_lens.max().item()) if B > 0 else 0
             if max_label_len is not None:

@@ -40,14 +40,17 @@ def _max_abs_diff(grads_f32, og, scale=1.0):
     return worst
 
 
-def _check(oracle, b200, d, **kw):
+def _check(oracle, b200, d, cost_floor=1e-30, **kw):
+    """cost_floor: costs below it are compared with the absolute error LOSS_RTOL * cost_floor (the emission
+    probabilities are fp32, as in the reference: a cost of 1e-5 -- every frame's probability within 1e-5 of 1 -- cannot be
+    right to 5 digits, its fp32 probability is off by up to 6e-8)"""
     big = d["acts"].numel() > (1 << 26)
     costs, grads = _run(b200, d, as_numpy=not big, **kw)
     oc, og = oracle.compute(d["acts"].numpy(), d["labels"].numpy(), d["act_lens"].numpy(), d["label_lens"].numpy(),
                             blank=kw.get("blank", 0), zero_infinity=kw.get("zero_infinity", True))
     fin = np.isfinite(oc)
     assert np.array_equal(np.isfinite(costs), fin)
-    rel = np.abs(costs[fin] - oc[fin]) / np.maximum(np.abs(oc[fin]), 1e-30)
+    rel = np.abs(costs[fin] - oc[fin]) / np.maximum(np.abs(oc[fin]), cost_floor)
     # per-utterance costs are fp32 on the device: allow fp32 rounding of the value itself
     assert rel.max(initial=0.0) <= LOSS_RTOL, f"cost rel err {rel.max()}"
     tot_rel = abs(costs[fin].sum() - oc[fin].sum()) / max(abs(oc[fin].sum()), 1e-30)
@@ -300,6 +303,39 @@ def test_edge_cases(oracle, b200):
     assert costs[0] == 0.0 and costs[5] == 0.0 and np.all(grads[:, 0] == 0) and np.all(grads[:, 5] == 0)
     costs, grads = _run(b200, d, zero_infinity=False)
     assert np.isinf(costs[0]) and np.isinf(costs[5]) and np.all(np.isfinite(grads)) and np.all(grads[:, 0] == 0)
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("CTC_TEST_RANDOM_SHAPES", "40"))))
+def test_randomised_shapes(oracle, b200, seed, monkeypatch):
+    # random small problems over everything that changes a launch plan: alphabet size (all three small-alphabet
+    # instantiations and the large-alphabet path), blank index, batch size (slicing starts at 16), slice count, one
+    # gradient launch or two warp classes, label lengths from 0 up to several gradient warps, tight and infeasible
+    # utterances, heavy label repetition
+    rng = np.random.default_rng(1000 + seed)
+    C = int(rng.choice([2, 3, 7, 29, 32, 33, 64, 97, 128, 129, 300]))
+    B = int(rng.choice([1, 3, 16, 21, 40]))
+    T = int(rng.choice([1, 9, 64, 257, 600]))
+    blank = int(rng.integers(0, C))
+    monkeypatch.setenv("CTC_B200_SLICES", str(int(rng.choice([1, 2, 5, 8]))))
+    monkeypatch.setenv("CTC_B200_GRAD_CLASSES", str(int(rng.integers(0, 2))))
+    act_lens = rng.integers(max(1, T // 3), T + 1, size=B).astype(np.int32)
+    act_lens[rng.integers(0, B)] = T
+    lens, labs = [], []
+    symbols = [c for c in range(C) if c != blank]
+    for b in range(B):
+        n = int(rng.integers(0, min(int(act_lens[b]), 400) + 1))
+        if rng.random() < 0.3:
+            n = n // 8
+        few = rng.random() < 0.3  # few distinct symbols: many repeats (each needs a blank between)
+        pool = symbols[:2] if few and len(symbols) > 1 else symbols
+        lab = rng.choice(pool, size=n).astype(np.int32) if n else np.zeros(0, np.int32)
+        lens.append(n)
+        labs.append(lab)
+    d = {"acts": torch.from_numpy((rng.standard_normal((T, B, C)) * rng.choice([0.5, 1.0, 4.0])).astype(np.float32)),
+         "labels": torch.from_numpy(np.concatenate(labs) if labs else np.zeros(0, np.int32)),
+         "act_lens": torch.from_numpy(act_lens), "label_lens": torch.tensor(lens, dtype=torch.int32)}
+    # (cost_floor: absolute error 5e-7 on near-zero costs = a few frames' worth of fp32 probability rounding, 6e-8 each)
+    _check(oracle, b200, d, cost_floor=5e-2, blank=blank, device_lens=bool(rng.integers(0, 2)))
 
 
 def test_uniform_logits_count(oracle, b200):

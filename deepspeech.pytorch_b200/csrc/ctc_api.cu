@@ -219,7 +219,9 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
         pl->nslices = ns;
         if (ns > 1 && pl->smem_prep < sizeof(int) * (size_t)B) pl->smem_prep = sizeof(int) * (size_t)B;
         // (Padding the engine's shared-memory request to keep gradient CTAs of other slices off its SM was measured:
-        // no effect at 0 / 120 / 180 KB, so engines simply request what they use.)
+        // no effect at 0 / 120 / 180 KB, so engines simply request what they use.  Likewise one engine CTA per SM
+        // when 2B exceeds the SM count: B=128 recursion 155 -> 174 us, B=160 163 -> 218: two CTAs share an SM better
+        // than the second one waits for it -- tools/batch_size_probe.py.)
         const size_t req = 0;
         pl->smem_engine_req = req > pl->smem_engine ? req : pl->smem_engine;
     }

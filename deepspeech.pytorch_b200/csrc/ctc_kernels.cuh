@@ -1435,7 +1435,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((kMaxLatticeWarps / 
 // a group every thread works with ONE alpha exponent and ONE beta exponent.  The next group's checkpoints
 // (registers) and emission tile (TMA, double buffer) are prefetched during the current one.
 constexpr int kMaxGradWarps = 10;  // ceil((2*1023+1) / 224)
-constexpr int kOccCopies = 4;  // occupancy tables per CTA (lane & 3 picks one: fewer same-address collisions)
+#ifndef CTC_OCC_COPIES
+#define CTC_OCC_COPIES 4
+#endif
+// occupancy tables per CTA (lane % copies picks one: fewer same-address collisions).  Gradient kernel alone, B=64 /
+// B=1024: 1 copy 84.1 / 909 us, 2: 86.2 / 948, 4: 82.0 / 885, 8: 82.0 / 913
+constexpr int kOccCopies = CTC_OCC_COPIES;
 
 struct GradSmem {
     size_t ytile, bar, psort, arow, total;

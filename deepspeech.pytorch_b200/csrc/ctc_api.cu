@@ -93,10 +93,7 @@ int env_int(const char *name, int dflt) {
 // issues fewer instructions per step (its warp-edge accesses are branches, not predicated instructions on all lanes)
 // and wins once three or more engine CTAs share an SM and the kernel is bound by issue slots instead of latency (B=256:
 // 259 against 270 us, B=1024: 731 against 790).  CTC_B200_ENGINE=1 / 2 forces one form (A/B measurements); 0 = by batch.
-int engine_version() {
-    static const int v = env_int("CTC_B200_ENGINE", 0);
-    return v;
-}
+int engine_version() { return env_int("CTC_B200_ENGINE", 0); }  // read per call: tests switch it inside one process
 inline bool engine_first_form(int B) {
     const int v = engine_version();
     // measured crossover (T=1500, C=29, us, first / second form): B=96 192 / 154, B=128 192 / 164, B=160 188 / 168,
@@ -228,7 +225,7 @@ bool make_plan(int T, int B, int C, int Lmax, Plan *pl) {
     size_t o = 0;
     const size_t ck = sizeof(int) * (size_t)B * pl->nblk * NT * kK;
     const size_t ckE = sizeof(int) * (size_t)B * pl->nblk * NT;
-    pl->o_y = o;      o = align256(o + sizeof(unsigned) * (size_t)T * B * 2 * pl->Cp);
+    pl->o_y = o;      o = align256(o + sizeof(unsigned) * (size_t)T * B * kYP * pl->Cp);
     pl->o_ckA = o;    o = align256(o + ck);
     pl->o_ckB = o;    o = align256(o + ck);
     pl->o_ckAE = o;   o = align256(o + ckE);

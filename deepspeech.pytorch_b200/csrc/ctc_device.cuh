@@ -155,6 +155,13 @@ struct YRow {
 // (Measured, tools/ubench/lat3.cu: interleaved fp64 rows need 2-4 wavefronts per LDS.64 gather and make the step
 // LSU-bound, 78 vs 43 clk; fp32 rows + conversion cost either the FP64 pipe (cvt) or ~20 extra integer/move
 // instructions per step.)  Row r of a tile starts at word r * 2 * CP: all offsets fold into immediates.
+// CTC_Y_PLANES = 1: only the high-word plane exists -- the emission probabilities rounded to 21 significant bits
+// (relative 2^-22): half the emission bytes, tile copies and gathers.  tools/y_rounding_study.py: on a T = 1500,
+// L = 400 utterance the cost moves by 1.5e-8 relative and the per-class occupancies by <= 6.6e-7.
+#ifndef CTC_Y_PLANES
+#define CTC_Y_PLANES 1
+#endif
+constexpr int kYP = CTC_Y_PLANES;
 template <int K, int CP>
 __device__ __forceinline__ void load_y(YRow<K> &y, const unsigned *tile, int r, int blank_idx, const int (&idx)[K / 2]) {
 #ifdef CTC_EXP_NOY
@@ -163,17 +170,26 @@ __device__ __forceinline__ void load_y(YRow<K> &y, const unsigned *tile, int r, 
     for (int h = 0; h < K / 2; ++h) y.yl[h] = 0.9 + 1e-9 * idx[h];
     (void)tile; (void)r;
 #else
-    const unsigned *row = tile + r * 2 * CP;
-    y.yb = __hiloint2double((int)row[blank_idx], (int)row[CP + blank_idx]);
+    const unsigned *row = tile + r * kYP * CP;
+    y.yb = __hiloint2double((int)row[blank_idx], kYP == 2 ? (int)row[CP + blank_idx] : 0);
 #pragma unroll
-    for (int h = 0; h < K / 2; ++h) y.yl[h] = __hiloint2double((int)row[idx[h]], (int)row[CP + idx[h]]);
+    for (int h = 0; h < K / 2; ++h)
+        y.yl[h] = __hiloint2double((int)row[idx[h]], kYP == 2 ? (int)row[CP + idx[h]] : 0);
 #endif
 }
 // exact fp32 -> planar fp64 words (positive normal floats only: y is clamped to >= 2^-126) and back
-__device__ __forceinline__ unsigned y_hi_word(float x) { return (__float_as_uint(x) >> 3) + 0x38000000u; }
+// (one plane: the high word is ROUNDED to nearest -- a carry into the exponent field is the right answer)
+__device__ __forceinline__ unsigned y_hi_word(float x) {
+    return ((__float_as_uint(x) + (kYP == 2 ? 0u : 4u)) >> 3) + 0x38000000u;
+}
 __device__ __forceinline__ unsigned y_lo_word(float x) { return __float_as_uint(x) << 29; }
 __device__ __forceinline__ float y_from_words(unsigned hi, unsigned lo) {
-    return __uint_as_float(((hi - 0x38000000u) << 3) | (lo >> 29));
+    return __uint_as_float(((hi - 0x38000000u) << 3) | (kYP == 2 ? (lo >> 29) : 0u));
+}
+// the emission probability of class cc in row r of a tile at pitch CP, as fp32
+__device__ __forceinline__ float y_of_tile(const unsigned *tile, int r, int CP, int cc) {
+    const unsigned *row = tile + r * kYP * CP;
+    return y_from_words(row[cc], kYP == 2 ? row[CP + cc] : 0u);
 }
 
 // alpha_t(s) = y_t(l'_s) * (alpha_{t-1}(s) + alpha_{t-1}(s-1) + [skip] alpha_{t-1}(s-2))      

@@ -2,7 +2,7 @@
 //
 //   ctc_prep_kernel   : grid ceil(T*B/128) + B (+1).  Row blocks: fused softmax over C per (t,b) -- coalesced float4
 //                       loads of 128 consecutive rows into shared memory, one thread per row for max / sum, coalesced
-//                       stores of the emission rows y[b,t,:] as PLANAR fp64 words (Cp high words, Cp low words;
+//                       stores of the emission rows y[b,t,:] as fp64 HIGH words (kYP = 1; kYP = 2: + a plane of low words;
 //                       utterance-major, so the 8 rows of a group are ONE TMA bulk copy); padding frames get their
 //                       zero gradient rows here.  Utterance blocks: label offsets and the per-thread label table.
 //                       Extra block of a sliced launch: utterances ranked by length (sort_by_length).
@@ -47,7 +47,7 @@ struct CtcParams {
     int Lmax;  // max label length
     int score_only;
     // workspace
-    unsigned *y;        // [B][T][2*Cp] softmax rows, planar fp64: Cp high words then Cp low words (exact widening
+    unsigned *y;        // [B][T][kYP*Cp] softmax rows: Cp high words of the fp64 values (kYP = 2: then Cp low words; exact widening
                         // of the fp32 softmax, clamped to >= 2^-126)
     int *ckA, *ckB;     // [B][nblk][nwl][K/4][32] int4: checkpoint mantissas as rounded high words (hi_round)
     int *ckAE, *ckBE;   // [B][nblk][nwl*32]   exponents
@@ -333,7 +333,7 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
             const float inv = 1.0f / sum;
             if (active) {
                 // y clamped to >= 2^-126: a feasible alignment never gets probability exactly 0 from fp32 underflow
-                unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * Cp;  // utterance-major: a tile of rows is one bulk copy
+                unsigned *ydst = p.y + ((size_t)b * p.T + t) * kYP * Cp;  // utterance-major: a tile of rows is one bulk copy
                 uint4 hi, lo;
                 float v = fmaxf(e[0] * inv, 1.17549435e-38f); hi.x = y_hi_word(v); lo.x = y_lo_word(v);
                 v = fmaxf(e[1] * inv, 1.17549435e-38f); hi.y = y_hi_word(v); lo.y = y_lo_word(v);
@@ -348,7 +348,7 @@ __global__ void __launch_bounds__(kPrepRows) ctc_prep_kernel(const CtcParams p) 
                     lo = make_uint4(0u, 0u, 0u, 0u);
                 }
                 *reinterpret_cast<uint4 *>(ydst + 4 * j) = hi;
-                *reinterpret_cast<uint4 *>(ydst + Cp + 4 * j) = lo;
+                if (kYP == 2) *reinterpret_cast<uint4 *>(ydst + Cp + 4 * j) = lo;
             } else if (valid && p.grads) {
                 // padding frame (t >= act_lens[b]): never read by the lattice kernels; its gradient row is zero
 #pragma unroll
@@ -401,7 +401,7 @@ __host__ __device__ inline EngineSmem engine_smem(int Cp, int nwl) {
     EngineSmem s;
     s.nstage = nwl + look_ahead(Cp) + 1;
     size_t o = 0;
-    s.ytile = o; o = align16(o + sizeof(unsigned) * s.nstage * kGroup * 2 * Cp);
+    s.ytile = o; o = align16(o + sizeof(unsigned) * s.nstage * kGroup * kYP * Cp);
     s.bars = o;  o = align16(o + sizeof(uint64_t) * s.nstage);
     s.slots = o; o = align16(o + sizeof(Slot) * kMaxLatticeWarps * kRing);
     s.misc = o;  o = align16(o + 64);
@@ -580,8 +580,8 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
             fence_mbar_init();
         }
         __syncwarp();
-        const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
-        const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
+        const unsigned *ybase = p.y + (size_t)b * p.T * kYP * Cp;
+        const uint32_t rowbytes = (uint32_t)(kYP * Cp * sizeof(unsigned));
         int ist = 0;  // ring slot of the next tile to issue (issue() is called with j = 0, 1, 2, ...)
         auto issue = [&](int j) {
             const int st = ist;
@@ -591,7 +591,7 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
                 const int t0 = G * kGroup;
                 const int nr = min(kGroup, Tb - t0);
                 mbar_arrive_expect_tx(&y_full[st], rowbytes * nr);
-                tma_bulk_g2s(ytile + (size_t)(st * kGroup) * 2 * Cp, ybase + (size_t)t0 * 2 * Cp, rowbytes * nr,
+                tma_bulk_g2s(ytile + (size_t)(st * kGroup) * kYP * Cp, ybase + (size_t)t0 * kYP * Cp, rowbytes * nr,
                              &y_full[st]);
             }
         };
@@ -713,7 +713,7 @@ __global__ void __launch_bounds__((kMaxLatticeWarps + 1) * 32) ctc_engine_kernel
             }
         }
         t0 += dt;
-        yt += kGroup * 2 * Cp;
+        yt += kGroup * kYP * Cp;
         if (++st == NS) { st = 0; yt = ytile; }
         PROF(long long tb = prof_clk();)
         named_bar_sync(1, nbar);
@@ -1164,7 +1164,7 @@ __device__ __forceinline__ void engine_lattice(const CtcParams &p, int b, int wa
             ckEp += ckEstep;
             // next tile: its first row is fetched here, before the barrier (the producer guarantees tile j + 1 of
             // this warp has landed: it waits one tile further ahead than the lattice needs)
-            yt += kGroup * 2 * Cp;
+            yt += kGroup * kYP * Cp;
             if (++st == NS) { st = 0; yt = ytile; }
 #ifndef CTC_V2_NOPREFETCH
             if (j + 1 < je) load_y<K, CP>(y, yt, FWD ? 0 : kGroup - 1, blank, idx);  // (the next part loads its own)
@@ -1265,8 +1265,8 @@ __device__ __forceinline__ void engine_producer(const CtcParams &p, int b, bool 
         fence_mbar_init();
     }
     __syncwarp();
-    const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
-    const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
+    const unsigned *ybase = p.y + (size_t)b * p.T * kYP * Cp;
+    const uint32_t rowbytes = (uint32_t)(kYP * Cp * sizeof(unsigned));
     int ist = 0;
     auto issue = [&](int j) {
         const int st = ist;
@@ -1276,7 +1276,7 @@ __device__ __forceinline__ void engine_producer(const CtcParams &p, int b, bool 
             const int t0 = G * kGroup;
             const int nr = min(kGroup, Tb - t0);
             mbar_arrive_expect_tx(&y_full[st], rowbytes * nr);
-            tma_bulk_g2s(ytile + (size_t)(st * kGroup) * 2 * Cp, ybase + (size_t)t0 * 2 * Cp, rowbytes * nr,
+            tma_bulk_g2s(ytile + (size_t)(st * kGroup) * kYP * Cp, ybase + (size_t)t0 * kYP * Cp, rowbytes * nr,
                          &y_full[st]);
         }
     };
@@ -1450,7 +1450,7 @@ __host__ __device__ inline GradSmem grad_smem(int C, int Cp, int Lmax, int nq, i
     GradSmem s;
     s.pitch = grad_row_pitch(Lmax, nq);
     size_t o = 0;
-    s.ytile = o; o = align16(o + sizeof(unsigned) * 2 * kGroup * 2 * Cp);
+    s.ytile = o; o = align16(o + sizeof(unsigned) * 2 * kGroup * kYP * Cp);
     s.bar = o;   o = align16(o + 2 * sizeof(uint64_t));
     {
         const size_t rows = sizeof(float) * kGroup * s.pitch, occ = sizeof(unsigned) * kOccCopies * (kGroup * Cp + 8);
@@ -1606,8 +1606,8 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
     const int Lp = lay.pitch;                    // pitch of a posterior row
     const int Lb = grad_blank_off(L, p.Lmax);    // where the blank partial sums start inside a row
     float *bpart = psort + Lb;                   // [row * Lp + warp * 32 + lane]
-    const uint32_t rowbytes = (uint32_t)(2 * Cp * sizeof(unsigned));
-    const unsigned *ybase = p.y + (size_t)b * p.T * 2 * Cp;
+    const uint32_t rowbytes = (uint32_t)(kYP * Cp * sizeof(unsigned));
+    const unsigned *ybase = p.y + (size_t)b * p.T * kYP * Cp;
 
     if (tid == 0) {
         mbar_init(&ybar[0], 1);
@@ -1615,7 +1615,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
         fence_mbar_init();
         const int nr0 = min(R, Tb - z * R);
         mbar_arrive_expect_tx(&ybar[0], rowbytes * nr0);
-        tma_bulk_g2s(ytile, ybase + (size_t)(z * R) * 2 * Cp, rowbytes * nr0, &ybar[0]);
+        tma_bulk_g2s(ytile, ybase + (size_t)(z * R) * kYP * Cp, rowbytes * nr0, &ybar[0]);
     }
     constexpr bool kOcc = !BIG;  // small alphabets: occupancies accumulate in fixed-point [row][class] tables
     if (kOcc)
@@ -1668,7 +1668,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
         const int cur = it & 1;
         const int t0 = blk * R;
         const int nrow = min(R, Tb - t0);
-        const unsigned *yt = ytile + (size_t)cur * R * 2 * Cp;
+        const unsigned *yt = ytile + (size_t)cur * R * kYP * Cp;
         // ---- current checkpoints out of the prefetch registers, then prefetch the next group
         Cells<K> c;
         double bsave[K];
@@ -1687,7 +1687,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
                 const int nrn = min(R, Tb - nblk_next * R);
                 fence_proxy_async();
                 mbar_arrive_expect_tx(&ybar[cur ^ 1], rowbytes * nrn);
-                tma_bulk_g2s(ytile + (size_t)(cur ^ 1) * R * 2 * Cp, ybase + (size_t)(nblk_next * R) * 2 * Cp,
+                tma_bulk_g2s(ytile + (size_t)(cur ^ 1) * R * kYP * Cp, ybase + (size_t)(nblk_next * R) * kYP * Cp,
                              rowbytes * nrn, &ybar[cur ^ 1]);
             }
             fetch(nblk_next);
@@ -1758,7 +1758,7 @@ __global__ void CTC_GRAD_ATTR ctc_grad_kernel(const CtcParams p) {
                 }
                 if (cc < C && r < nrow)
                     p.grads[((size_t)(t0 + r) * p.B + b) * C + cc] =
-                        scale * (y_from_words(yt[r * 2 * Cp + cc], yt[r * 2 * Cp + Cp + cc]) -
+                        scale * (y_of_tile(yt, r, Cp, cc) -
                                  ((float)v * (1.f / 1073741824.f) + bad));
             }
         } else {
@@ -1944,7 +1944,7 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const Ctc
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
     const int off = p.laboff[b];  // written by ctc_prep_utt_kernel, launched before this kernel
     const float *srow = reinterpret_cast<const float *>(s4);
-    unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * CP;
+    unsigned *ydst = p.y + ((size_t)b * p.T + t) * kYP * CP;
     for (int j = tid; j < CP; j += kBigThreads) {
         float y = 1.17549435e-38f;
         if (j <= L) {
@@ -1952,7 +1952,7 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_reg_kernel(const Ctc
             y = fmaxf(srow[c] * inv, 1.17549435e-38f);
         }
         ydst[j] = bad ? kNanHi : y_hi_word(y);
-        ydst[CP + j] = bad ? 0u : y_lo_word(y);
+        if (kYP == 2) ydst[CP + j] = bad ? 0u : y_lo_word(y);
     }
 }
 
@@ -2061,7 +2061,7 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
     const int L = min(max(p.label_lens[b], 0), p.Lmax);
     const int *lab = p.labels;
     const int off = p.laboff[b];  // written by ctc_prep_utt_kernel, launched before this kernel
-    unsigned *ydst = p.y + ((size_t)b * p.T + t) * 2 * CP;
+    unsigned *ydst = p.y + ((size_t)b * p.T + t) * kYP * CP;
     for (int j = tid; j < CP; j += kBigThreads) {
         float v = 1.17549435e-38f;
         if (j <= L) {
@@ -2070,7 +2070,7 @@ __global__ void __launch_bounds__(kBigThreads) ctc_prep_big_kernel(const CtcPara
             v = fmaxf(e * inv, 1.17549435e-38f);
         }
         ydst[j] = bad ? kNanHi : y_hi_word(v);
-        ydst[CP + j] = bad ? 0u : y_lo_word(v);
+        if (kYP == 2) ydst[CP + j] = bad ? 0u : y_lo_word(v);
     }
 }
 

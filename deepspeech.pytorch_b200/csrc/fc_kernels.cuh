@@ -499,7 +499,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
             }
             const float inv = 1.0f / sum;
             const bool bad = sum != sum;
-            uint4 *yd = reinterpret_cast<uint4 *>(p.y + ((size_t)b * p.T + t) * 2 * N);
+            uint4 *yd = reinterpret_cast<uint4 *>(p.y + ((size_t)b * p.T + t) * kYP * N);
 #pragma unroll
             for (int c = 0; c < N; c += 4) {
                 uint4 hw, l;
@@ -509,7 +509,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                 e = fmaxf(v[c + 3] * inv, 1.17549435e-38f);       hw.w = y_hi_word(e); l.w = y_lo_word(e);
                 if (bad) { hw = make_uint4(0x7ff80000u, 0x7ff80000u, 0x7ff80000u, 0x7ff80000u); l = make_uint4(0, 0, 0, 0); }
                 yd[c / 4] = hw;
-                yd[N / 4 + c / 4] = l;
+                if (kYP == 2) yd[N / 4 + c / 4] = l;
             }
           }
         }
@@ -813,7 +813,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
             }
             const float inv = 1.0f / sum;
             const bool bad = sum != sum;
-            uint4 *yd = reinterpret_cast<uint4 *>(p.y + ((size_t)b * p.T + t) * 2 * N);
+            uint4 *yd = reinterpret_cast<uint4 *>(p.y + ((size_t)b * p.T + t) * kYP * N);
 #pragma unroll
             for (int c = 0; c < N; c += 4) {
                 uint4 hw, l;
@@ -823,7 +823,7 @@ __global__ void __launch_bounds__(kFcThreads, 1)
                 e = fmaxf(v[c + 3] * inv, 1.17549435e-38f);       hw.w = y_hi_word(e); l.w = y_lo_word(e);
                 if (bad) { hw = make_uint4(0x7ff80000u, 0x7ff80000u, 0x7ff80000u, 0x7ff80000u); l = make_uint4(0, 0, 0, 0); }
                 yd[c / 4] = hw;
-                yd[N / 4 + c / 4] = l;
+                if (kYP == 2) yd[N / 4 + c / 4] = l;
             }
           }
         }

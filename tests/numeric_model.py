@@ -3,7 +3,8 @@
 Not an oracle and not the product: it mirrors, array-for-thread, the arithmetic of csrc/ctc_device.cuh and
 csrc/ctc_kernels.cuh so the representation can be checked on the CPU against oracle/ before any GPU time is spent:
 
-  * emissions y = softmax(acts) in fp32, clamped to >= 2^-126, widened (exactly) to fp64
+  * emissions y = softmax(acts) in fp32, clamped to >= 2^-126, widened (exactly) to fp64 (the kernels have since gone
+    to the rounded high word of that value, 21 significant bits: DESIGN.md section 3; this model keeps the exact one)
   * alpha / beta in the LINEAR domain, fp64 mantissa, one int exponent per group of K adjacent states
     ("thread"), value = m * 2^E
   * renormalisation every N steps: group max -> [1,2)  (exact power-of-two scaling)
